@@ -1,0 +1,217 @@
+// Gauss-Newton two-basis material decomposition, one independent 2x2 Newton problem per sinogram pixel.
+// Replaces optimize_sino_cpu (/root/reference/matdecomp.py:87-127) and the masking of get_basismat_sinos
+// (matdecomp.py:195-205).
+//
+// Per pixel and iteration (matdecomp.py:116-125):
+//   att_e   = exp(clip(-(a1 mu1_e + a2 mu2_e), +-700))
+//   nu_m    = sum_e i0_me att_e             grad_mp = -sum_e i0_me mu_pe att_e        hess_mpq = sum_e i0_me mu_pe mu_qe att_e
+//   r_m     = g_m/nu_m - 1                  dF_p    = -sum_m r_m grad_mp
+//   H_pq    = -sum_m ( r_m hess_mpq - g_m/nu_m^2 grad_mp grad_mq )                    a -= H^-1 dF
+// The twelve energy sums are twelve FMAs against a per-energy table row kept in shared memory:
+//   row_e = { -mu1_e*s, -mu2_e*s, i0_1e {1, mu1, mu2, mu1^2, mu1 mu2, mu2^2}, i0_2e {...} }   (s = log2(e) in float)
+// Every thread of a warp reads the same row (broadcast LDS.128), so the kernel is bound by the FP32 FMA pipe:
+// 14 FMA + 1 MUFU.EX2 per pixel, energy and iteration.  PX pixels per thread share each row load.
+#include "common.cuh"
+
+namespace dexct {
+
+constexpr int GN_ROW = 16;   // floats per table row (14 used), 64 B so a row is four LDS.128
+
+template <typename R> struct GnMath;
+template <> struct GnMath<float> {
+    static constexpr float scale = 1.4426950408889634f;                 // exponent kept in the log2 domain
+    static __device__ __forceinline__ float att(float x)                // x = -(a.mu) * log2(e)
+    {
+        // float: the reference's clip(-700, 700) is the identity here -- anything beyond +-128 (log2 domain) already
+        // saturates to 0 / inf in single precision, exactly as the clipped value would.
+        float y;
+        asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+        return y;
+    }
+    static __device__ __forceinline__ float fma(float a, float b, float c) { return fmaf(a, b, c); }
+};
+template <> struct GnMath<double> {
+    static constexpr double scale = 1.0;
+    static __device__ __forceinline__ double att(double x) { return exp(fmin(fmax(x, -700.0), 700.0)); }   // :116
+    static __device__ __forceinline__ double fma(double a, double b, double c) { return ::fma(a, b, c); }
+};
+
+// max over g[0][0..P) -> *out (scratch).  Non-negative counts: compare as ordered ints after a float reinterpretation
+// is avoided on purpose; a two-level block reduction plus one atomic per block on an integer view of the value.
+template <typename R>
+__global__ void gn_max_kernel(const R *__restrict__ g, long long P, R *out)
+{
+    R m = -INFINITY;
+    for (long long p = (long long)blockIdx.x * blockDim.x + threadIdx.x; p < P; p += (long long)gridDim.x * blockDim.x)
+        m = fmax(m, g[p]);
+    for (int o = 16; o > 0; o >>= 1) m = fmax(m, __shfl_xor_sync(0xffffffffu, m, o));
+    __shared__ R wm[32];
+    if ((threadIdx.x & 31) == 0) wm[threadIdx.x >> 5] = m;
+    __syncthreads();
+    if (threadIdx.x < 32) {
+        m = threadIdx.x < (blockDim.x >> 5) ? wm[threadIdx.x] : -INFINITY;
+        for (int o = 16; o > 0; o >>= 1) m = fmax(m, __shfl_xor_sync(0xffffffffu, m, o));
+        if (threadIdx.x == 0) {
+            // atomic max on a monotone integer key of the floating value (works for negatives too)
+            if (sizeof(R) == 4) {
+                int k = __float_as_int((float)m);
+                k = k >= 0 ? k : k ^ 0x7fffffff;
+                atomicMax((int *)out, k);
+            } else {
+                long long k = __double_as_longlong((double)m);
+                k = k >= 0 ? k : k ^ 0x7fffffffffffffffLL;
+                atomicMax((long long *)out, k);
+            }
+        }
+    }
+}
+
+template <typename R> __device__ __forceinline__ R decode_max(const void *scratch);
+template <> __device__ __forceinline__ float decode_max<float>(const void *s)
+{
+    int k = *(const int *)s;
+    k = k >= 0 ? k : k ^ 0x7fffffff;
+    return __int_as_float(k);
+}
+template <> __device__ __forceinline__ double decode_max<double>(const void *s)
+{
+    long long k = *(const long long *)s;
+    k = k >= 0 ? k : k ^ 0x7fffffffffffffffLL;
+    return __longlong_as_double(k);
+}
+
+template <typename R, int PX>
+__global__ void __launch_bounds__(256) gn_kernel(const R *__restrict__ g, const R *__restrict__ i0, const R *__restrict__ mus,
+                                                 int nE, long long P, int n_iters, R mask_thresh, const void *scratch,
+                                                 R *__restrict__ a_out)
+{
+    typedef GnMath<R> M;
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    R *tab = (R *)smem_raw;                                   // [nE][GN_ROW]
+    for (int e = threadIdx.x; e < nE; e += blockDim.x) {
+        const R m1 = mus[e], m2 = mus[nE + e], s1 = i0[e], s2 = i0[nE + e];
+        R *row = tab + e * GN_ROW;
+        row[0] = -m1 * M::scale; row[1] = -m2 * M::scale;
+        row[2] = s1; row[3] = s1 * m1; row[4] = s1 * m2; row[5] = s1 * (m1 * m1); row[6] = s1 * (m1 * m2); row[7] = s1 * (m2 * m2);
+        row[8] = s2; row[9] = s2 * m1; row[10] = s2 * m2; row[11] = s2 * (m1 * m1); row[12] = s2 * (m1 * m2); row[13] = s2 * (m2 * m2);
+        row[14] = (R)0; row[15] = (R)0;
+    }
+    __syncthreads();
+
+    const long long stride = (long long)gridDim.x * blockDim.x;
+    const R thr = mask_thresh > (R)0 ? mask_thresh * decode_max<R>(scratch) : (R)INFINITY;
+
+    // grid-stride over groups of PX pixels; pixel p_k = base + k*stride keeps every global access coalesced
+    for (long long base = (long long)blockIdx.x * blockDim.x + threadIdx.x; base < P; base += stride * PX) {
+        R a1[PX], a2[PX], g1[PX], g2[PX];
+#pragma unroll
+        for (int k = 0; k < PX; ++k) {
+            const long long p = base + k * stride;
+            a1[k] = a2[k] = (R)1e-6;                                         // matdecomp.py:98
+            g1[k] = p < P ? g[p] : (R)1;
+            g2[k] = p < P ? g[P + p] : (R)1;
+        }
+        for (int it = 0; it < n_iters; ++it) {
+            R acc[PX][12];
+#pragma unroll
+            for (int k = 0; k < PX; ++k)
+#pragma unroll
+                for (int q = 0; q < 12; ++q) acc[k][q] = (R)0;
+#pragma unroll 2
+            for (int e = 0; e < nE; ++e) {
+                const R *row = tab + e * GN_ROW;
+                R t[14];
+#pragma unroll
+                for (int q = 0; q < 14; ++q) t[q] = row[q];
+#pragma unroll
+                for (int k = 0; k < PX; ++k) {
+                    const R att = M::att(M::fma(a2[k], t[1], a1[k] * t[0]));
+#pragma unroll
+                    for (int q = 0; q < 12; ++q) acc[k][q] = M::fma(t[2 + q], att, acc[k][q]);
+                }
+            }
+#pragma unroll
+            for (int k = 0; k < PX; ++k) {
+                const R *A = acc[k];                                          // A[0..5] meas 1, A[6..11] meas 2
+                const R nu1 = A[0], nu2 = A[6];
+                const R r1 = g1[k] / nu1 - (R)1, r2 = g2[k] / nu2 - (R)1;      // g/nu - 1
+                const R s1 = g1[k] / (nu1 * nu1), s2 = g2[k] / (nu2 * nu2);    // g/nu^2
+                // grad_mp = -A[1+p]; the two minus signs of dF cancel, grad grad^T is sign-free
+                const R d1 = r1 * A[1] + r2 * A[7];
+                const R d2 = r1 * A[2] + r2 * A[8];
+                const R h11 = -(r1 * A[3] + r2 * A[9]) + (s1 * A[1] * A[1] + s2 * A[7] * A[7]);
+                const R h12 = -(r1 * A[4] + r2 * A[10]) + (s1 * A[1] * A[2] + s2 * A[7] * A[8]);
+                const R h22 = -(r1 * A[5] + r2 * A[11]) + (s1 * A[2] * A[2] + s2 * A[8] * A[8]);
+                // 2x2 solve; the determinant is a difference of like-sized products -> compensate the first product
+                const R w = h12 * h12;
+                const R err = M::fma(-h12, h12, w);
+                const R det = M::fma(h11, h22, -w) + err;
+                const R inv = (R)1 / det;
+                a1[k] -= (h22 * d1 - h12 * d2) * inv;
+                a2[k] -= (h11 * d2 - h12 * d1) * inv;
+            }
+        }
+#pragma unroll
+        for (int k = 0; k < PX; ++k) {
+            const long long p = base + k * stride;
+            if (p < P) {
+                const bool masked = g1[k] >= thr;                             // matdecomp.py:196,204-205
+                // a_out [P][2]: two adjacent values per pixel
+                if (sizeof(R) == 4) {
+                    float2 o = make_float2(masked ? 0.f : (float)a1[k], masked ? 0.f : (float)a2[k]);
+                    ((float2 *)a_out)[p] = o;
+                } else {
+                    double2 o = make_double2(masked ? 0.0 : (double)a1[k], masked ? 0.0 : (double)a2[k]);
+                    ((double2 *)a_out)[p] = o;
+                }
+            }
+        }
+    }
+}
+
+template <typename R, int PX>
+static int launch_gn(const void *g, const void *i0, const void *mus, int nE, long long P, int n_iters, double mask_thresh,
+                     void *a_out, void *scratch, cudaStream_t st)
+{
+    const int block = 256;
+    const size_t smem = sizeof(R) * (size_t)nE * GN_ROW;
+    if (smem > 200 * 1024) {
+        set_error("GN table needs %zu bytes of shared memory (limit 200 KiB): nE=%d", smem, nE);
+        return DEXCT_ECAPACITY;
+    }
+    auto kern = gn_kernel<R, PX>;
+    if (smem > 48 * 1024) DEXCT_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    int per_sm = 0;
+    DEXCT_CUDA_OK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, block, smem));
+    if (per_sm < 1) per_sm = 1;
+    const long long want = (P + (long long)block * PX - 1) / ((long long)block * PX);
+    long long grid = (long long)sm_count() * per_sm;          // one resident wave; the grid-stride loop does the rest
+    if (grid > want) grid = want;
+    if (mask_thresh > 0) {
+        DEXCT_CUDA_OK(cudaMemsetAsync(scratch, 0x80, 8, st));  // key of a very negative value for both key widths
+        gn_max_kernel<R><<<(unsigned)min((long long)sm_count() * 4, (P + 255) / 256), 256, 0, st>>>((const R *)g, P, (R *)scratch);
+        DEXCT_CUDA_OK(cudaGetLastError());
+    }
+    kern<<<(unsigned)grid, block, smem, st>>>((const R *)g, (const R *)i0, (const R *)mus, nE, P, n_iters, (R)mask_thresh,
+                                             scratch, (R *)a_out);
+    DEXCT_CUDA_OK(cudaGetLastError());
+    return DEXCT_OK;
+}
+
+}  // namespace dexct
+
+using namespace dexct;
+
+extern "C" int dexct_gn_decompose(const void *g, const void *i0, const void *mus, int32_t nE, int64_t P, int32_t n_iters,
+                                  double mask_thresh, void *a_out, void *scratch, int32_t dtype, void *stream)
+{
+    if (int e = check_device()) return e;
+    DEXCT_REQUIRE(g && i0 && mus && a_out, "g, i0, mus and a_out must be non-null");
+    DEXCT_REQUIRE(nE >= 1 && P >= 0 && n_iters >= 0, "need nE >= 1, P >= 0, n_iters >= 0");
+    DEXCT_REQUIRE(mask_thresh <= 0 || scratch, "scratch must be non-null when mask_thresh > 0");
+    DEXCT_REQUIRE(dtype == DEXCT_F32 || dtype == DEXCT_F64, "dtype must be DEXCT_F32 or DEXCT_F64");
+    if (P == 0) return DEXCT_OK;
+    cudaStream_t st = (cudaStream_t)stream;
+    if (dtype == DEXCT_F32) return launch_gn<float, 2>(g, i0, mus, nE, P, n_iters, mask_thresh, a_out, scratch, st);
+    return launch_gn<double, 1>(g, i0, mus, nE, P, n_iters, mask_thresh, a_out, scratch, st);
+}

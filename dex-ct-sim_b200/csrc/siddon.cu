@@ -1,0 +1,518 @@
+// Forward projection kernels: workspace preparation, Siddon traversal with fused polyenergetic detection,
+// detection from stored lengths, and the debug trace.  Replaces get_sino (/root/reference/main.py:120).
+#include "siddon_core.cuh"
+
+namespace dexct {
+
+// ---------------------------------------------------------------------------------------------------------
+// Workspace preparation
+
+__global__ void tables_kernel(DexctScan s, double *cosb, double *sinb, double *cosg, double *sing, double *zdet)
+{
+    const int t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t < s.n_views) {
+        const double b = __dadd_rn(s.beta0, __dmul_rn((double)t, s.dbeta));
+        double sn, cs;
+        sincos(b, &sn, &cs);
+        cosb[t] = cs; sinb[t] = sn;
+    }
+    if (t < s.n_ch) {
+        const double g = __dadd_rn(s.gamma0, __dmul_rn((double)t, s.dgamma));
+        double sn, cs;
+        sincos(g, &sn, &cs);
+        cosg[t] = cs; sing[t] = sn;
+    }
+    if (t < s.n_rows) zdet[t] = __dadd_rn(s.z0, __dmul_rn((double)t, s.dzdet));
+}
+
+// y-major layout: columns are rows of the image, minor axis x is already contiguous in the input.
+// ym[(k+1)][j][ii], ii = i + 1 in [0, nx+1]: low byte = label(i, j, k), high byte = label(i+1, j, k); 0 outside.
+__global__ void repack_ym_kernel(const uint8_t *__restrict__ labels, int nx, int ny, int nz,
+                                 uint16_t *__restrict__ ym, int pitch, long long plane)
+{
+    const long long row = blockIdx.x;                      // k*ny + j
+    const int k = (int)(row / ny), j = (int)(row % ny);
+    const uint8_t *src = labels + row * nx;
+    uint16_t *dst = ym + (long long)(k + 1) * plane + (long long)j * pitch;
+    for (int ii = threadIdx.x; ii < nx + 2; ii += blockDim.x) {
+        const int i = ii - 1;
+        const unsigned lo = (i >= 0 && i < nx) ? src[i] : 0u;
+        const unsigned hi = (i + 1 < nx) ? src[i + 1] : 0u;
+        dst[ii] = (uint16_t)(lo | (hi << 8));
+    }
+}
+
+// x-major layout: columns are image columns, minor axis y must become contiguous -> tiled transpose.
+// xm[(k+1)][i][jj], jj = j + 1: low byte = label(i, j, k), high byte = label(i, j+1, k).
+__global__ void repack_xm_kernel(const uint8_t *__restrict__ labels, int nx, int ny, int nz,
+                                 uint16_t *__restrict__ xm, int pitch, long long plane)
+{
+    __shared__ uint8_t tile[33][36];                       // [j_local (0..32)][i_local], one extra j row
+    const int k = blockIdx.z;
+    const int i0 = blockIdx.x * 32, j0 = blockIdx.y * 32 - 1;      // tile covers j in [j0, j0+33)
+    const uint8_t *src = labels + (long long)k * ny * nx;
+    for (int t = threadIdx.y; t < 33; t += blockDim.y) {
+        const int j = j0 + t, i = i0 + threadIdx.x;
+        tile[t][threadIdx.x] = (j >= 0 && j < ny && i < nx) ? src[(long long)j * nx + i] : (uint8_t)0;
+    }
+    __syncthreads();
+    uint16_t *dst = xm + (long long)(k + 1) * plane;
+    for (int t = threadIdx.y; t < 32; t += blockDim.y) {
+        const int i = i0 + t;
+        const int jj = blockIdx.y * 32 + threadIdx.x;      // = j + 1 with j = j0 + threadIdx.x
+        if (i < nx && jj < ny + 2) {
+            const unsigned lo = tile[threadIdx.x][t], hi = tile[threadIdx.x + 1][t];
+            dst[(long long)i * pitch + jj] = (uint16_t)(lo | (hi << 8));
+        }
+    }
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// Polyenergetic detection epilogue (forward model of matdecomp.py:116-118 with K materials):
+// counts_s = sum_e W[s][e] exp(-sum_m L_m mu[m][e]).
+
+// Tables are staged as mu * EXP_SCALE so that the float path needs no multiply ahead of MUFU.EX2:
+// att = 2^(-t) with t = sum_m L_m (mu_m log2 e).  The double path keeps natural units and calls exp().
+template <typename R> struct DetMath;
+template <> struct DetMath<float> {
+    static constexpr float scale = 1.4426950408889634f;
+    static __device__ __forceinline__ float att(float t)
+    {
+        float y;
+        asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(-t));
+        return y;
+    }
+    static __device__ __forceinline__ float fma(float a, float b, float c) { return fmaf(a, b, c); }
+};
+template <> struct DetMath<double> {
+    static constexpr double scale = 1.0;
+    static __device__ __forceinline__ double att(double t) { return exp(-t); }
+    static __device__ __forceinline__ double fma(double a, double b, double c) { return ::fma(a, b, c); }
+};
+
+constexpr int MAX_SPEC = 4;
+
+// Lm: per-thread lengths, element m at Lm[m * stride].  mu/W: tables (shared memory).
+template <typename R>
+__device__ __forceinline__ void detect(const R *Lm, int stride, int K, const R *mu, const R *W, int nE, int nSpec,
+                                       R *out /*[nSpec]*/)
+{
+    R acc[MAX_SPEC];
+#pragma unroll
+    for (int s = 0; s < MAX_SPEC; ++s) acc[s] = (R)0;
+    for (int e = 0; e < nE; ++e) {
+        R t = (R)0;
+        for (int m = 0; m < K; ++m) t = DetMath<R>::fma(Lm[m * stride], mu[m * nE + e], t);
+        const R att = DetMath<R>::att(t);
+#pragma unroll
+        for (int s = 0; s < MAX_SPEC; ++s)
+            if (s < nSpec) acc[s] = DetMath<R>::fma(W[s * nE + e], att, acc[s]);
+    }
+#pragma unroll
+    for (int s = 0; s < MAX_SPEC; ++s) out[s] = acc[s];
+}
+
+// Same with the lengths in registers (K <= KT), the common case: one broadcast LDS + one FMA per (m, e).
+template <typename R, int KT>
+__device__ __forceinline__ void detect_reg(const R (&Lr)[KT], const R *mu, const R *W, int nE, int nSpec, R *out)
+{
+    R acc[MAX_SPEC];
+#pragma unroll
+    for (int s = 0; s < MAX_SPEC; ++s) acc[s] = (R)0;
+    for (int e = 0; e < nE; ++e) {
+        R t = (R)0;
+#pragma unroll
+        for (int m = 0; m < KT; ++m) t = DetMath<R>::fma(Lr[m], mu[m * nE + e], t);
+        const R att = DetMath<R>::att(t);
+#pragma unroll
+        for (int s = 0; s < MAX_SPEC; ++s)
+            if (s < nSpec) acc[s] = DetMath<R>::fma(W[s * nE + e], att, acc[s]);
+    }
+#pragma unroll
+    for (int s = 0; s < MAX_SPEC; ++s) out[s] = acc[s];
+}
+
+struct DetectArgs {
+    const void *mu, *W;       // [K][nE], [nSpec][nE]
+    int K, nE, nSpec;
+    void *counts, *logs, *L_out;
+};
+
+// Stage mu (zero-padded to KP rows), W and the unattenuated ("air") signal of each spectrum in shared memory.
+template <typename R>
+__device__ __forceinline__ void stage_tables(const DetectArgs &d, int KP, R *mu_s, R *W_s, R *air_s)
+{
+    const R *mu = (const R *)d.mu, *W = (const R *)d.W;
+    for (int t = threadIdx.x; t < KP * d.nE; t += blockDim.x) mu_s[t] = t < d.K * d.nE ? mu[t] * DetMath<R>::scale : (R)0;
+    for (int t = threadIdx.x; t < d.nSpec * d.nE; t += blockDim.x) W_s[t] = W[t];
+    __syncthreads();
+    if (threadIdx.x < d.nSpec) {
+        R a = (R)0;
+        for (int e = 0; e < d.nE; ++e) a += W_s[threadIdx.x * d.nE + e];
+        air_s[threadIdx.x] = a;
+    }
+    __syncthreads();
+}
+
+template <typename R> __device__ __forceinline__ R neg_log_ratio(R c, R air);
+template <> __device__ __forceinline__ float neg_log_ratio<float>(float c, float air) { return -logf(c / air); }
+template <> __device__ __forceinline__ double neg_log_ratio<double>(double c, double air) { return -log(c / air); }
+
+// ---------------------------------------------------------------------------------------------------------
+// Production kernel: one ray per thread, adjacent lanes = adjacent channels (so a warp reads adjacent minor-axis
+// voxels of the same column: one or two 128-byte lines per request in the pair layout).
+
+template <typename R> struct AccSink {
+    R *acc;            // acc[label * BLOCK + tid] lives in shared memory; this points at [tid]
+    int stride;
+    __device__ __forceinline__ void operator()(int, int, int, int label, R w) const
+    {
+        R *p = acc + label * stride;
+        *p = Rn<R>::add(*p, w);
+    }
+};
+
+template <typename R, bool IS3D, int KT>
+__global__ void __launch_bounds__(128) siddon_poly_kernel(SiddonParams P, int view_begin, long long n_rays, DetectArgs d)
+{
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    const int KP = KT > 0 ? KT : d.K;
+    R *acc_s = (R *)smem_raw;                              // [KP][blockDim]
+    R *mu_s = acc_s + (size_t)KP * blockDim.x;             // [KP][nE]
+    R *W_s = mu_s + (size_t)KP * d.nE;                     // [nSpec][nE]
+    R *air_s = W_s + (size_t)d.nSpec * d.nE;               // [nSpec]
+    stage_tables<R>(d, KP, mu_s, W_s, air_s);
+
+    const int tid = threadIdx.x;
+    for (int m = 0; m < KP; ++m) acc_s[m * blockDim.x + tid] = (R)0;
+
+    const long long ray = (long long)blockIdx.x * blockDim.x + tid;
+    if (ray >= n_rays) return;
+    const int c = (int)(ray % P.scan.n_ch);
+    const long long line = ray / P.scan.n_ch;
+    const int r = (int)(line % P.scan.n_rows);
+    const int v = view_begin + (int)(line / P.scan.n_rows);
+
+    RaySetup s;
+    ray_setup(P, v, r, c, s);
+    R seglen = (R)0;
+    if (s.hit) {
+        RayLoop<R> L;
+        L.init(P, s);
+        AccSink<R> sink{acc_s + tid, (int)blockDim.x};
+        for (int i = s.i0; i <= s.i1; ++i) slab_column<R, IS3D>(L, i, sink);
+        seglen = (R)s.seglen;
+    }
+
+    R out[MAX_SPEC];
+    if (KT > 0) {
+        R Lr[KT > 0 ? KT : 1];
+#pragma unroll
+        for (int m = 0; m < (KT > 0 ? KT : 1); ++m) Lr[m] = acc_s[m * blockDim.x + tid] * seglen;
+        if (d.L_out) {
+            R *Lo = (R *)d.L_out + ray * d.K;
+#pragma unroll
+            for (int m = 0; m < (KT > 0 ? KT : 1); ++m)
+                if (m < d.K) Lo[m] = Lr[m];
+        }
+        detect_reg<R, (KT > 0 ? KT : 1)>(Lr, mu_s, W_s, d.nE, d.nSpec, out);
+    } else {
+        for (int m = 0; m < d.K; ++m) acc_s[m * blockDim.x + tid] *= seglen;
+        if (d.L_out) {
+            R *Lo = (R *)d.L_out + ray * d.K;
+            for (int m = 0; m < d.K; ++m) Lo[m] = acc_s[m * blockDim.x + tid];
+        }
+        detect<R>(acc_s + tid, blockDim.x, d.K, mu_s, W_s, d.nE, d.nSpec, out);
+    }
+#pragma unroll
+    for (int sp = 0; sp < MAX_SPEC; ++sp) {
+        if (sp < d.nSpec) {
+            ((R *)d.counts)[sp * n_rays + ray] = out[sp];
+            if (d.logs) ((R *)d.logs)[sp * n_rays + ray] = neg_log_ratio<R>(out[sp], air_s[sp]);
+        }
+    }
+}
+
+// Detection from stored lengths L [n_rays][K].
+template <typename R>
+__global__ void __launch_bounds__(128) poly_detect_kernel(const R *__restrict__ Lin, long long n_rays, DetectArgs d)
+{
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    R *acc_s = (R *)smem_raw;                              // [K][blockDim]
+    R *mu_s = acc_s + (size_t)d.K * blockDim.x;
+    R *W_s = mu_s + (size_t)d.K * d.nE;
+    R *air_s = W_s + (size_t)d.nSpec * d.nE;
+    stage_tables<R>(d, d.K, mu_s, W_s, air_s);
+    const int tid = threadIdx.x;
+    const long long ray0 = (long long)blockIdx.x * blockDim.x;
+    // coalesced load of this block's [blockDim][K] slab, transposed into acc_s[m][tid]
+    const long long base = ray0 * d.K;
+    const long long lim = n_rays * d.K;
+    for (int t = tid; t < (int)blockDim.x * d.K; t += blockDim.x) {
+        const long long gidx = base + t;
+        const int rr = t / d.K, m = t % d.K;
+        acc_s[m * blockDim.x + rr] = gidx < lim ? Lin[gidx] : (R)0;
+    }
+    __syncthreads();
+    const long long ray = ray0 + tid;
+    if (ray >= n_rays) return;
+    R out[MAX_SPEC];
+    detect<R>(acc_s + tid, blockDim.x, d.K, mu_s, W_s, d.nE, d.nSpec, out);
+#pragma unroll
+    for (int sp = 0; sp < MAX_SPEC; ++sp) {
+        if (sp < d.nSpec) {
+            ((R *)d.counts)[sp * n_rays + ray] = out[sp];
+            if (d.logs) ((R *)d.logs)[sp * n_rays + ray] = neg_log_ratio<R>(out[sp], air_s[sp]);
+        }
+    }
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// Debug trace: same set-up, same column routine, pieces written out in ray order.
+
+template <typename R> struct TraceSink {
+    int64_t vox[3];
+    int lab[3];
+    R w[3];
+    int n;
+    bool xmajor;
+    int i, nx, ny, nq, nz;
+    __device__ __forceinline__ void operator()(int slot, int j, int k, int label, R wt)
+    {
+        const bool inside = j >= 0 && j < nq && k >= 0 && k < nz;
+        vox[slot] = inside ? (xmajor ? ((int64_t)k * ny + j) * nx + i : ((int64_t)k * ny + i) * nx + j) : -1;
+        lab[slot] = label;
+        w[slot] = wt;
+        n = slot + 1;
+    }
+};
+
+template <typename R, bool IS3D>
+__global__ void siddon_trace_kernel(SiddonParams P, const int64_t *__restrict__ ray_ids, int n_rays, int max_seg,
+                                    int64_t *__restrict__ vox, uint8_t *__restrict__ lab, R *__restrict__ len,
+                                    int32_t *__restrict__ n_seg)
+{
+    const int t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= n_rays) return;
+    const int64_t ray = ray_ids[t];
+    const int c = (int)(ray % P.scan.n_ch);
+    const int64_t line = ray / P.scan.n_ch;
+    const int r = (int)(line % P.scan.n_rows);
+    const int v = (int)(line / P.scan.n_rows);
+    RaySetup s;
+    ray_setup(P, v, r, c, s);
+    int n = 0;
+    if (s.hit) {
+        RayLoop<R> L;
+        L.init(P, s);
+        const R seglen = (R)s.seglen;
+        TraceSink<R> sink;
+        sink.xmajor = s.xmajor; sink.nx = P.vol.nx; sink.ny = P.vol.ny; sink.nq = s.nq; sink.nz = P.vol.nz;
+        const int step = s.fwd ? 1 : -1;
+        for (int i = s.fwd ? s.i0 : s.i1; s.fwd ? (i <= s.i1) : (i >= s.i0); i += step) {
+            sink.n = 0; sink.i = i;
+            slab_column<R, IS3D>(L, i, sink);
+            for (int q = 0; q < sink.n; ++q) {
+                const int slot = s.fwd ? q : sink.n - 1 - q;
+                if (!(sink.w[slot] > (R)0) || sink.vox[slot] < 0) continue;
+                if (n < max_seg) {
+                    const size_t o = (size_t)t * max_seg + n;
+                    vox[o] = sink.vox[slot];
+                    lab[o] = (uint8_t)sink.lab[slot];
+                    len[o] = Rn<R>::mul(sink.w[slot], seglen);
+                }
+                ++n;
+            }
+        }
+    }
+    n_seg[t] = n;
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// Host side
+
+static int make_params(const DexctScan *scan, const DexctVolume *vol, const void *workspace, SiddonParams &P)
+{
+    DEXCT_REQUIRE(scan && vol && workspace, "scan, vol and workspace must be non-null");
+    DEXCT_REQUIRE(scan->n_views > 0 && scan->n_rows > 0 && scan->n_ch > 0, "scan sizes must be positive");
+    DEXCT_REQUIRE(vol->nx > 0 && vol->ny > 0 && vol->nz > 0, "volume sizes must be positive");
+    DEXCT_REQUIRE(vol->dx > 0 && vol->dy > 0 && vol->dz > 0, "voxel sizes must be positive");
+    DEXCT_REQUIRE(scan->sid > 0 && scan->sdd > 0, "SID and SDD must be positive");
+    const WsLayout L = ws_layout(*scan, *vol);
+    const char *w = (const char *)workspace;
+    P.scan = *scan; P.vol = *vol;
+    P.cosb = (const double *)(w + L.off_cosb); P.sinb = (const double *)(w + L.off_sinb);
+    P.cosg = (const double *)(w + L.off_cosg); P.sing = (const double *)(w + L.off_sing);
+    P.zdet = (const double *)(w + L.off_zdet);
+    P.xm = (const uint16_t *)(w + L.off_xm); P.ym = (const uint16_t *)(w + L.off_ym);
+    P.pitch_xm = L.pitch_xm; P.pitch_ym = L.pitch_ym; P.plane_xm = L.plane_xm; P.plane_ym = L.plane_ym;
+    return DEXCT_OK;
+}
+
+static bool scan_is_3d(const DexctScan &s, const DexctVolume &v)
+{
+    return v.nz > 1 || s.n_rows > 1 || s.z0 != 0.0;
+}
+
+template <typename R, bool IS3D, int KT>
+static int launch_poly(const SiddonParams &P, int view_begin, long long n_rays, const DetectArgs &d, cudaStream_t st)
+{
+    const int block = 128;
+    const int KP = KT > 0 ? KT : d.K;
+    const size_t smem = sizeof(R) * ((size_t)KP * block + (size_t)KP * d.nE + (size_t)d.nSpec * d.nE + MAX_SPEC);
+    if (smem > 200 * 1024) {
+        set_error("material/energy tables need %zu bytes of shared memory (limit 200 KiB): K=%d nE=%d", smem, d.K, d.nE);
+        return DEXCT_ECAPACITY;
+    }
+    auto kern = siddon_poly_kernel<R, IS3D, KT>;
+    if (smem > 48 * 1024) DEXCT_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    const long long grid = (n_rays + block - 1) / block;
+    kern<<<(unsigned)grid, block, smem, st>>>(P, view_begin, n_rays, d);
+    DEXCT_CUDA_OK(cudaGetLastError());
+    return DEXCT_OK;
+}
+
+template <typename R, bool IS3D>
+static int dispatch_k(const SiddonParams &P, int view_begin, long long n_rays, const DetectArgs &d, cudaStream_t st)
+{
+    if (d.K <= 4) return launch_poly<R, IS3D, 4>(P, view_begin, n_rays, d, st);
+    if (d.K <= 8) return launch_poly<R, IS3D, 8>(P, view_begin, n_rays, d, st);
+    if (d.K <= 16) return launch_poly<R, IS3D, 16>(P, view_begin, n_rays, d, st);
+    return launch_poly<R, IS3D, 0>(P, view_begin, n_rays, d, st);
+}
+
+}  // namespace dexct
+
+using namespace dexct;
+
+extern "C" size_t dexct_siddon_workspace_bytes(const DexctScan *scan, const DexctVolume *vol)
+{
+    if (!scan || !vol || scan->n_views <= 0 || scan->n_ch <= 0 || scan->n_rows <= 0 || vol->nx <= 0 || vol->ny <= 0 ||
+        vol->nz <= 0)
+        return 0;
+    return ws_layout(*scan, *vol).total;
+}
+
+extern "C" int dexct_siddon_prepare(const DexctScan *scan, const DexctVolume *vol, const uint8_t *labels,
+                                    void *workspace, void *stream)
+{
+    if (int e = check_device()) return e;
+    SiddonParams P;
+    if (int e = make_params(scan, vol, workspace, P)) return e;
+    DEXCT_REQUIRE(labels, "labels must be non-null");
+    cudaStream_t st = (cudaStream_t)stream;
+    const WsLayout L = ws_layout(*scan, *vol);
+    char *w = (char *)workspace;
+    const int nmax = max(scan->n_views, max(scan->n_ch, scan->n_rows));
+    tables_kernel<<<(nmax + 127) / 128, 128, 0, st>>>(*scan, (double *)(w + L.off_cosb), (double *)(w + L.off_sinb),
+                                                      (double *)(w + L.off_cosg), (double *)(w + L.off_sing),
+                                                      (double *)(w + L.off_zdet));
+    DEXCT_CUDA_OK(cudaGetLastError());
+    // apron planes (k = -1, nz) and pitch padding must read as label 0
+    DEXCT_CUDA_OK(cudaMemsetAsync(w + L.off_xm, 0, L.total - L.off_xm, st));
+    repack_ym_kernel<<<(unsigned)((long long)vol->nz * vol->ny), 128, 0, st>>>(labels, vol->nx, vol->ny, vol->nz,
+                                                                               (uint16_t *)(w + L.off_ym), L.pitch_ym, L.plane_ym);
+    DEXCT_CUDA_OK(cudaGetLastError());
+    dim3 grid((vol->nx + 31) / 32, (vol->ny + 2 + 31) / 32, vol->nz);
+    repack_xm_kernel<<<grid, dim3(32, 8), 0, st>>>(labels, vol->nx, vol->ny, vol->nz, (uint16_t *)(w + L.off_xm),
+                                                  L.pitch_xm, L.plane_xm);
+    DEXCT_CUDA_OK(cudaGetLastError());
+    return DEXCT_OK;
+}
+
+extern "C" int dexct_siddon_tables_host(const DexctScan *scan, const void *workspace, double *cb, double *sb, double *cg,
+                                        double *sg, double *zd, void *stream)
+{
+    if (int e = check_device()) return e;
+    DEXCT_REQUIRE(scan && workspace, "scan and workspace must be non-null");
+    DexctVolume dummy = {1, 1, 1, 0, 1.0, 1.0, 1.0};
+    const WsLayout L = ws_layout(*scan, dummy);          // table offsets do not depend on the volume
+    const char *w = (const char *)workspace;
+    cudaStream_t st = (cudaStream_t)stream;
+    DEXCT_CUDA_OK(cudaStreamSynchronize(st));
+    if (cb) DEXCT_CUDA_OK(cudaMemcpy(cb, w + L.off_cosb, sizeof(double) * scan->n_views, cudaMemcpyDeviceToHost));
+    if (sb) DEXCT_CUDA_OK(cudaMemcpy(sb, w + L.off_sinb, sizeof(double) * scan->n_views, cudaMemcpyDeviceToHost));
+    if (cg) DEXCT_CUDA_OK(cudaMemcpy(cg, w + L.off_cosg, sizeof(double) * scan->n_ch, cudaMemcpyDeviceToHost));
+    if (sg) DEXCT_CUDA_OK(cudaMemcpy(sg, w + L.off_sing, sizeof(double) * scan->n_ch, cudaMemcpyDeviceToHost));
+    if (zd) DEXCT_CUDA_OK(cudaMemcpy(zd, w + L.off_zdet, sizeof(double) * scan->n_rows, cudaMemcpyDeviceToHost));
+    return DEXCT_OK;
+}
+
+extern "C" int dexct_siddon_poly(const DexctScan *scan, const DexctVolume *vol, const void *workspace,
+                                 int32_t view_begin, int32_t view_count, const void *mu, int32_t K, int32_t nE,
+                                 const void *W, int32_t nSpec, void *counts, void *logs, void *L_out, int32_t dtype,
+                                 void *stream)
+{
+    if (int e = check_device()) return e;
+    SiddonParams P;
+    if (int e = make_params(scan, vol, workspace, P)) return e;
+    DEXCT_REQUIRE(view_begin >= 0 && view_count >= 0 && view_begin + view_count <= scan->n_views,
+                  "view range [%d, %d) outside the scan's %d views", view_begin, view_begin + view_count, scan->n_views);
+    DEXCT_REQUIRE(mu && W && counts, "mu, W and counts must be non-null");
+    DEXCT_REQUIRE(K >= 1 && K <= 256 && nE >= 1, "need 1 <= K <= 256 and nE >= 1 (K=%d nE=%d)", K, nE);
+    DEXCT_REQUIRE(nSpec >= 1 && nSpec <= MAX_SPEC, "nSpec must be in 1..%d", MAX_SPEC);
+    DEXCT_REQUIRE(dtype == DEXCT_F32 || dtype == DEXCT_F64, "dtype must be DEXCT_F32 or DEXCT_F64");
+    if (view_count == 0) return DEXCT_OK;
+    const long long n_rays = (long long)view_count * scan->n_rows * scan->n_ch;
+    DetectArgs d{mu, W, K, nE, nSpec, counts, logs, L_out};
+    cudaStream_t st = (cudaStream_t)stream;
+    const bool is3d = scan_is_3d(*scan, *vol);
+    if (dtype == DEXCT_F32)
+        return is3d ? dispatch_k<float, true>(P, view_begin, n_rays, d, st) : dispatch_k<float, false>(P, view_begin, n_rays, d, st);
+    return is3d ? dispatch_k<double, true>(P, view_begin, n_rays, d, st) : dispatch_k<double, false>(P, view_begin, n_rays, d, st);
+}
+
+extern "C" int dexct_poly_detect(const void *L, int64_t n_rays, const void *mu, int32_t K, int32_t nE, const void *W,
+                                 int32_t nSpec, void *counts, void *logs, int32_t dtype, void *stream)
+{
+    if (int e = check_device()) return e;
+    DEXCT_REQUIRE(L && mu && W && counts, "L, mu, W and counts must be non-null");
+    DEXCT_REQUIRE(K >= 1 && K <= 256 && nE >= 1, "need 1 <= K <= 256 and nE >= 1 (K=%d nE=%d)", K, nE);
+    DEXCT_REQUIRE(nSpec >= 1 && nSpec <= MAX_SPEC, "nSpec must be in 1..%d", MAX_SPEC);
+    DEXCT_REQUIRE(dtype == DEXCT_F32 || dtype == DEXCT_F64, "dtype must be DEXCT_F32 or DEXCT_F64");
+    if (n_rays <= 0) return DEXCT_OK;
+    DetectArgs d{mu, W, K, nE, nSpec, counts, logs, nullptr};
+    cudaStream_t st = (cudaStream_t)stream;
+    const int block = 128;
+    const size_t esz = dtype == DEXCT_F32 ? 4 : 8;
+    const size_t smem = esz * ((size_t)K * block + (size_t)K * nE + (size_t)nSpec * nE + MAX_SPEC);
+    if (smem > 200 * 1024) {
+        set_error("material/energy tables need %zu bytes of shared memory (limit 200 KiB): K=%d nE=%d", smem, K, nE);
+        return DEXCT_ECAPACITY;
+    }
+    const long long grid = (n_rays + block - 1) / block;
+    if (dtype == DEXCT_F32) {
+        if (smem > 48 * 1024) DEXCT_CUDA_OK(cudaFuncSetAttribute(poly_detect_kernel<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        poly_detect_kernel<float><<<(unsigned)grid, block, smem, st>>>((const float *)L, n_rays, d);
+    } else {
+        if (smem > 48 * 1024) DEXCT_CUDA_OK(cudaFuncSetAttribute(poly_detect_kernel<double>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        poly_detect_kernel<double><<<(unsigned)grid, block, smem, st>>>((const double *)L, n_rays, d);
+    }
+    DEXCT_CUDA_OK(cudaGetLastError());
+    return DEXCT_OK;
+}
+
+extern "C" int dexct_siddon_trace(const DexctScan *scan, const DexctVolume *vol, const void *workspace,
+                                  const int64_t *ray_ids, int32_t n_rays, int32_t max_seg, int64_t *vox, uint8_t *lab,
+                                  void *len, int32_t *n_seg, int32_t dtype, void *stream)
+{
+    if (int e = check_device()) return e;
+    SiddonParams P;
+    if (int e = make_params(scan, vol, workspace, P)) return e;
+    DEXCT_REQUIRE(ray_ids && vox && lab && len && n_seg, "trace buffers must be non-null");
+    DEXCT_REQUIRE(n_rays >= 0 && max_seg > 0, "n_rays >= 0 and max_seg > 0 required");
+    DEXCT_REQUIRE(dtype == DEXCT_F32 || dtype == DEXCT_F64, "dtype must be DEXCT_F32 or DEXCT_F64");
+    if (n_rays == 0) return DEXCT_OK;
+    cudaStream_t st = (cudaStream_t)stream;
+    const bool is3d = scan_is_3d(*scan, *vol);
+    const int block = 64, grid = (n_rays + block - 1) / block;
+    if (dtype == DEXCT_F32) {
+        if (is3d) siddon_trace_kernel<float, true><<<grid, block, 0, st>>>(P, ray_ids, n_rays, max_seg, vox, lab, (float *)len, n_seg);
+        else siddon_trace_kernel<float, false><<<grid, block, 0, st>>>(P, ray_ids, n_rays, max_seg, vox, lab, (float *)len, n_seg);
+    } else {
+        if (is3d) siddon_trace_kernel<double, true><<<grid, block, 0, st>>>(P, ray_ids, n_rays, max_seg, vox, lab, (double *)len, n_seg);
+        else siddon_trace_kernel<double, false><<<grid, block, 0, st>>>(P, ray_ids, n_rays, max_seg, vox, lab, (double *)len, n_seg);
+    }
+    DEXCT_CUDA_OK(cudaGetLastError());
+    return DEXCT_OK;
+}

@@ -1,0 +1,197 @@
+// Ray set-up and the "slab" form of Siddon's traversal, shared by the production and the trace kernel.
+//
+// Replaces the tracer inside get_sino (/root/reference/main.py:120; source absent from the reference tree, the
+// algorithm is Siddon 1985 as cited at /root/reference/README.md:28,41).  DESIGN.md section 4 derives the form
+// used here; oracle/siddon_oracle.c section (B) is its operation-for-operation CPU twin and section (A) there
+// (the paper's alpha-merge) is the independent truth both are tested against.
+//
+// Idea: pick the in-plane axis along which the ray advances fastest (the MAJOR axis, coordinate p, "columns").
+// Inside one column the ray crosses at most one plane of the other in-plane axis (MINOR, coordinate q) and at
+// most one z plane, because |dq/dp| <= 1 and CT cone angles keep |dz/dp| <= 1.  So a column contributes to at
+// most two (2-D) or three (3-D) voxels, found with one floor() per axis -- no alpha lists, no sorting, and every
+// column is independent of the previous one (no serial dependency, unlike the incremental alpha update).
+// The lengths are exactly Siddon's: column share w in [0,1] times the ray length per column.
+#pragma once
+#include "common.cuh"
+
+namespace dexct {
+
+struct WsLayout {
+    size_t off_cosb, off_sinb, off_cosg, off_sing, off_zdet;   // double tables
+    size_t off_xm, off_ym;                                     // uint16 pair layouts (bytes from workspace start)
+    size_t total;
+    int pitch_xm, pitch_ym;                                    // entries per column (nq + 2, rounded up)
+    long long plane_xm, plane_ym;                              // entries per z plane
+};
+
+__host__ __device__ inline size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
+
+inline WsLayout ws_layout(const DexctScan &s, const DexctVolume &v)
+{
+    WsLayout L;
+    size_t o = 0;
+    L.off_cosb = o; o = align_up(o + sizeof(double) * (size_t)s.n_views, 256);
+    L.off_sinb = o; o = align_up(o + sizeof(double) * (size_t)s.n_views, 256);
+    L.off_cosg = o; o = align_up(o + sizeof(double) * (size_t)s.n_ch, 256);
+    L.off_sing = o; o = align_up(o + sizeof(double) * (size_t)s.n_ch, 256);
+    L.off_zdet = o; o = align_up(o + sizeof(double) * (size_t)s.n_rows, 256);
+    L.pitch_xm = (int)align_up((size_t)v.ny + 2, 8);
+    L.pitch_ym = (int)align_up((size_t)v.nx + 2, 8);
+    L.plane_xm = (long long)v.nx * L.pitch_xm;
+    L.plane_ym = (long long)v.ny * L.pitch_ym;
+    L.off_xm = o; o = align_up(o + sizeof(uint16_t) * (size_t)L.plane_xm * (size_t)(v.nz + 2), 256);
+    L.off_ym = o; o = align_up(o + sizeof(uint16_t) * (size_t)L.plane_ym * (size_t)(v.nz + 2), 256);
+    L.total = o;
+    return L;
+}
+
+// Everything the kernels need about scan + volume + workspace, passed by value.
+struct SiddonParams {
+    DexctScan scan;
+    DexctVolume vol;
+    const double *cosb, *sinb, *cosg, *sing, *zdet;
+    const uint16_t *xm, *ym;          // pair layouts; element (k, i, j) at ((k+1)*plane + i*pitch + (j+1))
+    int pitch_xm, pitch_ym;
+    long long plane_xm, plane_ym;
+};
+
+// Per-ray constants, computed in double with one rounding per operation (the CPU twin does the same).
+struct RaySetup {
+    bool hit, xmajor, fwd;
+    int np, nq, i0, i1, jshift, kshift;
+    double m, mz, cq, cw, ua, ub, halfp, inv_am, inv_amz, seglen;
+};
+
+#define DEXCT_BIG 1e30
+
+__device__ __forceinline__ void ray_setup(const SiddonParams &P, int v, int r, int c, RaySetup &s)
+{
+    typedef Rn<double> D;
+    const double cb = P.cosb[v], sb = P.sinb[v], cg = P.cosg[c], sg = P.sing[c];
+    const double ex = D::sub(D::mul(cb, cg), D::mul(sb, sg));
+    const double ey = D::add(D::mul(sb, cg), D::mul(cb, sg));
+    const double Sx = D::mul(P.scan.sid, cb), Sy = D::mul(P.scan.sid, sb), Sz = 0.0;
+    const double Dx = -D::mul(P.scan.sdd, ex), Dy = -D::mul(P.scan.sdd, ey), Dz = P.zdet[r];
+    const double gx = D::div(Dx, P.vol.dx), gy = D::div(Dy, P.vol.dy), gz = D::div(Dz, P.vol.dz);
+    double gp, gq, pS, qS;
+    s.hit = false;
+    s.xmajor = fabs(gx) >= fabs(gy);
+    if (s.xmajor) { gp = gx; gq = gy; pS = D::div(Sx, P.vol.dx); qS = D::div(Sy, P.vol.dy); s.np = P.vol.nx; s.nq = P.vol.ny; }
+    else          { gp = gy; gq = gx; pS = D::div(Sy, P.vol.dy); qS = D::div(Sx, P.vol.dx); s.np = P.vol.ny; s.nq = P.vol.nx; }
+    const double wS = D::div(Sz, P.vol.dz);
+    s.m = D::div(gq, gp);
+    s.mz = D::div(gz, gp);
+    const double q0 = D::sub(qS, D::mul(s.m, pS));
+    const double w0 = D::sub(wS, D::mul(s.mz, pS));
+    const double hp = D::mul(0.5, (double)s.np), hq = D::mul(0.5, (double)s.nq), hw = D::mul(0.5, (double)P.vol.nz);
+    s.halfp = hp;
+    const double pe = D::add(pS, gp);
+    double pa = pS < pe ? pS : pe, pb = pS < pe ? pe : pS;
+    if (pa < -hp) pa = -hp;
+    if (pb > hp) pb = hp;
+    if (s.m != 0.0) {
+        const double t1 = D::div(D::sub(-hq, q0), s.m), t2 = D::div(D::sub(hq, q0), s.m);
+        const double lo = t1 < t2 ? t1 : t2, hi = t1 < t2 ? t2 : t1;
+        if (lo > pa) pa = lo;
+        if (hi < pb) pb = hi;
+    } else if (!(q0 >= -hq && q0 < hq)) return;
+    if (s.mz != 0.0) {
+        const double t1 = D::div(D::sub(-hw, w0), s.mz), t2 = D::div(D::sub(hw, w0), s.mz);
+        const double lo = t1 < t2 ? t1 : t2, hi = t1 < t2 ? t2 : t1;
+        if (lo > pa) pa = lo;
+        if (hi < pb) pb = hi;
+    } else if (!(w0 >= -hw && w0 < hw)) return;
+    if (!(pa < pb)) return;
+    s.ua = D::add(pa, hp);
+    s.ub = D::add(pb, hp);
+    int i0 = (int)floor(s.ua), i1 = (int)ceil(s.ub) - 1;
+    if (i0 < 0) i0 = 0;
+    if (i1 > s.np - 1) i1 = s.np - 1;
+    if (i1 < i0) return;
+    s.i0 = i0; s.i1 = i1;
+    s.fwd = gp > 0.0;
+    s.jshift = s.nq / 2;
+    s.kshift = P.vol.nz / 2;
+    s.cq = D::add(q0, D::sub(hq, (double)s.jshift));
+    s.cw = D::add(w0, D::sub(hw, (double)s.kshift));
+    const double am = fabs(s.m), amz = fabs(s.mz);
+    s.inv_am = am > 0.0 ? D::div(1.0, am) : DEXCT_BIG;
+    if (s.inv_am > DEXCT_BIG) s.inv_am = DEXCT_BIG;
+    s.inv_amz = amz > 0.0 ? D::div(1.0, amz) : DEXCT_BIG;
+    if (s.inv_amz > DEXCT_BIG) s.inv_amz = DEXCT_BIG;
+    const double len2 = D::add(D::add(D::mul(Dx, Dx), D::mul(Dy, Dy)), D::mul(Dz, Dz));
+    s.seglen = D::div(__dsqrt_rn(len2), fabs(gp));
+    s.hit = true;
+}
+
+// Loop constants in the compute precision.
+template <typename R> struct RayLoop {
+    R m, mz, cq, cw, ua, ub, halfp, inv_am, inv_amz;
+    bool mpos, mzpos;
+    int jshift, kshift, nq, nz;
+    const uint16_t *pairs;     // layout of this ray's major axis, already offset to plane k = 0, j = 0
+    int pitch;
+    long long plane;
+    __device__ __forceinline__ void init(const SiddonParams &P, const RaySetup &s)
+    {
+        m = (R)s.m; mz = (R)s.mz; cq = (R)s.cq; cw = (R)s.cw; ua = (R)s.ua; ub = (R)s.ub; halfp = (R)s.halfp;
+        inv_am = (R)s.inv_am; inv_amz = (R)s.inv_amz;
+        mpos = m >= (R)0; mzpos = mz >= (R)0;
+        jshift = s.jshift; kshift = s.kshift; nq = s.nq; nz = P.vol.nz;
+        pitch = s.xmajor ? P.pitch_xm : P.pitch_ym;
+        plane = s.xmajor ? P.plane_xm : P.plane_ym;
+        pairs = (s.xmajor ? P.xm : P.ym) + plane + 1;
+    }
+};
+
+// One column.  Calls sink(slot, j, k, label, w) for slot = 0,1(,2) in order of INCREASING column coordinate.
+// Weights may be zero; j/k may sit in the one-voxel apron (-1 or n) with a weight at rounding level.
+template <typename R, bool IS3D, typename Sink>
+__device__ __forceinline__ void slab_column(const RayLoop<R> &L, int i, Sink &sink)
+{
+    typedef Rn<R> A;
+    const R fi = (R)i;
+    const R a = A::max(fi, L.ua), b = A::min(A::add(fi, (R)1), L.ub);
+    const R wtot = A::sub(b, a);
+    if (!(wtot > (R)0)) return;
+    const R pa = A::sub(a, L.halfp), pb = A::sub(b, L.halfp);
+    const R qa = A::fma(L.m, pa, L.cq), qb = A::fma(L.m, pb, L.cq);
+    const R qmin = A::min(qa, qb), qmax = A::max(qa, qb);
+    const R jf = A::floor(qmin);
+    const R qhi = A::min(A::max(A::mul(A::sub(qmax, A::add(jf, (R)1)), L.inv_am), (R)0), wtot);
+    int j = (int)jf + L.jshift;
+    j = min(max(j, -1), L.nq - 1);                       // memory safety only; a no-op for finite geometry
+    const uint16_t *col = L.pairs + (long long)i * L.pitch + j;
+    if (!IS3D) {
+        const unsigned pr = *col;
+        const int lo = pr & 0xff, hi = pr >> 8;
+        const R wlo = A::sub(wtot, qhi);
+        if (L.mpos) { sink(0, j, 0, lo, wlo); sink(1, j + 1, 0, hi, qhi); }
+        else        { sink(0, j + 1, 0, hi, qhi); sink(1, j, 0, lo, wlo); }
+    } else {
+        const R wa = A::fma(L.mz, pa, L.cw), wb = A::fma(L.mz, pb, L.cw);
+        const R wmin = A::min(wa, wb), wmax = A::max(wa, wb);
+        const R kf = A::floor(wmin);
+        const R zhi = A::min(A::max(A::mul(A::sub(wmax, A::add(kf, (R)1)), L.inv_amz), (R)0), wtot);
+        int k = (int)kf + L.kshift;
+        k = min(max(k, -1), L.nz - 1);
+        const unsigned p0 = col[(long long)k * L.plane];
+        const unsigned p1 = col[(long long)(k + 1) * L.plane];
+        // p-length spent before the q / z crossing, walking towards +p
+        const R tq = L.mpos ? A::sub(wtot, qhi) : qhi;
+        const R tz = L.mzpos ? A::sub(wtot, zhi) : zhi;
+        const int jA = L.mpos ? j : j + 1, jB = L.mpos ? j + 1 : j;        // first / second along +p
+        const int kA = L.mzpos ? k : k + 1, kB = L.mzpos ? k + 1 : k;
+        const unsigned pA = L.mzpos ? p0 : p1, pB = L.mzpos ? p1 : p0;     // pair of plane kA / kB
+        const int shA = L.mpos ? 0 : 8, shB = L.mpos ? 8 : 0;              // byte of jA / jB inside a pair
+        const R t1 = A::min(tq, tz), t2 = A::max(tq, tz);
+        const R w1 = t1, w3 = A::sub(wtot, t2), w2 = A::sub(t2, t1);
+        const bool qfirst = tq < tz;                                       // q plane is crossed before z plane
+        sink(0, jA, kA, (pA >> shA) & 0xff, w1);
+        if (qfirst) sink(1, jB, kA, (pA >> shB) & 0xff, w2);
+        else        sink(1, jA, kB, (pB >> shA) & 0xff, w2);
+        sink(2, jB, kB, (pB >> shB) & 0xff, w3);
+    }
+}
+
+}  // namespace dexct

@@ -1,0 +1,16 @@
+"""Run-time switches of the drop-in modules (the reference has none: its constants are hard-coded in main.py)."""
+import os
+
+# Arithmetic of the kernels: 'f32' (default, the throughput path) or 'f64' (matches the reference's float64 numpy
+# results to ~1e-10).  Environment override: DEXCT_DTYPE.
+dtype = os.environ.get('DEXCT_DTYPE', 'f32')
+
+# Keep the per-material path lengths of the last (ct, phantom) pair on the device so that the second get_sino call
+# of a dual-energy pair (/root/reference/main.py:109-120) only re-runs the detection epilogue.
+cache_lengths = os.environ.get('DEXCT_CACHE_LENGTHS', '1') != '0'
+
+# Shard projection views (and decomposition pixels) over torch.distributed ranks when a process group is initialised.
+shard_views = os.environ.get('DEXCT_SHARD_VIEWS', '1') != '0'
+
+# Print progress the way the reference does (matdecomp.py:111-112)
+verbose = os.environ.get('DEXCT_VERBOSE', '0') != '0'

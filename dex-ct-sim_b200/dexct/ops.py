@@ -1,0 +1,176 @@
+"""Device-level operators over libdexct: torch tensors in, torch tensors out, nothing computed in Python.
+
+``Projector``   -- prepared workspace + Siddon/polyenergetic projection (replaces get_sino, /root/reference/main.py:120)
+``poly_detect`` -- detection from stored path lengths (second spectrum of a scan, main.py:109-120)
+``gn_decompose``-- Gauss-Newton decomposition (replaces optimize_sino_cpu, /root/reference/matdecomp.py:87-127)
+"""
+from __future__ import annotations
+
+import ctypes as C
+
+import numpy as np
+import torch
+
+from . import _native as N
+from ._native import DexctScan, DexctVolume, F32, F64
+
+_TORCH_DTYPE = {F32: torch.float32, F64: torch.float64}
+
+
+def dtype_code(dtype):
+    if dtype in (F32, 'f32', 'float32', torch.float32, np.float32):
+        return F32
+    if dtype in (F64, 'f64', 'float64', torch.float64, np.float64):
+        return F64
+    raise ValueError(f'dtype must be f32 or f64, got {dtype!r}')
+
+
+def make_scan(n_views, n_ch, fan_angle_total, SID, SDD, n_rows=1, h_iso=1.0, rotation=2.0 * np.pi, beta0=0.0):
+    """Project-defined scan conventions: view angles start at beta0 and advance by rotation/n_views;
+    channel centres are symmetric about the central ray; row centres symmetric about z = 0, pitch h_iso at the isocentre."""
+    dgamma = float(fan_angle_total) / n_ch
+    dzdet = float(h_iso) * SDD / SID
+    return DexctScan(n_views=n_views, n_rows=n_rows, n_ch=n_ch, reserved=0, sid=SID, sdd=SDD,
+                     beta0=beta0, dbeta=float(rotation) / n_views,
+                     gamma0=-0.5 * (n_ch - 1) * dgamma, dgamma=dgamma,
+                     z0=-0.5 * (n_rows - 1) * dzdet, dzdet=dzdet)
+
+
+def _as_device(a, dtype, device):
+    if isinstance(a, torch.Tensor):
+        return a.to(device=device, dtype=dtype).contiguous()
+    return torch.as_tensor(np.ascontiguousarray(a), device=device).to(dtype).contiguous()
+
+
+class Projector:
+    """Owns the device copy of the label volume and the prepared workspace for one (scan, volume) pair."""
+
+    def __init__(self, scan: DexctScan, labels, voxel, device=None):
+        N.require_device()
+        self.device = torch.device('cuda', torch.cuda.current_device()) if device is None else torch.device(device)
+        lab = labels if isinstance(labels, torch.Tensor) else torch.as_tensor(np.ascontiguousarray(labels, dtype=np.uint8))
+        if lab.dtype != torch.uint8:
+            raise TypeError('labels must be uint8')
+        if lab.dim() == 2:
+            lab = lab[None]
+        if lab.dim() != 3:
+            raise ValueError('labels must be [nz, ny, nx] or [ny, nx]')
+        self.labels = lab.to(self.device).contiguous()
+        nz, ny, nx = self.labels.shape
+        self.scan = scan
+        self.vol = DexctVolume(nx=nx, ny=ny, nz=nz, reserved=0, dx=float(voxel[0]), dy=float(voxel[1]), dz=float(voxel[2]))
+        nbytes = N.lib().dexct_siddon_workspace_bytes(C.byref(self.scan), C.byref(self.vol))
+        if nbytes == 0:
+            raise N.DexctError('invalid scan/volume sizes')
+        self.workspace = torch.empty(nbytes, dtype=torch.uint8, device=self.device)
+        self.prepare()
+
+    def prepare(self):
+        """Re-run after the label tensor was modified in place."""
+        with torch.cuda.device(self.device):
+            N.check(N.lib().dexct_siddon_prepare(C.byref(self.scan), C.byref(self.vol), N.ptr(self.labels),
+                                                 N.ptr(self.workspace), N.stream_ptr()))
+
+    @property
+    def rays_per_view(self):
+        return self.scan.n_rows * self.scan.n_ch
+
+    def tables_host(self):
+        """The sin/cos/z tables exactly as the device uses them (for checkers)."""
+        s = self.scan
+        out = dict(cos_beta=np.zeros(s.n_views), sin_beta=np.zeros(s.n_views), cos_gamma=np.zeros(s.n_ch),
+                   sin_gamma=np.zeros(s.n_ch), zdet=np.zeros(s.n_rows))
+        with torch.cuda.device(self.device):
+            N.check(N.lib().dexct_siddon_tables_host(
+                C.byref(s), N.ptr(self.workspace), *[out[k].ctypes.data_as(C.c_void_p) for k in
+                                                     ('cos_beta', 'sin_beta', 'cos_gamma', 'sin_gamma', 'zdet')],
+                N.stream_ptr()))
+        return out
+
+    def project(self, mu, W, view_begin=0, view_count=None, dtype=F32, want_log=True, want_L=False,
+                counts=None, logs=None, L=None):
+        """counts/logs [nSpec, view_count, n_rows, n_ch], L [view_count, n_rows, n_ch, K] (or None)."""
+        code = dtype_code(dtype)
+        td = _TORCH_DTYPE[code]
+        s = self.scan
+        view_count = s.n_views - view_begin if view_count is None else view_count
+        mu = _as_device(mu, td, self.device)
+        W = _as_device(W, td, self.device)
+        if mu.dim() != 2 or W.dim() != 2 or mu.shape[1] != W.shape[1]:
+            raise ValueError('mu must be [K, nE] and W [nSpec, nE] on the same energy grid')
+        K, nE = mu.shape
+        nS = W.shape[0]
+        shape = (nS, view_count, s.n_rows, s.n_ch)
+        if counts is None:
+            counts = torch.empty(shape, dtype=td, device=self.device)
+        if want_log and logs is None:
+            logs = torch.empty(shape, dtype=td, device=self.device)
+        if want_L and L is None:
+            L = torch.empty((view_count, s.n_rows, s.n_ch, K), dtype=td, device=self.device)
+        with torch.cuda.device(self.device):
+            N.check(N.lib().dexct_siddon_poly(C.byref(s), C.byref(self.vol), N.ptr(self.workspace), view_begin, view_count,
+                                              N.ptr(mu), K, nE, N.ptr(W), nS, N.ptr(counts),
+                                              N.ptr(logs if want_log else None), N.ptr(L if want_L else None),
+                                              code, N.stream_ptr()))
+        return counts, (logs if want_log else None), (L if want_L else None)
+
+    def trace(self, ray_ids, max_seg=4096, dtype=F32):
+        """Ordered voxel sequence of the given rays: list of (vox int64[], lab uint8[], len float[]) numpy triples."""
+        code = dtype_code(dtype)
+        td = _TORCH_DTYPE[code]
+        ids = torch.as_tensor(np.asarray(ray_ids, dtype=np.int64), device=self.device)
+        n = ids.numel()
+        vox = torch.empty((n, max_seg), dtype=torch.int64, device=self.device)
+        lab = torch.empty((n, max_seg), dtype=torch.uint8, device=self.device)
+        ln = torch.empty((n, max_seg), dtype=td, device=self.device)
+        ns = torch.empty(n, dtype=torch.int32, device=self.device)
+        with torch.cuda.device(self.device):
+            N.check(N.lib().dexct_siddon_trace(C.byref(self.scan), C.byref(self.vol), N.ptr(self.workspace), N.ptr(ids), n,
+                                               max_seg, N.ptr(vox), N.ptr(lab), N.ptr(ln), N.ptr(ns), code, N.stream_ptr()))
+        ns_h = ns.cpu().numpy()
+        if (ns_h > max_seg).any():
+            raise N.DexctError(f'trace overflow: a ray has {ns_h.max()} segments, max_seg={max_seg}')
+        vox_h, lab_h, ln_h = vox.cpu().numpy(), lab.cpu().numpy(), ln.cpu().numpy()
+        return [(vox_h[t, :ns_h[t]], lab_h[t, :ns_h[t]], ln_h[t, :ns_h[t]]) for t in range(n)]
+
+
+def poly_detect(L, mu, W, dtype=F32, want_log=True):
+    """counts, logs [nSpec, *L.shape[:-1]] from stored lengths L [..., K] (device tensor)."""
+    N.require_device()
+    code = dtype_code(dtype)
+    td = _TORCH_DTYPE[code]
+    dev = L.device
+    L2 = L.to(td).contiguous()
+    mu = _as_device(mu, td, dev)
+    W = _as_device(W, td, dev)
+    K, nE = mu.shape
+    nS = W.shape[0]
+    n_rays = L2.numel() // K
+    counts = torch.empty((nS,) + tuple(L2.shape[:-1]), dtype=td, device=dev)
+    logs = torch.empty_like(counts) if want_log else None
+    with torch.cuda.device(dev):
+        N.check(N.lib().dexct_poly_detect(N.ptr(L2), n_rays, N.ptr(mu), K, nE, N.ptr(W), nS, N.ptr(counts), N.ptr(logs),
+                                          code, N.stream_ptr()))
+    return counts, logs
+
+
+def gn_decompose(g, i0, mus, n_iters, mask_thresh=0.0, dtype=F32, out=None):
+    """g [2, ...] counts (device tensor or array), i0 [2, nE], mus [2, nE] -> a [..., 2] device tensor."""
+    N.require_device()
+    code = dtype_code(dtype)
+    td = _TORCH_DTYPE[code]
+    dev = g.device if isinstance(g, torch.Tensor) and g.is_cuda else torch.device('cuda', torch.cuda.current_device())
+    g = _as_device(g, td, dev)
+    i0 = _as_device(i0, td, dev)
+    mus = _as_device(mus, td, dev)
+    if g.shape[0] != 2 or i0.shape[0] != 2 or mus.shape[0] != 2 or i0.shape != mus.shape:
+        raise ValueError('g must be [2, ...], i0 and mus [2, nE]')
+    P = g[0].numel()
+    nE = i0.shape[1]
+    if out is None:
+        out = torch.empty(tuple(g.shape[1:]) + (2,), dtype=td, device=dev)
+    scratch = torch.empty(16, dtype=torch.uint8, device=dev)
+    with torch.cuda.device(dev):
+        N.check(N.lib().dexct_gn_decompose(N.ptr(g), N.ptr(i0), N.ptr(mus), nE, P, int(n_iters), float(mask_thresh),
+                                           N.ptr(out), N.ptr(scratch), code, N.stream_ptr()))
+    return out

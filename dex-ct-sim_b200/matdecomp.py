@@ -1,0 +1,101 @@
+"""Drop-in ``matdecomp``: dual-energy basis-material decomposition on the B200.
+
+Same public names as /root/reference/matdecomp.py (``get_basismat_sinos``, ``do_matdecomp_gn``, ``optimize_sino``,
+``optimize_sino_cpu``, the basis-material constants) so that /root/reference/main.py:22,153 and plots.py:18 work
+unchanged.  The per-pixel Newton iteration of matdecomp.py:87-127 runs in csrc/gn.cu; this module only assembles the
+small spectral tables on the host (matdecomp.py:138-160) and moves arrays across the boundary.
+"""
+from __future__ import annotations
+
+import numpy as np
+import torch
+
+import xcompy as xc
+from dexct import config, dist
+from dexct.ops import dtype_code, gn_decompose
+
+# Basis materials -- the same two ICRU compositions the reference hard-codes (matdecomp.py:11-17).
+mat1 = 'ICRU tissue'
+matcomp1 = 'H(10.2)C(14.3)N(3.4)O(70.8)Na(0.2)P(0.3)S(0.3)Cl(0.2)K(0.3)'
+density1 = 1.06  # [g/cm3]
+mat2 = 'ICRU bone'
+matcomp2 = 'H(3.4)C(15.5)N(4.2)O(43.5)Na(0.1)Mg(0.2)P(10.3)S(0.3)Ca(22.5)'
+density2 = 1.92  # [g/cm3]
+
+
+def spectral_tables(ct, spec1, spec2):
+    """Host-side model tables of the decomposition (matdecomp.py:138-160).
+
+    Union energy grid of the two spectra; first bin width runs from 0; detector efficiency interpolated onto the grid
+    (times E for an energy-integrating detector); spectra interpolated with numpy's end-value clamping; basis rows are
+    MASS attenuation (the reference leaves the density multiply commented out, so the outputs are g/cm^2).
+    Returns ee [nE], i0 [2, nE], mus [2, nE].
+    """
+    ee = np.unique(np.concatenate([np.asarray(spec1.E), np.asarray(spec2.E)]))
+    dE = np.diff(ee, prepend=0.0)
+    resp = np.interp(ee, ct.det_E, ct.det_eta_E)
+    if ct.eid:
+        resp = resp * ee
+    i0 = np.stack([np.interp(ee, s.E, s.I0) * resp * dE for s in (spec1, spec2)])
+    mus = np.stack([xc.mixatten(mc, ee) for mc in (matcomp1, matcomp2)])
+    return ee, i0, mus
+
+
+def optimize_sino(Sino_gg, ee, i0, mus, n_iters, verbose=True, dtype=None, mask_thresh=0.0, to_host=True):
+    """GPU Newton iterations; signature of matdecomp.py:20 (``ee`` is unused there too).
+
+    Sino_gg [2, nViews, nBins] counts; i0 [2, nBins, nE] (all bins identical, matdecomp.py:151) or [2, nE];
+    mus [2, nE].  Returns [nViews, nBins, 2] -- float64 numpy by default, the device tensor with ``to_host=False``.
+    """
+    del ee, verbose
+    code = dtype_code(config.dtype if dtype is None else dtype)
+    i0 = np.asarray(i0, dtype=np.float64)
+    if i0.ndim == 3:
+        if i0.shape[1] > 1 and not np.array_equal(i0[:, :1, :].repeat(i0.shape[1], axis=1), i0):
+            raise NotImplementedError('per-channel spectra are not supported: the reference tiles one spectrum over '
+                                      'all channels (matdecomp.py:151) and the kernel relies on that')
+        i0 = i0[:, 0, :]
+    mus = np.asarray(mus, dtype=np.float64)
+    if mus.shape[0] != 2:
+        raise NotImplementedError('two basis materials only (matdecomp.py:155)')
+    out = gn_decompose(Sino_gg, i0, mus, n_iters, mask_thresh=mask_thresh, dtype=code)
+    return out.detach().cpu().numpy().astype(np.float64) if to_host else out
+
+
+# The reference keeps a CPU twin because its cupy version misbehaved (matdecomp.py:89-91); here both names run the
+# same kernel -- there is no CPU implementation in this package.
+optimize_sino_cpu = optimize_sino
+
+
+def do_matdecomp_gn(ct, sino1, sino2, spec1, spec2, n_iters, mask_thresh=0.0, to_host=True):
+    """matdecomp.py:130-164.  With a process group and ``config.shard_views`` the pixels are split by view range,
+    decomposed without communication and the result all-gathered."""
+    ee, i0, mus = spectral_tables(ct, spec1, spec2)
+    if isinstance(sino1, torch.Tensor):
+        g = torch.stack([sino1, sino2])
+    else:
+        g = np.stack([np.asarray(sino1, dtype=np.float64), np.asarray(sino2, dtype=np.float64)])
+    rank, ws = dist.world() if config.shard_views else (0, 1)
+    if ws > 1:
+        n_views = g.shape[1]
+        v0, nv = dist.shard_range(n_views, rank, ws)
+        # the air threshold needs the global maximum: every rank holds the full input here, so take it locally
+        gmax = float(g[0].max())
+        local = optimize_sino(g[:, v0:v0 + nv], ee, i0, mus, n_iters, mask_thresh=0.0, to_host=False)
+        if mask_thresh > 0:
+            g1 = torch.as_tensor(g[0, v0:v0 + nv], device=local.device)
+            local[g1 >= mask_thresh * gmax] = 0
+        full = dist.all_gather_views(local, n_views, dim=0)
+        return full.detach().cpu().numpy().astype(np.float64) if to_host else full
+    return optimize_sino(g, ee, i0, mus, n_iters, mask_thresh=mask_thresh, to_host=to_host)
+
+
+def get_basismat_sinos(ct, sino_raw_1, sino_raw_2, spec1, spec2, n_iters=30, mask_thresh=0.95):
+    """Basis-material sinograms of a dual-energy acquisition (matdecomp.py:167-207).
+
+    ``sino_raw_1/2``: photon counts ``[N_proj, N_channels]``; ``spec1/2``: the spectra they were acquired with.  Pixels
+    whose first measurement reaches ``mask_thresh`` of its maximum (air) are zeroed, as in the reference
+    (matdecomp.py:195-196,204-205) -- inside the kernel.  Returns two float64 arrays ``[N_proj, N_channels]``.
+    """
+    a = do_matdecomp_gn(ct, sino_raw_1, sino_raw_2, spec1, spec2, n_iters, mask_thresh=mask_thresh)
+    return a[..., 0], a[..., 1]

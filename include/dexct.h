@@ -1,0 +1,142 @@
+/*
+ * dexct.h -- C ABI of libdexct.so: the B200 (sm_100a) implementation of the data-parallel hot path of
+ * gjadick/dex-ct-sim.  Plain pointers and sizes only; no C++/torch types cross this boundary.
+ *
+ * The reference has no FFI of its own -- its "operator API" for this path is three Python call sites:
+ *     xtomosim.forward_project.get_sino(ct, phantom, spec)            /root/reference/main.py:120
+ *     matdecomp.get_basismat_sinos(ct, s1, s2, spec1, spec2, n_iters)  /root/reference/main.py:153, matdecomp.py:167
+ *     xtomosim.back_project.get_recon(sino, ct, spec, N, FOV, ramp)    /root/reference/main.py:134,168
+ * Each entry point below states which of those (and which lines of matdecomp.py) it replaces.  The ctypes
+ * binding a maintainer would add on the reference side is shown in INTEGRATION.md and lives, working, in
+ * dex-ct-sim_b200/dexct/_native.py.
+ *
+ * Conventions
+ *   - Every data pointer is a DEVICE pointer unless its name ends in _host.  The caller owns all buffers.
+ *   - Work is enqueued on the given CUDA stream (a cudaStream_t passed as void*; NULL = default stream) and the
+ *     call returns without synchronising, except the *_host helpers which synchronise that stream.
+ *   - Return value: 0 on success, negative DEXCT_E* on failure; dexct_last_error() gives the message of the last
+ *     failure on the calling thread.  No global mutable state besides that thread-local string.
+ *   - dtype: DEXCT_F32 or DEXCT_F64 selects the arithmetic of the kernels and the element type of every
+ *     "void*" floating-point buffer of that call.
+ */
+#ifndef DEXCT_H
+#define DEXCT_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define DEXCT_VERSION 100
+
+#define DEXCT_F32 0
+#define DEXCT_F64 1
+
+#define DEXCT_OK            0
+#define DEXCT_EINVAL      (-1)   /* bad argument (null pointer, non-positive size, unsupported combination) */
+#define DEXCT_ECUDA       (-2)   /* CUDA runtime error, text in dexct_last_error() */
+#define DEXCT_ENODEVICE   (-3)   /* no sm_100 device: there is NO CPU fallback */
+#define DEXCT_ECAPACITY   (-4)   /* tables too large for on-chip staging */
+
+/* Scan geometry: third-generation equiangular fan (cone when n_rows > 1), source on a circle in the z = 0 plane.
+ * Mirrors the fields of the reference's FanBeamGeometry(N_channels, N_proj, gamma_fan, SID, SDD, h_iso, ...)
+ * (/root/reference/plots.py:109-111, input/params.txt:18-27).
+ *   beta_v  = beta0  + v * dbeta      source angle of view v;   S = SID (cos beta, sin beta, 0)
+ *   gamma_c = gamma0 + c * dgamma     fan angle of channel c;   ray direction -(cos(beta+gamma), sin(beta+gamma))
+ *   zdet_r  = z0     + r * dzdet      z of detector row r at the detector (distance SDD from the source)      */
+typedef struct DexctScan {
+    int32_t n_views;      /* views in the whole scan (size of the angle table) */
+    int32_t n_rows;       /* detector rows (1 = single-slice fan beam) */
+    int32_t n_ch;         /* detector channels */
+    int32_t reserved;
+    double sid, sdd;      /* source-isocentre and source-detector distance [cm] */
+    double beta0, dbeta;
+    double gamma0, dgamma;
+    double z0, dzdet;
+} DexctScan;
+
+/* Voxel phantom: uint8 material labels, labels[(k*ny + j)*nx + i], centred on the origin, voxel size in cm
+ * (input/params.txt:10-15; VoxelPhantom at plots.py:124).                                                   */
+typedef struct DexctVolume {
+    int32_t nx, ny, nz;
+    int32_t reserved;
+    double dx, dy, dz;
+} DexctVolume;
+
+int         dexct_version(void);
+const char *dexct_last_error(void);
+/* Number of CUDA devices with compute capability 10.x visible to the process (0 => every call fails). */
+int         dexct_device_count(void);
+
+/* ---- forward projection: replaces get_sino (main.py:120) ------------------------------------------------ */
+
+/* Bytes of device scratch needed by dexct_siddon_prepare for this scan + volume (angle tables and the two
+ * minor-axis-contiguous "pair" layouts of the label volume).                        */
+size_t dexct_siddon_workspace_bytes(const DexctScan *scan, const DexctVolume *vol);
+
+/* Fill the workspace: sin/cos tables (device double precision) and the re-laid-out label volume.  Must be
+ * called again whenever labels, scan or vol change.  Cost: one pass over the volume.                        */
+int dexct_siddon_prepare(const DexctScan *scan, const DexctVolume *vol, const uint8_t *labels,
+                         void *workspace, void *stream);
+
+/* Copy the angle tables the device uses to host arrays (each may be NULL): cos/sin beta [n_views],
+ * cos/sin gamma [n_ch], zdet [n_rows].  Synchronises.  Lets a checker trace exactly the rays the kernel traces. */
+int dexct_siddon_tables_host(const DexctScan *scan, const void *workspace, double *cos_beta_host,
+                             double *sin_beta_host, double *cos_gamma_host, double *sin_gamma_host,
+                             double *zdet_host, void *stream);
+
+/* Siddon traversal + fused polyenergetic Beer-Lambert detection for views [view_begin, view_begin+view_count).
+ *   mu_KxE   [K][nE]        linear attenuation of material label m at energy bin e [1/cm]
+ *   W_SxE    [nSpec][nE]    detected weight of spectrum s in bin e (I0 * eta * (E if energy-integrating) * dE,
+ *                           the reference's i0, matdecomp.py:146-150)
+ *   counts   [nSpec][view_count][n_rows][n_ch]   sum_e W exp(-sum_m L_m mu_m)            (sino_raw)
+ *   logs     same shape or NULL                   -ln(counts / sum_e W)                   (sino_log)
+ *   L_out    [view_count][n_rows][n_ch][K] or NULL  per-material path length [cm]
+ * K <= 256 (uint8 labels); labels >= K are a caller error (checked only in debug builds).                   */
+int dexct_siddon_poly(const DexctScan *scan, const DexctVolume *vol, const void *workspace,
+                      int32_t view_begin, int32_t view_count,
+                      const void *mu_KxE, int32_t K, int32_t nE, const void *W_SxE, int32_t nSpec,
+                      void *counts, void *logs, void *L_out, int32_t dtype, void *stream);
+
+/* Detection only, from stored path lengths L [n_rays][K] (second spectrum of the same scan: main.py:109-120
+ * calls get_sino twice on the same ct/phantom).  counts/logs [nSpec][n_rays].                               */
+int dexct_poly_detect(const void *L, int64_t n_rays, const void *mu_KxE, int32_t K, int32_t nE,
+                      const void *W_SxE, int32_t nSpec, void *counts, void *logs, int32_t dtype, void *stream);
+
+/* Debug: ordered voxel crossing sequence of selected rays.  ray_ids [n_rays] = (view*n_rows + row)*n_ch + ch.
+ * For ray t the first min(n_seg[t], max_seg) entries of vox/lab/len rows t are valid: linear voxel index
+ * (k*ny + j)*nx + i, its label, and the intersection length [cm] (float or double per dtype).               */
+int dexct_siddon_trace(const DexctScan *scan, const DexctVolume *vol, const void *workspace,
+                       const int64_t *ray_ids, int32_t n_rays, int32_t max_seg,
+                       int64_t *vox, uint8_t *lab, void *len, int32_t *n_seg, int32_t dtype, void *stream);
+
+/* ---- Gauss-Newton two-basis decomposition: replaces optimize_sino_cpu (matdecomp.py:87-127) --------------- */
+
+/* Per pixel p (P = views*channels, any order): n_iters full-Newton steps on the Poisson likelihood of the two
+ * measurements g[0][p], g[1][p] under nu_m = sum_e i0[m][e] exp(-(a1 mu[0][e] + a2 mu[1][e])), from a = 1e-6.
+ *   g_2xP   [2][P] measured counts;  i0_2xE [2][nE] (the reference tiles it over channels, matdecomp.py:151);
+ *   mus_2xE [2][nE] basis attenuation;  a_out [P][2].
+ * mask_thresh > 0 additionally zeroes both outputs of pixels with g[0][p] >= mask_thresh * max_p g[0][p]
+ * (get_basismat_sinos, matdecomp.py:195-205); scratch = >= 16 bytes of device memory for that maximum
+ * (may be NULL when mask_thresh <= 0).                                                                        */
+int dexct_gn_decompose(const void *g_2xP, const void *i0_2xE, const void *mus_2xE, int32_t nE, int64_t P,
+                       int32_t n_iters, double mask_thresh, void *a_out_Px2, void *scratch,
+                       int32_t dtype, void *stream);
+
+/* ---- fan-beam filtered back-projection: replaces get_recon (main.py:134,168) ------------------------------ */
+
+/* Equiangular fan-beam FBP of one sinogram row-set as a gather over views.
+ *   sino [n_views][n_ch] (dtype);  image [n_matrix][n_matrix] (dtype), attenuation units of the sinogram per cm;
+ *   fov  side of the reconstructed square [cm];  ramp  cut-off as a fraction of Nyquist (sinc window);
+ *   scratch: dexct_fbp_workspace_bytes() of device memory.                                                    */
+size_t dexct_fbp_workspace_bytes(const DexctScan *scan, int32_t dtype);
+int dexct_fbp_fan(const DexctScan *scan, const void *sino, int32_t view_begin, int32_t view_count,
+                  int32_t n_matrix, double fov, double ramp, void *image, int32_t accumulate,
+                  void *scratch, int32_t dtype, void *stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* DEXCT_H */
