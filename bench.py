@@ -1,0 +1,404 @@
+#!/usr/bin/env python3
+"""Benchmark of the hot path: Siddon polyenergetic forward projection + Gauss-Newton two-basis decomposition.
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl b200|reference]
+    python -m torch.distributed.run --nnodes=1 --nproc-per-node N ... bench.py --gpus N ...
+
+Workload (BASELINE.json configs[1], "C2"): synthetic 512x512 single-slice phantom, 900 channels x 1000 views, 120 energy
+bins, dual-spectrum sinograms (both spectra in ONE traversal) followed by the GN decomposition of every sinogram pixel
+(10 iterations, the fixed count configs[2] names).  One step = one whole scan: 900 000 rays -> 2 count sinograms ->
+900 000 decomposed pixel pairs.  Unit = rays (= pixels) per second through the whole path.
+
+N > 1 (weak scaling): the scan has N x 1000 views; rank r owns the contiguous view range [1000 r, 1000 (r+1)), traces and
+decomposes it without communication, and the view-major sinograms are assembled with one NCCL all-gather per array.
+
+`value`   : device throughput, inputs resident in HBM, CUDA events around every step, max over ranks.
+`e2e`     : the same work through the reference-facing Python entry points (get_sino x2 / get_basismat_sinos) with host
+            numpy arrays in and out; every step uploads the phantom again and reads the results back.
+`roofline`: the Siddon kernel against the bytes-per-ray HBM roofline of SURVEY.md section 8(d); `roofline_gn`: the GN kernel
+            against the FP32 FMA pipe.
+`cpu_baseline` / `--impl reference`: the CPU oracle (oracle/: C restatement of Siddon 1985 with OpenMP + the numpy
+            restatement of the reference's optimize_sino_cpu, one process per core) on a bounded sample of the same scan.
+"""
+import argparse
+import json
+import os
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+PKG = os.path.join(ROOT, 'dex-ct-sim_b200')
+for _p in (ROOT, PKG):
+    if _p not in sys.path:
+        sys.path.insert(0, _p)
+
+import numpy as np  # noqa: E402
+
+VIEWS_PER_GPU = 1000
+N_CH = 900
+GN_ITERS = 10
+MASK_THRESH = 0.95
+METRIC = 'siddon_poly_gn_rays_per_s'
+UNIT = 'rays/s'
+WORKLOAD = ('C2: 512x512x1 phantom (K=8 materials), 900 ch x 1000 views per GPU, 120 energy bins, 2 spectra fused, '
+            'GN 10 iters water/bone, air mask 0.95')
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument('--gpus', type=int, default=1)
+    ap.add_argument('--steps', type=int, default=200)
+    ap.add_argument('--warmup', type=int, default=5)
+    ap.add_argument('--impl', default='b200', choices=['b200', 'reference'])
+    ap.add_argument('--dtype', default='f32', choices=['f32', 'f64'])
+    ap.add_argument('--cpu-views', type=int, default=0, help='views in the CPU sample (0 = auto)')
+    ap.add_argument('--no-cpu-baseline', action='store_true')
+    ap.add_argument('--no-e2e', action='store_true')
+    return ap.parse_args()
+
+
+# ----------------------------------------------------------------------------------------------------------------
+# CPU arm (oracle).  Used for `cpu_baseline` and `--impl reference`.
+
+def _gn_view_job(args):
+    from oracle import gn_oracle
+    g, i0, mus, n_iters = args
+    nB = g.shape[2]
+    i0_t = np.tile(i0, (1, nB)).reshape(2, nB, i0.shape[1])
+    return gn_oracle.optimize_sino_cpu(g, None, i0_t, mus, n_iters)
+
+
+class CpuArm:
+    """The oracle's CPU implementation of one bounded sample of the workload: `n_views` views spread evenly over the
+    rotation; Siddon + detection in C with OpenMP over all host threads, GN in numpy with one worker process per core."""
+
+    def __init__(self, n_views):
+        import multiprocessing as mp
+        import oracle
+        from oracle import gn_oracle
+        from dexct import synthetic as S
+        from xtomosim.forward_project import spectral_weights
+        oracle.build()
+        self.oracle = oracle
+        ct, ph, lo, hi = S.make_config('C2', n_views=VIEWS_PER_GPU)
+        tabs = oracle.fan_tables(ct.N_channels, ct.N_proj, ct.gamma_fan, ct.rotation, ct.beta0, ct.N_rows, ct.h_iso, ct.SID, ct.SDD)
+        pick = np.linspace(0, ct.N_proj, n_views, endpoint=False).astype(int)
+        tabs = {k: (v[pick] if k.endswith('beta') else v) for k, v in tabs.items()}
+        self.scan = oracle.Scan(ph.M, (ph.dx, ph.dy, ph.dz), ct.SID, ct.SDD, tabs)
+        self.mu = ph.mu_table(lo.E)
+        self.W = np.stack([spectral_weights(ct, lo), spectral_weights(ct, hi)])
+        import matdecomp
+        _, self.i0, self.mus = gn_oracle.gn_model_tables(ct, lo, hi, matdecomp.xc.mixatten)
+        self.n_views = n_views
+        self.cores = os.cpu_count() or 1
+        self.threads = oracle.num_threads()
+        self.pool = mp.get_context('spawn').Pool(self.cores, initializer=_worker_init) if self.cores > 1 else None
+        self.seg_per_ray = None
+
+    def step(self):
+        counts, _, seg = self.scan.project_poly(self.mu, self.W, want_log=True)
+        self.seg_per_ray = seg / (self.n_views * N_CH)
+        g = counts[:, :, 0, :]                                            # [2, views, ch]
+        mask = g[0] >= MASK_THRESH * g[0].max()
+        jobs = [(g[:, v:v + 1], self.i0, self.mus, GN_ITERS) for v in range(self.n_views)]
+        outs = self.pool.map(_gn_view_job, jobs, chunksize=1) if self.pool else [_gn_view_job(j) for j in jobs]
+        a = np.concatenate(outs, axis=0)
+        a[mask] = 0
+        return a
+
+    def close(self):
+        if self.pool:
+            self.pool.close()
+            self.pool.join()
+
+    def describe(self, value):
+        return {'value': value, 'unit': UNIT, 'cores': self.cores, 'kind': 'port',
+                'sample': f'{self.n_views} of {VIEWS_PER_GPU} views of the C2 scan, evenly spaced ({self.n_views * N_CH} rays): '
+                          f'oracle/siddon_oracle.c float64 Siddon 1985 + Beer-Lambert (OpenMP, {self.threads} threads) then '
+                          f'oracle/gn_oracle.py optimize_sino_cpu float64 numpy ({GN_ITERS} iters, {self.cores} worker processes)'}
+
+
+def auto_cpu_views():
+    # ~80 ms per view and core for the numpy Newton loop at 900 x 120 x 10: 24 views per core
+    # make a step of about 2-3 s
+    return int(min(VIEWS_PER_GPU, 24 * (os.cpu_count() or 1)))
+
+
+def _worker_init():
+    os.environ['OMP_NUM_THREADS'] = '1'
+
+
+def run_reference(args):
+    rank = int(os.environ.get('RANK', '0'))
+    if rank != 0:
+        return
+    arm = CpuArm(args.cpu_views or auto_cpu_views())
+    for _ in range(min(args.warmup, 1)):
+        arm.step()
+    t = []
+    for _ in range(max(1, min(args.steps, 5))):
+        t0 = time.perf_counter()
+        arm.step()
+        t.append(time.perf_counter() - t0)
+    arm.close()
+    steps = len(t)
+    ms = 1e3 * sum(t) / steps
+    value = arm.n_views * N_CH / (ms * 1e-3)
+    line = {'impl': 'reference', 'metric': METRIC, 'value': value, 'unit': UNIT, 'n_gpus': args.gpus, 'steps': steps,
+            'warmup': min(args.warmup, 1), 'ms_per_step': ms, 'higher_is_better': True, 'scaling': 'weak',
+            'vs_baseline': None, 'dtype': 'f64', 'data': 'synthetic',
+            'config': {'workload': WORKLOAD, 'step': 'bounded sample: see cpu_baseline.sample'},
+            'cpu_baseline': arm.describe(value),
+            'e2e': {'value': value, 'unit': UNIT, 'h2d_bytes_per_step': 0, 'd2h_bytes_per_step': 0},
+            'gpu_launches': 0}
+    print(json.dumps(line), flush=True)
+
+
+# ----------------------------------------------------------------------------------------------------------------
+# clocks
+
+class ClockSampler(threading.Thread):
+    def __init__(self, index, period=0.02):
+        super().__init__(daemon=True)
+        self.period = period
+        self.samples = []
+        self.reasons = set()
+        self.stop_flag = threading.Event()
+        self.ok = False
+        try:
+            import pynvml
+            import torch
+            pynvml.nvmlInit()
+            self.nv = pynvml
+            try:
+                self.h = pynvml.nvmlDeviceGetHandleByUUID(('GPU-' + str(torch.cuda.get_device_properties(index).uuid)).encode())
+            except Exception:                                             # noqa: BLE001
+                self.h = pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.max_mhz = pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM)
+            self.ok = True
+        except Exception as e:                                            # noqa: BLE001
+            self.err = repr(e)
+
+    NAMES = {0x1: 'gpu_idle', 0x2: 'applications_clocks_setting', 0x4: 'sw_power_cap', 0x8: 'hw_slowdown', 0x10: 'sync_boost',
+             0x20: 'sw_thermal_slowdown', 0x40: 'hw_thermal_slowdown', 0x80: 'hw_power_brake_slowdown', 0x100: 'display_clock_setting'}
+
+    def sample(self):
+        nv = self.nv
+        mhz = nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM)
+        try:
+            r = nv.nvmlDeviceGetCurrentClocksEventReasons(self.h)
+        except Exception:                                                 # noqa: BLE001
+            r = nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
+        util = nv.nvmlDeviceGetUtilizationRates(self.h).gpu
+        self.samples.append((mhz, util))
+        for bit, name in self.NAMES.items():
+            if r & bit and name != 'gpu_idle':
+                self.reasons.add(name)
+
+    def run(self):
+        while self.ok and not self.stop_flag.is_set():
+            try:
+                self.sample()
+            except Exception:                                             # noqa: BLE001
+                pass
+            time.sleep(self.period)
+
+    def finish(self):
+        self.stop_flag.set()
+        if self.ok:
+            self.join(timeout=2)
+        if not self.ok or not self.samples:
+            return {'sm_mhz': None, 'sm_max_mhz': getattr(self, 'max_mhz', None), 'reasons': [], 'note': 'no samples'}
+        mhz = sorted(m for m, _ in self.samples)
+        return {'sm_mhz': mhz[len(mhz) // 2], 'sm_max_mhz': self.max_mhz, 'reasons': sorted(self.reasons),
+                'samples': len(mhz)}
+
+
+# ----------------------------------------------------------------------------------------------------------------
+# B200 arm
+
+def run_b200(args):
+    import torch
+    import torch.distributed as dist
+
+    from dexct import _native as N
+    from dexct import synthetic as S
+    from dexct import dist as ddist
+    from dexct.ops import Projector, count_segments, dtype_code, gn_decompose, make_scan
+    from xtomosim import forward_project as FP
+    import matdecomp
+
+    rank = int(os.environ.get('RANK', '0'))
+    local_rank = int(os.environ.get('LOCAL_RANK', '0'))
+    ws = int(os.environ.get('WORLD_SIZE', '1'))
+    if not torch.cuda.is_available():
+        raise SystemExit('bench.py: no CUDA device -- this framework has no CPU fallback (use --impl reference for the CPU arm)')
+    torch.cuda.set_device(local_rank)
+    dev = torch.device('cuda', local_rank)
+    if ws > 1:
+        os.environ.setdefault('MASTER_ADDR', '127.0.0.1')
+        dist.init_process_group('nccl', device_id=dev)
+    N.require_device()
+    code = dtype_code(args.dtype)
+    td = torch.float32 if args.dtype == 'f32' else torch.float64
+
+    # ---- the scan: ws x 1000 views, this rank owns [v0, v0 + nv)
+    n_views = VIEWS_PER_GPU * ws
+    ct, ph, lo, hi = S.make_config('C2', n_views=n_views)
+    v0, nv = ddist.shard_range(n_views, rank, ws)
+    scan = make_scan(ct.N_proj, ct.N_channels, ct.gamma_fan, ct.SID, ct.SDD, rotation=ct.rotation)
+    pj = Projector(scan, ph.M, (ph.dx, ph.dy, ph.dz), device=dev)
+    mu = torch.as_tensor(ph.mu_table(lo.E), dtype=td, device=dev)
+    W = torch.as_tensor(np.stack([FP.spectral_weights(ct, lo), FP.spectral_weights(ct, hi)]), dtype=td, device=dev)
+    ee, i0_h, mus_h = matdecomp.spectral_tables(ct, lo, hi)
+    i0 = torch.as_tensor(i0_h, dtype=td, device=dev)
+    mus = torch.as_tensor(mus_h, dtype=td, device=dev)
+    rays_local = nv * N_CH
+    counts = torch.empty((2, nv, 1, N_CH), dtype=td, device=dev)
+    logs = torch.empty_like(counts)
+    basis = torch.empty((nv, 1, N_CH, 2), dtype=td, device=dev)
+    if ws > 1:
+        g_counts = torch.empty((ws, 2, nv, 1, N_CH), dtype=td, device=dev)
+        g_logs = torch.empty_like(g_counts)
+        g_basis = torch.empty((ws, nv, 1, N_CH, 2), dtype=td, device=dev)
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)      # > 126 MB L2
+
+    ev = lambda: torch.cuda.Event(enable_timing=True)                   # noqa: E731
+
+    def step(timers=None):
+        if timers is not None:
+            timers[0].record()
+        pj.project(mu, W, view_begin=v0, view_count=nv, dtype=code, want_log=True, counts=counts, logs=logs)
+        if timers is not None:
+            timers[1].record()
+        gn_decompose(counts.view(2, -1), i0, mus, GN_ITERS, mask_thresh=MASK_THRESH, dtype=code, out=basis.view(-1, 2),
+                     reduce_max_over_ranks=ws > 1)
+        if timers is not None:
+            timers[2].record()
+        if ws > 1:
+            dist.all_gather_into_tensor(g_counts, counts)
+            dist.all_gather_into_tensor(g_logs, logs)
+            dist.all_gather_into_tensor(g_basis, basis)
+
+    def barrier():
+        if ws > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for _ in range(max(args.warmup, 3)):
+        flush.zero_()
+        step()
+    barrier()
+
+    sampler = ClockSampler(local_rank) if rank == 0 else None
+    if sampler:
+        sampler.start()
+    marks = []
+    barrier()
+    for _ in range(args.steps):
+        flush.zero_()
+        t = [ev() for _ in range(4)]
+        step(t)
+        t[3].record()
+        marks.append(t)
+    barrier()
+    clocks = sampler.finish() if sampler else None
+    tot = sum(t[0].elapsed_time(t[3]) for t in marks)
+    t_sid = sum(t[0].elapsed_time(t[1]) for t in marks) / args.steps
+    t_gn = sum(t[1].elapsed_time(t[2]) for t in marks) / args.steps
+    tt = torch.tensor([tot, t_sid, t_gn], dtype=torch.float64, device=dev)
+    if ws > 1:
+        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+    tot, t_sid, t_gn = [float(x) for x in tt.cpu()]
+    ms = tot / args.steps
+    value = rays_local * ws / (ms * 1e-3)
+
+    # ---- end to end through the reference-facing entry points, host buffers in and out
+    e2e = None
+    if not args.no_e2e:
+        from dexct import config as cfg
+        cfg.dtype = args.dtype
+        k_e2e = max(3, min(args.steps, 10))
+
+        def e2e_step():
+            FP.clear_cache()                                            # the phantom is uploaded and re-laid-out every step
+            (raw_lo, log_lo), (raw_hi, log_hi) = FP.get_sinos(ct, ph, [lo, hi])
+            m1, m2 = matdecomp.get_basismat_sinos(ct, raw_lo, raw_hi, lo, hi, n_iters=GN_ITERS, mask_thresh=MASK_THRESH)
+            return raw_lo, m1
+
+        for _ in range(2):
+            e2e_step()
+        barrier()
+        t0 = time.perf_counter()
+        for _ in range(k_e2e):
+            e2e_step()
+        barrier()
+        dt = torch.tensor([(time.perf_counter() - t0) / k_e2e], dtype=torch.float64, device=dev)
+        if ws > 1:
+            dist.all_reduce(dt, op=dist.ReduceOp.MAX)
+        esz = 4 if args.dtype == 'f32' else 8
+        # up: labels + tables + the two count sinograms handed to get_basismat_sinos; down: 2 x (raw, log) + 2 basis sinograms
+        h2d = ph.M.nbytes + (mu.numel() + W.numel() + i0.numel() + mus.numel()) * esz + 2 * n_views * N_CH * esz
+        d2h = 6 * n_views * N_CH * esz
+        e2e = {'value': n_views * N_CH / float(dt[0]), 'unit': UNIT, 'h2d_bytes_per_step': int(h2d), 'd2h_bytes_per_step': int(d2h),
+               'ms_per_step': 1e3 * float(dt[0]), 'steps': k_e2e,
+               'api': 'xtomosim.forward_project.get_sinos + matdecomp.get_basismat_sinos (numpy in/out, cache cleared every step)'}
+
+    if rank == 0:
+        peaks = {}
+        try:
+            peaks = json.load(open(os.path.join(ROOT, 'MEASURED_PEAKS.json')))
+        except Exception:                                                 # noqa: BLE001
+            pass
+        hbm = float(peaks.get('hbm_gbs', 6650.0))
+        seg = count_segments(pj, v0, min(nv, 100)) / (min(nv, 100) * N_CH)
+        bytes_per_ray = seg * 1 + 2 * (4 if args.dtype == 'f32' else 8)
+        ach = rays_local * bytes_per_ray / (t_sid * 1e-3) / 1e9
+        sm_mhz = (clocks or {}).get('sm_mhz') or peaks.get('sm_max_mhz', 1965.0)
+        fma_peak = 148 * 128 * 2 * sm_mhz * 1e6 / 1e12                    # TFLOP/s fp32 at the clock seen during the run
+        nE = int(i0.shape[1])
+        gn_flops = 28.0 * nE * GN_ITERS * rays_local
+        line = {
+            'metric': METRIC, 'value': value, 'unit': UNIT, 'n_gpus': ws, 'steps': args.steps, 'warmup': max(args.warmup, 3),
+            'ms_per_step': ms, 'higher_is_better': True, 'scaling': 'weak', 'vs_baseline': None, 'dtype': args.dtype,
+            'data': 'synthetic',
+            'config': {'workload': WORKLOAD, 'views_total': n_views, 'rays_per_step': rays_local * ws, 'gn_iters': GN_ITERS,
+                       'l2': 'flushed between timed steps (256 MiB write)', 'parallelism': f'view-sharded x{ws}',
+                       'collective': 'all-gather of counts/logs/basis sinograms inside the step' if ws > 1 else 'none'},
+            'kernel_ms': {'siddon_poly': t_sid, 'gn': t_gn},
+            'siddon_rays_per_s': rays_local * ws / (t_sid * 1e-3), 'gn_pixels_per_s': rays_local * ws / (t_gn * 1e-3),
+            'roofline': {'bound': 'hbm', 'achieved': ach, 'peak': hbm, 'unit': 'GB/s', 'frac': ach / hbm, 'traffic': None,
+                         'kernel': 'siddon_poly_kernel', 'bytes_per_ray': bytes_per_ray, 'segments_per_ray': seg,
+                         'peak_source': 'MEASURED_PEAKS.json hbm_gbs' if peaks else 'fallback'},
+            'roofline_gn': {'bound': 'fp32_fma', 'achieved': gn_flops / (t_gn * 1e-3) / 1e12, 'peak': fma_peak, 'unit': 'TFLOP/s',
+                            'frac': gn_flops / (t_gn * 1e-3) / 1e12 / fma_peak, 'kernel': 'gn_kernel',
+                            'flop_per_pixel': 28.0 * nE * GN_ITERS},
+            'gpu_launches': 3 * args.steps, 'clocks': clocks,
+        }
+        if e2e:
+            line['e2e'] = e2e
+        if ws == 1 and not args.no_cpu_baseline:
+            arm = CpuArm(args.cpu_views or auto_cpu_views())
+            arm.step()
+            t0 = time.perf_counter()
+            arm.step()
+            dtc = time.perf_counter() - t0
+            arm.close()
+            line['cpu_baseline'] = arm.describe(arm.n_views * N_CH / dtc)
+        print(json.dumps(line), flush=True)
+    if ws > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+def main():
+    args = parse()
+    if args.impl == 'reference':
+        run_reference(args)
+    else:
+        run_b200(args)
+
+
+if __name__ == '__main__':
+    main()

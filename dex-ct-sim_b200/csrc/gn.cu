@@ -169,9 +169,20 @@ __global__ void __launch_bounds__(256) gn_kernel(const R *__restrict__ g, const 
     }
 }
 
+template <typename R>
+static int launch_max(const void *g, long long P, void *scratch, cudaStream_t st)
+{
+    DEXCT_CUDA_OK(cudaMemsetAsync(scratch, 0x80, 8, st));      // key of a very negative value for both key widths
+    if (P > 0) {
+        gn_max_kernel<R><<<(unsigned)min((long long)sm_count() * 4, (P + 255) / 256), 256, 0, st>>>((const R *)g, P, (R *)scratch);
+        DEXCT_CUDA_OK(cudaGetLastError());
+    }
+    return DEXCT_OK;
+}
+
 template <typename R, int PX>
 static int launch_gn(const void *g, const void *i0, const void *mus, int nE, long long P, int n_iters, double mask_thresh,
-                     void *a_out, void *scratch, cudaStream_t st)
+                     void *a_out, void *scratch, bool have_max, cudaStream_t st)
 {
     const int block = 256;
     const size_t smem = sizeof(R) * (size_t)nE * GN_ROW;
@@ -187,10 +198,8 @@ static int launch_gn(const void *g, const void *i0, const void *mus, int nE, lon
     const long long want = (P + (long long)block * PX - 1) / ((long long)block * PX);
     long long grid = (long long)sm_count() * per_sm;          // one resident wave; the grid-stride loop does the rest
     if (grid > want) grid = want;
-    if (mask_thresh > 0) {
-        DEXCT_CUDA_OK(cudaMemsetAsync(scratch, 0x80, 8, st));  // key of a very negative value for both key widths
-        gn_max_kernel<R><<<(unsigned)min((long long)sm_count() * 4, (P + 255) / 256), 256, 0, st>>>((const R *)g, P, (R *)scratch);
-        DEXCT_CUDA_OK(cudaGetLastError());
+    if (mask_thresh > 0 && !have_max) {
+        if (int e = launch_max<R>(g, P, scratch, st)) return e;
     }
     kern<<<(unsigned)grid, block, smem, st>>>((const R *)g, (const R *)i0, (const R *)mus, nE, P, n_iters, (R)mask_thresh,
                                              scratch, (R *)a_out);
@@ -202,8 +211,18 @@ static int launch_gn(const void *g, const void *i0, const void *mus, int nE, lon
 
 using namespace dexct;
 
+extern "C" int dexct_gn_air_max(const void *g1, int64_t P, void *scratch, int32_t dtype, void *stream)
+{
+    if (int e = check_device()) return e;
+    DEXCT_REQUIRE(scratch && (g1 || P == 0) && P >= 0, "g1 and scratch must be non-null, P >= 0");
+    DEXCT_REQUIRE(dtype == DEXCT_F32 || dtype == DEXCT_F64, "dtype must be DEXCT_F32 or DEXCT_F64");
+    cudaStream_t st = (cudaStream_t)stream;
+    return dtype == DEXCT_F32 ? launch_max<float>(g1, P, scratch, st) : launch_max<double>(g1, P, scratch, st);
+}
+
 extern "C" int dexct_gn_decompose(const void *g, const void *i0, const void *mus, int32_t nE, int64_t P, int32_t n_iters,
-                                  double mask_thresh, void *a_out, void *scratch, int32_t dtype, void *stream)
+                                  double mask_thresh, void *a_out, void *scratch, int32_t scratch_has_max,
+                                  int32_t dtype, void *stream)
 {
     if (int e = check_device()) return e;
     DEXCT_REQUIRE(g && i0 && mus && a_out, "g, i0, mus and a_out must be non-null");
@@ -212,6 +231,7 @@ extern "C" int dexct_gn_decompose(const void *g, const void *i0, const void *mus
     DEXCT_REQUIRE(dtype == DEXCT_F32 || dtype == DEXCT_F64, "dtype must be DEXCT_F32 or DEXCT_F64");
     if (P == 0) return DEXCT_OK;
     cudaStream_t st = (cudaStream_t)stream;
-    if (dtype == DEXCT_F32) return launch_gn<float, 2>(g, i0, mus, nE, P, n_iters, mask_thresh, a_out, scratch, st);
-    return launch_gn<double, 1>(g, i0, mus, nE, P, n_iters, mask_thresh, a_out, scratch, st);
+    const bool have = scratch_has_max != 0;
+    if (dtype == DEXCT_F32) return launch_gn<float, 2>(g, i0, mus, nE, P, n_iters, mask_thresh, a_out, scratch, have, st);
+    return launch_gn<double, 1>(g, i0, mus, nE, P, n_iters, mask_thresh, a_out, scratch, have, st);
 }

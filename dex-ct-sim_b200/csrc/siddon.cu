@@ -315,7 +315,7 @@ __global__ void siddon_trace_kernel(SiddonParams P, const int64_t *__restrict__ 
             for (int q = 0; q < sink.n; ++q) {
                 const int slot = s.fwd ? q : sink.n - 1 - q;
                 if (!(sink.w[slot] > (R)0) || sink.vox[slot] < 0) continue;
-                if (n < max_seg) {
+                if (vox && n < max_seg) {
                     const size_t o = (size_t)t * max_seg + n;
                     vox[o] = sink.vox[slot];
                     lab[o] = (uint8_t)sink.lab[slot];
@@ -499,8 +499,9 @@ extern "C" int dexct_siddon_trace(const DexctScan *scan, const DexctVolume *vol,
     if (int e = check_device()) return e;
     SiddonParams P;
     if (int e = make_params(scan, vol, workspace, P)) return e;
-    DEXCT_REQUIRE(ray_ids && vox && lab && len && n_seg, "trace buffers must be non-null");
-    DEXCT_REQUIRE(n_rays >= 0 && max_seg > 0, "n_rays >= 0 and max_seg > 0 required");
+    DEXCT_REQUIRE(ray_ids && n_seg, "ray_ids and n_seg must be non-null");
+    DEXCT_REQUIRE((vox && lab && len) || (!vox && !lab && !len), "vox, lab and len must be all given or all NULL");
+    DEXCT_REQUIRE(n_rays >= 0 && (max_seg > 0 || !vox), "n_rays >= 0 and max_seg > 0 required");
     DEXCT_REQUIRE(dtype == DEXCT_F32 || dtype == DEXCT_F64, "dtype must be DEXCT_F32 or DEXCT_F64");
     if (n_rays == 0) return DEXCT_OK;
     cudaStream_t st = (cudaStream_t)stream;

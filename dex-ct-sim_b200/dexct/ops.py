@@ -134,6 +134,24 @@ class Projector:
         return [(vox_h[t, :ns_h[t]], lab_h[t, :ns_h[t]], ln_h[t, :ns_h[t]]) for t in range(n)]
 
 
+def count_segments(pj, view_begin=0, view_count=None, chunk=1 << 22):
+    """Total number of voxel segments (pieces of positive length) of the rays of a view range -- the unit of the
+    bytes-per-ray roofline."""
+    s = pj.scan
+    view_count = s.n_views - view_begin if view_count is None else view_count
+    lo = view_begin * pj.rays_per_view
+    hi = lo + view_count * pj.rays_per_view
+    total = 0
+    with torch.cuda.device(pj.device):
+        for a in range(lo, hi, chunk):
+            ids = torch.arange(a, min(a + chunk, hi), dtype=torch.int64, device=pj.device)
+            ns = torch.empty(ids.numel(), dtype=torch.int32, device=pj.device)
+            N.check(N.lib().dexct_siddon_trace(C.byref(s), C.byref(pj.vol), N.ptr(pj.workspace), N.ptr(ids), ids.numel(), 0,
+                                               None, None, None, N.ptr(ns), F32, N.stream_ptr()))
+            total += int(ns.sum(dtype=torch.int64))
+    return total
+
+
 def poly_detect(L, mu, W, dtype=F32, want_log=True):
     """counts, logs [nSpec, *L.shape[:-1]] from stored lengths L [..., K] (device tensor)."""
     N.require_device()
@@ -154,8 +172,12 @@ def poly_detect(L, mu, W, dtype=F32, want_log=True):
     return counts, logs
 
 
-def gn_decompose(g, i0, mus, n_iters, mask_thresh=0.0, dtype=F32, out=None):
-    """g [2, ...] counts (device tensor or array), i0 [2, nE], mus [2, nE] -> a [..., 2] device tensor."""
+def gn_decompose(g, i0, mus, n_iters, mask_thresh=0.0, dtype=F32, out=None, reduce_max_over_ranks=False):
+    """g [2, ...] counts (device tensor or array), i0 [2, nE], mus [2, nE] -> a [..., 2] device tensor.
+
+    ``reduce_max_over_ranks``: the pixels are one shard of a larger sinogram; the air threshold then uses the maximum of the
+    first measurement over ALL ranks (one 8-byte integer MAX all-reduce), as the unsharded reference does
+    (matdecomp.py:196)."""
     N.require_device()
     code = dtype_code(dtype)
     td = _TORCH_DTYPE[code]
@@ -169,8 +191,15 @@ def gn_decompose(g, i0, mus, n_iters, mask_thresh=0.0, dtype=F32, out=None):
     nE = i0.shape[1]
     if out is None:
         out = torch.empty(tuple(g.shape[1:]) + (2,), dtype=td, device=dev)
-    scratch = torch.empty(16, dtype=torch.uint8, device=dev)
+    scratch = torch.empty(2, dtype=torch.int64, device=dev)
+    have_max = 0
     with torch.cuda.device(dev):
+        if reduce_max_over_ranks and mask_thresh > 0:
+            import torch.distributed as dist
+            N.check(N.lib().dexct_gn_air_max(N.ptr(g), P, N.ptr(scratch), code, N.stream_ptr()))
+            key = scratch[:1] if code == F64 else scratch.view(torch.int32)[:1]
+            dist.all_reduce(key, op=dist.ReduceOp.MAX)
+            have_max = 1
         N.check(N.lib().dexct_gn_decompose(N.ptr(g), N.ptr(i0), N.ptr(mus), nE, P, int(n_iters), float(mask_thresh),
-                                           N.ptr(out), N.ptr(scratch), code, N.stream_ptr()))
+                                           N.ptr(out), N.ptr(scratch), have_max, code, N.stream_ptr()))
     return out

@@ -41,7 +41,8 @@ def spectral_tables(ct, spec1, spec2):
     return ee, i0, mus
 
 
-def optimize_sino(Sino_gg, ee, i0, mus, n_iters, verbose=True, dtype=None, mask_thresh=0.0, to_host=True):
+def optimize_sino(Sino_gg, ee, i0, mus, n_iters, verbose=True, dtype=None, mask_thresh=0.0, to_host=True,
+                  reduce_max_over_ranks=False):
     """GPU Newton iterations; signature of matdecomp.py:20 (``ee`` is unused there too).
 
     Sino_gg [2, nViews, nBins] counts; i0 [2, nBins, nE] (all bins identical, matdecomp.py:151) or [2, nE];
@@ -58,7 +59,8 @@ def optimize_sino(Sino_gg, ee, i0, mus, n_iters, verbose=True, dtype=None, mask_
     mus = np.asarray(mus, dtype=np.float64)
     if mus.shape[0] != 2:
         raise NotImplementedError('two basis materials only (matdecomp.py:155)')
-    out = gn_decompose(Sino_gg, i0, mus, n_iters, mask_thresh=mask_thresh, dtype=code)
+    out = gn_decompose(Sino_gg, i0, mus, n_iters, mask_thresh=mask_thresh, dtype=code,
+                       reduce_max_over_ranks=reduce_max_over_ranks)
     return out.detach().cpu().numpy().astype(np.float64) if to_host else out
 
 
@@ -79,12 +81,9 @@ def do_matdecomp_gn(ct, sino1, sino2, spec1, spec2, n_iters, mask_thresh=0.0, to
     if ws > 1:
         n_views = g.shape[1]
         v0, nv = dist.shard_range(n_views, rank, ws)
-        # the air threshold needs the global maximum: every rank holds the full input here, so take it locally
-        gmax = float(g[0].max())
-        local = optimize_sino(g[:, v0:v0 + nv], ee, i0, mus, n_iters, mask_thresh=0.0, to_host=False)
-        if mask_thresh > 0:
-            g1 = torch.as_tensor(g[0, v0:v0 + nv], device=local.device)
-            local[g1 >= mask_thresh * gmax] = 0
+        # the air threshold needs the maximum over the whole sinogram: one integer MAX all-reduce between the shards
+        local = optimize_sino(g[:, v0:v0 + nv], ee, i0, mus, n_iters, mask_thresh=mask_thresh, to_host=False,
+                              reduce_max_over_ranks=True)
         full = dist.all_gather_views(local, n_views, dim=0)
         return full.detach().cpu().numpy().astype(np.float64) if to_host else full
     return optimize_sino(g, ee, i0, mus, n_iters, mask_thresh=mask_thresh, to_host=to_host)

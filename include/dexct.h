@@ -107,7 +107,9 @@ int dexct_poly_detect(const void *L, int64_t n_rays, const void *mu_KxE, int32_t
 
 /* Debug: ordered voxel crossing sequence of selected rays.  ray_ids [n_rays] = (view*n_rows + row)*n_ch + ch.
  * For ray t the first min(n_seg[t], max_seg) entries of vox/lab/len rows t are valid: linear voxel index
- * (k*ny + j)*nx + i, its label, and the intersection length [cm] (float or double per dtype).               */
+ * (k*ny + j)*nx + i, its label, and the intersection length [cm] (float or double per dtype).
+ * vox, lab and len may all be NULL to obtain only the segment counts n_seg (the unit of the bytes-per-ray
+ * roofline).                                                                                                */
 int dexct_siddon_trace(const DexctScan *scan, const DexctVolume *vol, const void *workspace,
                        const int64_t *ray_ids, int32_t n_rays, int32_t max_seg,
                        int64_t *vox, uint8_t *lab, void *len, int32_t *n_seg, int32_t dtype, void *stream);
@@ -120,10 +122,16 @@ int dexct_siddon_trace(const DexctScan *scan, const DexctVolume *vol, const void
  *   mus_2xE [2][nE] basis attenuation;  a_out [P][2].
  * mask_thresh > 0 additionally zeroes both outputs of pixels with g[0][p] >= mask_thresh * max_p g[0][p]
  * (get_basismat_sinos, matdecomp.py:195-205); scratch = >= 16 bytes of device memory for that maximum
- * (may be NULL when mask_thresh <= 0).                                                                        */
+ * (may be NULL when mask_thresh <= 0).  scratch_has_max != 0: scratch already holds the maximum as written by
+ * dexct_gn_air_max (pixel-sharded runs reduce it over ranks first); 0: it is computed here from g[0][0..P).   */
 int dexct_gn_decompose(const void *g_2xP, const void *i0_2xE, const void *mus_2xE, int32_t nE, int64_t P,
                        int32_t n_iters, double mask_thresh, void *a_out_Px2, void *scratch,
-                       int32_t dtype, void *stream);
+                       int32_t scratch_has_max, int32_t dtype, void *stream);
+
+/* max_p g1[p] (the first measurement, matdecomp.py:196) into scratch[0..8) as an order-preserving integer key:
+ * int32 (DEXCT_F32) or int64 (DEXCT_F64), so that ranks holding different pixels can combine their values with an
+ * integer MAX all-reduce before calling dexct_gn_decompose(..., scratch_has_max = 1).                          */
+int dexct_gn_air_max(const void *g1, int64_t P, void *scratch, int32_t dtype, void *stream);
 
 /* ---- fan-beam filtered back-projection: replaces get_recon (main.py:134,168) ------------------------------ */
 

@@ -51,7 +51,7 @@ def test_no_device_means_loud_failure():
         pytest.skip('this check is for the CPU-only machine')
     L = N.lib()
     assert L.dexct_device_count() == 0
-    rc = L.dexct_gn_decompose(None, None, None, 1, 1, 1, 0.0, None, None, 0, None)
+    rc = L.dexct_gn_decompose(None, None, None, 1, 1, 1, 0.0, None, None, 0, 0, None)
     assert rc == -3 and b'no CPU fallback' in L.dexct_last_error()
     with pytest.raises(N.DexctError):
         N.require_device()

@@ -1,0 +1,234 @@
+"""Parity of the CUDA forward projector (csrc/siddon.cu, through the C ABI) with the oracle.
+
+* voxel-index / material-id SEQUENCES: bit-exact against oracle section (B) (the operation-for-operation CPU twin), which
+  tests/test_oracle_siddon.py ties to Siddon 1985 (section A);
+* per-material lengths, counts, log sinograms: against Siddon 1985 in float64 -- 1e-10 scale-relative in f64 mode,
+  1e-5 in f32 mode (the tolerances of BASELINE.json's north_star);
+* full-size properties at config C2 and a slab of C4: chord-length conservation, linearity, closed forms.
+"""
+import ctypes as C
+
+import numpy as np
+import pytest
+import torch
+
+import oracle
+from conftest import scale_rel_err
+from dexct import _native as N
+from dexct import synthetic as S
+from dexct.ops import F32, F64, Projector, make_scan, poly_detect
+
+pytestmark = pytest.mark.gpu
+
+FAN = 0.8230337
+TOL = {F32: 1e-5, F64: 1e-10}
+
+
+def _labels(n, nz, K, seed=3):
+    r = np.random.default_rng(seed)
+    lab = r.integers(0, K, (nz, n, n)).astype(np.uint8)
+    lab[:, n // 4:n // 2, n // 3:2 * n // 3] = min(2, K - 1)
+    return lab
+
+
+def _pair(n=96, n_ch=120, n_views=36, n_rows=1, nz=1, K=4, fov=51.2, h_iso=0.4, beta0=0.0, seed=3, fan=FAN):
+    """(Projector, oracle.Scan built from the DEVICE's own angle tables)."""
+    lab = _labels(n, nz, K, seed)
+    vox = fov / n
+    voxel = (vox, vox, vox if nz > 1 else 0.1)
+    scan = make_scan(n_views, n_ch, fan, 60.0, 100.0, n_rows=n_rows, h_iso=h_iso, beta0=beta0)
+    pj = Projector(scan, lab, voxel)
+    sc = oracle.Scan(lab, voxel, 60.0, 100.0, pj.tables_host())
+    return pj, sc
+
+
+def _tables(K, nE=24, nS=2, seed=5):
+    r = np.random.default_rng(seed)
+    E = np.linspace(30, 120, nE)
+    mu = np.stack([(0.02 + 0.08 * m) * (0.6 + (60.0 / E) ** (1.0 + 0.2 * m)) for m in range(K)])
+    mu[0] = 0.0002                                    # air
+    W = r.uniform(0.2, 1.0, (nS, nE)) * 1e4
+    return mu, W
+
+
+def test_device_tables_are_the_stated_conventions():
+    pj, _ = _pair(n_rows=3, nz=4, beta0=0.3)
+    t = pj.tables_host()
+    want = oracle.fan_tables(120, 36, FAN, beta0=0.3, N_rows=3, h_iso=0.4)
+    for k in want:
+        assert np.allclose(t[k], want[k], rtol=0, atol=2e-15), k
+
+
+@pytest.mark.parametrize('dtype', [F32, F64])
+@pytest.mark.parametrize('nz,n_rows', [(1, 1), (16, 6)])
+def test_voxel_sequences_bit_exact(dtype, nz, n_rows):
+    pj, sc = _pair(nz=nz, n_rows=n_rows)
+    r = np.random.default_rng(11)
+    n_all = sc.n_views * sc.n_rows * sc.n_ch
+    ids = np.unique(np.concatenate([r.integers(0, n_all, 1500),
+                                    # central and edge channels of the axis-parallel / diagonal views
+                                    [((v * sc.n_rows + row) * sc.n_ch + c) for v in (0, 9, 18, 27, 4, 5)
+                                     for row in (0, sc.n_rows - 1) for c in (0, 59, 60, 119)]]))
+    got = pj.trace(ids, max_seg=1024, dtype=dtype)
+    n_seg = 0
+    for rid, (vox, lab, ln) in zip(ids, got):
+        c = int(rid % sc.n_ch)
+        row = int((rid // sc.n_ch) % sc.n_rows)
+        v = int(rid // (sc.n_ch * sc.n_rows))
+        w_vox, w_lab, w_len = sc.slab_trace(v, row, c, dtype == F64)
+        assert np.array_equal(vox, w_vox), (rid, v, row, c)
+        assert np.array_equal(lab, w_lab), (rid, v, row, c)
+        assert np.array_equal(ln.astype(np.float64), w_len), (rid, v, row, c)
+        n_seg += len(vox)
+    assert n_seg > 50 * len(ids)
+
+
+def test_degenerate_rays_bit_exact():
+    """Rays along grid planes, through voxel corners, axis-parallel; even and odd grids; source inside the volume."""
+    for n, n_ch, fov, beta0 in ((64, 9, 64.0, 0.0), (65, 9, 65.0, 0.0), (64, 8, 64.0, np.pi / 4), (64, 9, 200.0, 0.0)):
+        lab = _labels(n, 1, 4)
+        vox = fov / n
+        # 8 views -> beta = k pi/4 (+beta0): the central channel of an odd detector is exactly axis-parallel/diagonal
+        scan = make_scan(8, n_ch, 0.4, 60.0, 100.0, beta0=beta0)
+        pj = Projector(scan, lab, (vox, vox, 0.1))
+        sc = oracle.Scan(lab, (vox, vox, 0.1), 60.0, 100.0, pj.tables_host())
+        ids = np.arange(8 * n_ch)
+        for dtype in (F32, F64):
+            for rid, (vx, lb, ln) in zip(ids, pj.trace(ids, max_seg=512, dtype=dtype)):
+                w = sc.slab_trace(int(rid // n_ch), 0, int(rid % n_ch), dtype == F64)
+                assert np.array_equal(vx, w[0]) and np.array_equal(lb, w[1]) and np.array_equal(ln.astype(np.float64), w[2])
+        # and the float64 sequences are Siddon's on these rays up to zero-length corner touches: lengths agree
+        L = sc.slab_lengths(4, True)
+        Lc, _ = sc.classic_lengths(4)
+        assert np.max(np.abs(L - Lc)) < 1e-10
+
+
+@pytest.mark.parametrize('dtype', [F32, F64])
+@pytest.mark.parametrize('nz,n_rows,K', [(1, 1, 4), (16, 6, 4), (1, 1, 1), (1, 1, 7), (12, 3, 13), (1, 1, 20)])
+def test_lengths_counts_logs_vs_siddon1985(dtype, nz, n_rows, K):
+    pj, sc = _pair(nz=nz, n_rows=n_rows, K=K)
+    mu, W = _tables(K)
+    counts, logs, L = pj.project(mu, W, dtype=dtype, want_log=True, want_L=True)
+    torch.cuda.synchronize()
+    L_ref, seg = sc.classic_lengths(K)
+    assert seg > 0
+    assert scale_rel_err(L.cpu().numpy(), L_ref) < TOL[dtype]
+    c_ref, l_ref, _ = sc.project_poly(mu, W)
+    assert scale_rel_err(counts.cpu().numpy(), c_ref) < TOL[dtype]
+    # the log sinogram is O(1..10): absolute error of tol x its scale
+    assert scale_rel_err(logs.cpu().numpy(), l_ref) < (1e-9 if dtype == F64 else 3e-5)
+    # detection from the stored lengths reproduces the fused epilogue
+    c2, l2 = poly_detect(L, mu, W, dtype=dtype)
+    assert scale_rel_err(c2.cpu().numpy(), counts.cpu().numpy()) < (1e-14 if dtype == F64 else 1e-6)
+
+
+def test_view_ranges_and_spectrum_counts():
+    pj, sc = _pair()
+    mu, W4 = _tables(4, nS=4)
+    full, _, _ = pj.project(mu, W4, dtype=F64, want_log=False)
+    assert full.shape == (4, 36, 1, 120)
+    a, _, _ = pj.project(mu, W4, view_begin=0, view_count=17, dtype=F64, want_log=False)
+    b, _, _ = pj.project(mu, W4, view_begin=17, view_count=19, dtype=F64, want_log=False)
+    assert torch.equal(torch.cat([a, b], dim=1), full)               # view sharding is exact
+    one, _, _ = pj.project(mu, W4[2:3], dtype=F64, want_log=False)
+    assert torch.equal(one[0], full[2])
+    empty, _, _ = pj.project(mu, W4, view_begin=5, view_count=0, dtype=F64, want_log=False)
+    assert empty.shape == (4, 0, 1, 120)
+
+
+def test_rays_that_miss_see_air_exactly():
+    # a 6.4 cm object under a 47 degree fan: the outer channels pass beside it
+    pj, sc = _pair(n=64, fov=6.4)
+    mu, W = _tables(4)
+    counts, logs, L = pj.project(mu, W, dtype=F32, want_L=True)
+    Lh = L.cpu().numpy()
+    miss = Lh.sum(-1) == 0
+    assert miss.any() and (~miss).any()
+    air = torch.as_tensor(W, dtype=torch.float32).cuda().sum(1)
+    c = counts.cpu().numpy()
+    assert np.all(np.abs(c[:, miss] / air.cpu().numpy()[:, None] - 1) < 1e-6)
+    assert np.all(np.abs(logs.cpu().numpy()[:, miss]) < 1e-6)
+    L_ref, _ = sc.classic_lengths(4)
+    assert np.array_equal(L_ref.sum(-1) == 0, miss)
+
+
+def test_argument_errors_are_reported():
+    pj, _ = _pair()
+    mu, W = _tables(4)
+    with pytest.raises(N.DexctError, match='view range'):
+        pj.project(mu, W, view_begin=30, view_count=10)
+    with pytest.raises(N.DexctError, match='nSpec'):
+        pj.project(mu, np.tile(W, (3, 1)))
+    with pytest.raises(ValueError):
+        pj.project(mu, W[:, :-1])
+    big = np.ones((200, 300))
+    with pytest.raises(N.DexctError, match='shared memory'):
+        pj.project(big, np.ones((1, 300)), dtype=F64)
+    L = N.lib()
+    assert L.dexct_siddon_poly(None, None, None, 0, 0, None, 1, 1, None, 1, None, None, None, 0, None) == -1
+
+
+# ---- full-size properties ---------------------------------------------------------------------------------------
+
+def _box_chords(ct, half):
+    """Analytic chord of every (view, channel) ray of a 2-D fan with the square [-half, half]^2 (float64 numpy)."""
+    b = ct.betas[:, None]
+    g = ct.gammas[None, :]
+    S = np.stack([ct.SID * np.cos(b) + 0 * g, ct.SID * np.sin(b) + 0 * g])
+    D = np.stack([-ct.SDD * np.cos(b + g), -ct.SDD * np.sin(b + g)])
+    with np.errstate(divide='ignore', invalid='ignore'):
+        t1, t2 = (-half - S) / D, (half - S) / D
+    lo = np.minimum(t1, t2).max(0).clip(0, 1)
+    hi = np.maximum(t1, t2).min(0).clip(0, 1)
+    return np.maximum(hi - lo, 0) * ct.SDD
+
+
+@pytest.mark.parametrize('dtype', [F32, F64])
+def test_c2_full_size_chord_conservation_and_linearity(dtype):
+    """Config C2 (512x512, 900 ch x 1000 views, 120 bins): sum_m L_m is the chord of the ray with the phantom's bounding
+    square; doubling W doubles the counts exactly; a one-material phantom gives the closed-form spectrum integral."""
+    ct, ph, lo, hi = S.make_config('C2')
+    from xtomosim.forward_project import spectral_weights
+    scan = make_scan(ct.N_proj, ct.N_channels, ct.gamma_fan, ct.SID, ct.SDD, rotation=ct.rotation)
+    pj = Projector(scan, ph.M, (ph.dx, ph.dy, ph.dz))
+    mu = ph.mu_table(lo.E)
+    W = np.stack([spectral_weights(ct, lo), spectral_weights(ct, hi)])
+    counts, logs, L = pj.project(mu, W, dtype=dtype, want_L=True)
+    chord = _box_chords(ct, 25.6)
+    Ls = L.sum(-1)[:, 0].cpu().numpy()
+    assert np.max(np.abs(Ls - chord)) < (2e-4 if dtype == F32 else 1e-9)      # chords are up to 72 cm
+    c2, _, _ = pj.project(mu, 2.0 * W, dtype=dtype, want_log=False)
+    assert torch.equal(c2, 2.0 * counts)
+    # checksum against the oracle on a view subset (the whole scan takes the CPU minutes)
+    tabs = pj.tables_host()
+    sub = {k: (v[::125] if k.endswith('beta') else v) for k, v in tabs.items()}
+    sc = oracle.Scan(ph.M, (ph.dx, ph.dy, ph.dz), ct.SID, ct.SDD, sub)
+    c_ref, l_ref, seg = sc.project_poly(mu, W)
+    assert 500 < seg / (8 * 900) < 700
+    assert scale_rel_err(counts[:, ::125].cpu().numpy(), c_ref) < TOL[dtype]
+    # homogeneous phantom: closed form
+    uni = np.ones_like(ph.M)
+    pj1 = Projector(scan, uni, (ph.dx, ph.dy, ph.dz))
+    c1, _, _ = pj1.project(mu, W, dtype=dtype, want_log=False)
+    want = np.einsum('se,vce->svc', W, np.exp(-chord[..., None] * mu[1]))
+    assert scale_rel_err(c1[:, :, 0].cpu().numpy(), want) < (3e-5 if dtype == F32 else 1e-10)
+
+
+def test_c4_slab_3d_parity_and_chords():
+    """Config C4 geometry (512^3, 64 rows x 900 ch) on 6 of its 1200 views: lengths vs Siddon 1985 on a ray subset,
+    chord conservation on all rays."""
+    ct, ph, lo, hi = S.make_config('C4', n_views=6, nz=128)
+    from xtomosim.forward_project import spectral_weights
+    scan = make_scan(ct.N_proj, ct.N_channels, ct.gamma_fan, ct.SID, ct.SDD, n_rows=ct.N_rows, h_iso=ct.h_iso,
+                     rotation=ct.rotation)
+    pj = Projector(scan, ph.M, (ph.dx, ph.dy, ph.dz))
+    mu = ph.mu_table(lo.E)
+    W = np.stack([spectral_weights(ct, lo), spectral_weights(ct, hi)])
+    tabs = pj.tables_host()
+    sc = oracle.Scan(ph.M, (ph.dx, ph.dy, ph.dz), ct.SID, ct.SDD, tabs)
+    for dtype in (F32, F64):
+        counts, logs, L = pj.project(mu, W, dtype=dtype, want_L=True)
+        L_ref, seg = sc.classic_lengths(S.K, v0=2, nv=1)
+        assert scale_rel_err(L[2:3].cpu().numpy(), L_ref) < TOL[dtype]
+        c_ref, _ = oracle.poly_detect(L_ref, mu, W, want_log=False)
+        assert scale_rel_err(counts[:, 2].reshape(2, -1).cpu().numpy(), c_ref) < TOL[dtype]
