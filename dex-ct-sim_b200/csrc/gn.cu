@@ -225,8 +225,8 @@ extern "C" int dexct_gn_decompose(const void *g, const void *i0, const void *mus
                                   int32_t dtype, void *stream)
 {
     if (int e = check_device()) return e;
-    DEXCT_REQUIRE(g && i0 && mus && a_out, "g, i0, mus and a_out must be non-null");
     DEXCT_REQUIRE(nE >= 1 && P >= 0 && n_iters >= 0, "need nE >= 1, P >= 0, n_iters >= 0");
+    DEXCT_REQUIRE(P == 0 || (g && i0 && mus && a_out), "g, i0, mus and a_out must be non-null");
     DEXCT_REQUIRE(mask_thresh <= 0 || scratch, "scratch must be non-null when mask_thresh > 0");
     DEXCT_REQUIRE(dtype == DEXCT_F32 || dtype == DEXCT_F64, "dtype must be DEXCT_F32 or DEXCT_F64");
     if (P == 0) return DEXCT_OK;

@@ -161,6 +161,12 @@ template <> __device__ __forceinline__ double neg_log_ratio<double>(double c, do
 // ---------------------------------------------------------------------------------------------------------
 // Production kernel: one ray per thread, adjacent lanes = adjacent channels (so a warp reads adjacent minor-axis
 // voxels of the same column: one or two 128-byte lines per request in the pair layout).
+//
+// Per-material column weights accumulate in shared memory, acc[label][thread].  Whole columns whose two (2-D) or four
+// (3-D) candidate voxels all carry the label of the current RUN never touch it: they bump a register counter that is
+// flushed when the run ends.  Inside homogeneous regions -- most of any anatomy -- a column then costs one FMA, one
+// floor, one 2-byte load and a compare; columns are processed four at a time so that the four loads are in flight
+// together.
 
 template <typename R> struct AccSink {
     R *acc;            // acc[label * BLOCK + tid] lives in shared memory; this points at [tid]
@@ -171,6 +177,89 @@ template <typename R> struct AccSink {
         *p = Rn<R>::add(*p, w);
     }
 };
+
+template <typename R> struct RunState {
+    unsigned curp;     // label of the current run replicated in both bytes of a pair; 0xffffffff = no run
+    R run;             // whole columns in the run (an exact integer)
+};
+
+template <typename R>
+__device__ __forceinline__ void run_flush(RunState<R> &st, const AccSink<R> &sink)
+{
+    if (st.run > (R)0) sink(0, 0, 0, (int)(st.curp & 0xff), st.run);
+    st.run = (R)0;
+}
+
+// A column that is not (known to be) inside the current run: close the run, account the column voxel by voxel, and
+// start a new run if the column itself is homogeneous.
+template <typename R, bool IS3D>
+__device__ __forceinline__ void slow_column(const RayLoop<R> &L, int i, unsigned pr, unsigned pr1, RunState<R> &st,
+                                            AccSink<R> &sink)
+{
+    run_flush(st, sink);
+    slab_column<R, IS3D>(L, i, sink);
+    const unsigned lo = pr & 0xff, homog = lo | (lo << 8);
+    st.curp = (pr == homog && (!IS3D || pr1 == homog)) ? homog : 0xffffffffu;
+}
+
+// Interior columns [ia, ib] (each fully inside the ray's clipped range, so every column weighs exactly 1).
+// q at a column boundary is the same expression fma(m, boundary - i_c, cq) that slab_column evaluates, so the
+// voxel choice is bit-identical to the general routine (and to the CPU twin).
+template <typename R, bool IS3D, bool MPOS, int CH>
+__device__ __forceinline__ void walk_interior(const RayLoop<R> &L, int ia, int ib, RunState<R> &st, AccSink<R> &sink)
+{
+    typedef Rn<R> A;
+    R p = (R)(ia - L.i_c);
+    int jprev = FloorInt<R>::of(A::fma(L.m, p, L.cq));
+    int kprev = IS3D ? FloorInt<R>::of(A::fma(L.mz, p, L.cw)) : 0;
+    const uint16_t *col = L.pairs + (long long)ia * L.pitch;
+    int i = ia;
+    for (; i + CH - 1 <= ib; i += CH) {
+        unsigned pr[CH], pr1[CH];
+#pragma unroll
+        for (int u = 0; u < CH; ++u) {
+            p = A::add(p, (R)1);
+            const int jb = FloorInt<R>::of(A::fma(L.m, p, L.cq));
+            int j = MPOS ? jprev : jb;                                   // = floor(min(q_a, q_b))
+            jprev = jb;
+            j = min(max(j, L.jmin), L.jmax);
+            const uint16_t *e = col + (long long)u * L.pitch + j;
+            if (IS3D) {
+                const int kb = FloorInt<R>::of(A::fma(L.mz, p, L.cw));
+                int k = L.mzpos ? kprev : kb;
+                kprev = kb;
+                k = min(max(k, L.kmin), L.kmax);
+                e += (long long)k * L.plane;
+                pr1[u] = e[L.plane];
+            } else {
+                pr1[u] = 0;
+            }
+            pr[u] = *e;
+        }
+#pragma unroll
+        for (int u = 0; u < CH; ++u) {
+            if (pr[u] == st.curp && (!IS3D || pr1[u] == st.curp)) st.run = A::add(st.run, (R)1);
+            else slow_column<R, IS3D>(L, i + u, pr[u], pr1[u], st, sink);
+        }
+        col += (long long)CH * L.pitch;
+    }
+    if (CH > 1 && i <= ib) walk_interior<R, IS3D, MPOS, 1>(L, i, ib, st, sink);
+}
+
+template <typename R, bool IS3D>
+__device__ __forceinline__ void walk_ray(const RayLoop<R> &L, int i0, int i1, AccSink<R> &sink)
+{
+    RunState<R> st{0xffffffffu, (R)0};
+    slab_column<R, IS3D>(L, i0, sink);                                  // first and last column may be partial
+    if (i1 > i0) {
+        if (i1 - 1 >= i0 + 1) {
+            if (L.mpos) walk_interior<R, IS3D, true, 4>(L, i0 + 1, i1 - 1, st, sink);
+            else        walk_interior<R, IS3D, false, 4>(L, i0 + 1, i1 - 1, st, sink);
+            run_flush(st, sink);
+        }
+        slab_column<R, IS3D>(L, i1, sink);
+    }
+}
 
 template <typename R, bool IS3D, int KT>
 __global__ void __launch_bounds__(128) siddon_poly_kernel(SiddonParams P, int view_begin, long long n_rays, DetectArgs d)
@@ -200,7 +289,7 @@ __global__ void __launch_bounds__(128) siddon_poly_kernel(SiddonParams P, int vi
         RayLoop<R> L;
         L.init(P, s);
         AccSink<R> sink{acc_s + tid, (int)blockDim.x};
-        for (int i = s.i0; i <= s.i1; ++i) slab_column<R, IS3D>(L, i, sink);
+        walk_ray<R, IS3D>(L, s.i0, s.i1, sink);
         seglen = (R)s.seglen;
     }
 
@@ -276,9 +365,10 @@ template <typename R> struct TraceSink {
     R w[3];
     int n;
     bool xmajor;
-    int i, nx, ny, nq, nz;
-    __device__ __forceinline__ void operator()(int slot, int j, int k, int label, R wt)
+    int i, nx, ny, nq, nz, j_c, k_c;
+    __device__ __forceinline__ void operator()(int slot, int jrel, int krel, int label, R wt)
     {
+        const int j = jrel + j_c, k = krel + k_c;
         const bool inside = j >= 0 && j < nq && k >= 0 && k < nz;
         vox[slot] = inside ? (xmajor ? ((int64_t)k * ny + j) * nx + i : ((int64_t)k * ny + i) * nx + j) : -1;
         lab[slot] = label;
@@ -308,6 +398,7 @@ __global__ void siddon_trace_kernel(SiddonParams P, const int64_t *__restrict__ 
         const R seglen = (R)s.seglen;
         TraceSink<R> sink;
         sink.xmajor = s.xmajor; sink.nx = P.vol.nx; sink.ny = P.vol.ny; sink.nq = s.nq; sink.nz = P.vol.nz;
+        sink.j_c = s.j_c; sink.k_c = s.k_c;
         const int step = s.fwd ? 1 : -1;
         for (int i = s.fwd ? s.i0 : s.i1; s.fwd ? (i <= s.i1) : (i >= s.i0); i += step) {
             sink.n = 0; sink.i = i;
@@ -448,11 +539,11 @@ extern "C" int dexct_siddon_poly(const DexctScan *scan, const DexctVolume *vol, 
     if (int e = make_params(scan, vol, workspace, P)) return e;
     DEXCT_REQUIRE(view_begin >= 0 && view_count >= 0 && view_begin + view_count <= scan->n_views,
                   "view range [%d, %d) outside the scan's %d views", view_begin, view_begin + view_count, scan->n_views);
-    DEXCT_REQUIRE(mu && W && counts, "mu, W and counts must be non-null");
     DEXCT_REQUIRE(K >= 1 && K <= 256 && nE >= 1, "need 1 <= K <= 256 and nE >= 1 (K=%d nE=%d)", K, nE);
     DEXCT_REQUIRE(nSpec >= 1 && nSpec <= MAX_SPEC, "nSpec must be in 1..%d", MAX_SPEC);
     DEXCT_REQUIRE(dtype == DEXCT_F32 || dtype == DEXCT_F64, "dtype must be DEXCT_F32 or DEXCT_F64");
     if (view_count == 0) return DEXCT_OK;
+    DEXCT_REQUIRE(mu && W && counts, "mu, W and counts must be non-null");
     const long long n_rays = (long long)view_count * scan->n_rows * scan->n_ch;
     DetectArgs d{mu, W, K, nE, nSpec, counts, logs, L_out};
     cudaStream_t st = (cudaStream_t)stream;
@@ -466,11 +557,11 @@ extern "C" int dexct_poly_detect(const void *L, int64_t n_rays, const void *mu, 
                                  int32_t nSpec, void *counts, void *logs, int32_t dtype, void *stream)
 {
     if (int e = check_device()) return e;
-    DEXCT_REQUIRE(L && mu && W && counts, "L, mu, W and counts must be non-null");
     DEXCT_REQUIRE(K >= 1 && K <= 256 && nE >= 1, "need 1 <= K <= 256 and nE >= 1 (K=%d nE=%d)", K, nE);
     DEXCT_REQUIRE(nSpec >= 1 && nSpec <= MAX_SPEC, "nSpec must be in 1..%d", MAX_SPEC);
     DEXCT_REQUIRE(dtype == DEXCT_F32 || dtype == DEXCT_F64, "dtype must be DEXCT_F32 or DEXCT_F64");
     if (n_rays <= 0) return DEXCT_OK;
+    DEXCT_REQUIRE(L && mu && W && counts, "L, mu, W and counts must be non-null");
     DetectArgs d{mu, W, K, nE, nSpec, counts, logs, nullptr};
     cudaStream_t st = (cudaStream_t)stream;
     const int block = 128;

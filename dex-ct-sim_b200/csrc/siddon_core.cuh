@@ -56,10 +56,16 @@ struct SiddonParams {
 };
 
 // Per-ray constants, computed in double with one rounding per operation (the CPU twin does the same).
+//
+// Coordinates of the column loop are RE-CENTRED PER RAY: the column coordinate is measured from the integer column
+// boundary i_c in the middle of the ray's clipped column range, the minor / z coordinates from the integer voxel
+// indices j_c / k_c the ray occupies there.  The loop therefore evaluates q'(p') = m p' + cq with |p'| <= np/2 and
+// cq in [0,1): |q'| <= 1 + |m| np/2, so its float32 rounding error scales with |m| and the crossing position
+// (q' - integer) / |m| keeps an absolute accuracy of about 2^-24 np columns for EVERY slope, shallow ones included.
 struct RaySetup {
     bool hit, xmajor, fwd;
-    int np, nq, i0, i1, jshift, kshift;
-    double m, mz, cq, cw, ua, ub, halfp, inv_am, inv_amz, seglen;
+    int np, nq, i0, i1, i_c, j_c, k_c;
+    double m, mz, cq, cw, ua, ub, inv_am, inv_amz, seglen;     // ua, ub relative to i_c
 };
 
 #define DEXCT_BIG 1e30
@@ -84,7 +90,6 @@ __device__ __forceinline__ void ray_setup(const SiddonParams &P, int v, int r, i
     const double q0 = D::sub(qS, D::mul(s.m, pS));
     const double w0 = D::sub(wS, D::mul(s.mz, pS));
     const double hp = D::mul(0.5, (double)s.np), hq = D::mul(0.5, (double)s.nq), hw = D::mul(0.5, (double)P.vol.nz);
-    s.halfp = hp;
     const double pe = D::add(pS, gp);
     double pa = pS < pe ? pS : pe, pb = pS < pe ? pe : pS;
     if (pa < -hp) pa = -hp;
@@ -102,18 +107,23 @@ __device__ __forceinline__ void ray_setup(const SiddonParams &P, int v, int r, i
         if (hi < pb) pb = hi;
     } else if (!(w0 >= -hw && w0 < hw)) return;
     if (!(pa < pb)) return;
-    s.ua = D::add(pa, hp);
-    s.ub = D::add(pb, hp);
-    int i0 = (int)floor(s.ua), i1 = (int)ceil(s.ub) - 1;
+    const double ua = D::add(pa, hp), ub = D::add(pb, hp);          // column coordinates in [0, np]
+    int i0 = (int)floor(ua), i1 = (int)ceil(ub) - 1;
     if (i0 < 0) i0 = 0;
     if (i1 > s.np - 1) i1 = s.np - 1;
     if (i1 < i0) return;
     s.i0 = i0; s.i1 = i1;
     s.fwd = gp > 0.0;
-    s.jshift = s.nq / 2;
-    s.kshift = P.vol.nz / 2;
-    s.cq = D::add(q0, D::sub(hq, (double)s.jshift));
-    s.cw = D::add(w0, D::sub(hw, (double)s.kshift));
+    s.i_c = (i0 + i1 + 1) / 2;
+    const double pc = D::sub((double)s.i_c, hp);
+    const double qfull = D::add(D::mul(s.m, pc), D::add(q0, hq));   // minor index coordinate at column boundary i_c
+    const double wfull = D::add(D::mul(s.mz, pc), D::add(w0, hw));
+    const double qfl = floor(qfull), wfl = floor(wfull);
+    s.j_c = (int)qfl; s.k_c = (int)wfl;
+    s.cq = D::sub(qfull, qfl);
+    s.cw = D::sub(wfull, wfl);
+    s.ua = D::sub(ua, (double)s.i_c);
+    s.ub = D::sub(ub, (double)s.i_c);
     const double am = fabs(s.m), amz = fabs(s.mz);
     s.inv_am = am > 0.0 ? D::div(1.0, am) : DEXCT_BIG;
     if (s.inv_am > DEXCT_BIG) s.inv_am = DEXCT_BIG;
@@ -124,43 +134,48 @@ __device__ __forceinline__ void ray_setup(const SiddonParams &P, int v, int r, i
     s.hit = true;
 }
 
+template <typename R> struct FloorInt;
+template <> struct FloorInt<float> { static __device__ __forceinline__ int of(float x) { return __float2int_rd(x); } };
+template <> struct FloorInt<double> { static __device__ __forceinline__ int of(double x) { return __double2int_rd(x); } };
+
 // Loop constants in the compute precision.
 template <typename R> struct RayLoop {
-    R m, mz, cq, cw, ua, ub, halfp, inv_am, inv_amz;
+    R m, mz, cq, cw, ua, ub, inv_am, inv_amz;
     bool mpos, mzpos;
-    int jshift, kshift, nq, nz;
-    const uint16_t *pairs;     // layout of this ray's major axis, already offset to plane k = 0, j = 0
+    int i_c, jmin, jmax, kmin, kmax;      // clamp range of the RELATIVE minor / z index (memory safety only)
+    const uint16_t *pairs;                // this ray's layout, offset to (column 0, row j_c, plane k_c)
     int pitch;
     long long plane;
     __device__ __forceinline__ void init(const SiddonParams &P, const RaySetup &s)
     {
-        m = (R)s.m; mz = (R)s.mz; cq = (R)s.cq; cw = (R)s.cw; ua = (R)s.ua; ub = (R)s.ub; halfp = (R)s.halfp;
+        m = (R)s.m; mz = (R)s.mz; cq = (R)s.cq; cw = (R)s.cw; ua = (R)s.ua; ub = (R)s.ub;
         inv_am = (R)s.inv_am; inv_amz = (R)s.inv_amz;
         mpos = m >= (R)0; mzpos = mz >= (R)0;
-        jshift = s.jshift; kshift = s.kshift; nq = s.nq; nz = P.vol.nz;
+        i_c = s.i_c;
+        jmin = -1 - s.j_c; jmax = s.nq - 1 - s.j_c;
+        kmin = -1 - s.k_c; kmax = P.vol.nz - 1 - s.k_c;
         pitch = s.xmajor ? P.pitch_xm : P.pitch_ym;
         plane = s.xmajor ? P.plane_xm : P.plane_ym;
-        pairs = (s.xmajor ? P.xm : P.ym) + plane + 1;
+        pairs = (s.xmajor ? P.xm : P.ym) + (long long)(s.k_c + 1) * plane + (s.j_c + 1);
     }
 };
 
-// One column.  Calls sink(slot, j, k, label, w) for slot = 0,1(,2) in order of INCREASING column coordinate.
-// Weights may be zero; j/k may sit in the one-voxel apron (-1 or n) with a weight at rounding level.
+// One column, general form (partial first / last columns included).  Calls sink(slot, jrel, krel, label, w) for
+// slot = 0,1(,2) in order of INCREASING column coordinate; jrel / krel are relative to (j_c, k_c).  Weights may be
+// zero; indices may sit in the one-voxel apron (-1 or n) with a weight at rounding level.
 template <typename R, bool IS3D, typename Sink>
 __device__ __forceinline__ void slab_column(const RayLoop<R> &L, int i, Sink &sink)
 {
     typedef Rn<R> A;
-    const R fi = (R)i;
+    const R fi = (R)(i - L.i_c);
     const R a = A::max(fi, L.ua), b = A::min(A::add(fi, (R)1), L.ub);
     const R wtot = A::sub(b, a);
     if (!(wtot > (R)0)) return;
-    const R pa = A::sub(a, L.halfp), pb = A::sub(b, L.halfp);
-    const R qa = A::fma(L.m, pa, L.cq), qb = A::fma(L.m, pb, L.cq);
+    const R qa = A::fma(L.m, a, L.cq), qb = A::fma(L.m, b, L.cq);
     const R qmin = A::min(qa, qb), qmax = A::max(qa, qb);
-    const R jf = A::floor(qmin);
-    const R qhi = A::min(A::max(A::mul(A::sub(qmax, A::add(jf, (R)1)), L.inv_am), (R)0), wtot);
-    int j = (int)jf + L.jshift;
-    j = min(max(j, -1), L.nq - 1);                       // memory safety only; a no-op for finite geometry
+    int j = FloorInt<R>::of(qmin);
+    const R qhi = A::min(A::max(A::mul(A::sub(qmax, (R)(j + 1)), L.inv_am), (R)0), wtot);
+    j = min(max(j, L.jmin), L.jmax);                     // memory safety only; a no-op for finite geometry
     const uint16_t *col = L.pairs + (long long)i * L.pitch + j;
     if (!IS3D) {
         const unsigned pr = *col;
@@ -169,12 +184,11 @@ __device__ __forceinline__ void slab_column(const RayLoop<R> &L, int i, Sink &si
         if (L.mpos) { sink(0, j, 0, lo, wlo); sink(1, j + 1, 0, hi, qhi); }
         else        { sink(0, j + 1, 0, hi, qhi); sink(1, j, 0, lo, wlo); }
     } else {
-        const R wa = A::fma(L.mz, pa, L.cw), wb = A::fma(L.mz, pb, L.cw);
+        const R wa = A::fma(L.mz, a, L.cw), wb = A::fma(L.mz, b, L.cw);
         const R wmin = A::min(wa, wb), wmax = A::max(wa, wb);
-        const R kf = A::floor(wmin);
-        const R zhi = A::min(A::max(A::mul(A::sub(wmax, A::add(kf, (R)1)), L.inv_amz), (R)0), wtot);
-        int k = (int)kf + L.kshift;
-        k = min(max(k, -1), L.nz - 1);
+        int k = FloorInt<R>::of(wmin);
+        const R zhi = A::min(A::max(A::mul(A::sub(wmax, (R)(k + 1)), L.inv_amz), (R)0), wtot);
+        k = min(max(k, L.kmin), L.kmax);
         const unsigned p0 = col[(long long)k * L.plane];
         const unsigned p1 = col[(long long)(k + 1) * L.plane];
         // p-length spent before the q / z crossing, walking towards +p

@@ -287,11 +287,10 @@ typedef struct {
     int np, nq;              /* voxel counts along major / minor axis */
     int i0, i1;              /* first / last column index touched */
     int fwd;                 /* 1 if the ray travels towards increasing column index */
+    int i_c, j_c, k_c;       /* per-ray origin: column boundary in the middle of the range, voxel indices there */
     double m, mz;            /* minor / z slope per column, voxel units */
-    double cq, cw;           /* q'(p) = cq + m p, w'(p) = cw + mz p with p centred; floor(q')+jshift = index */
-    int jshift, kshift;
-    double ua, ub;           /* clipped column-space interval [ua, ub] in [0, np] */
-    double halfp;            /* np / 2 */
+    double cq, cw;           /* q'(p') = cq + m p', w'(p') = cw + mz p', p' = column coordinate - i_c; cq, cw in [0,1) */
+    double ua, ub;           /* clipped column-space interval, relative to i_c */
     double inv_am, inv_amz;  /* 1/|m|, 1/|mz| (capped at DEXO_BIG) */
     double seglen;           /* ray length per unit column [cm] */
 } slab_ray;
@@ -314,7 +313,6 @@ static void slab_setup(const dexo_setup *g, int v, int r, int c, slab_ray *s)
     const double q0 = qS - s->m * pS;
     const double w0 = wS - s->mz * pS;
     const double hp = 0.5 * (double)s->np, hq = 0.5 * (double)s->nq, hw = 0.5 * (double)g->nz;
-    s->halfp = hp;
     double pe = pS + gp;
     double pa = pS < pe ? pS : pe, pb = pS < pe ? pe : pS;
     if (pa < -hp) pa = -hp;
@@ -332,18 +330,23 @@ static void slab_setup(const dexo_setup *g, int v, int r, int c, slab_ray *s)
         if (hi < pb) pb = hi;
     } else if (!(w0 >= -hw && w0 < hw)) return;
     if (!(pa < pb)) return;
-    s->ua = pa + hp;
-    s->ub = pb + hp;
-    int i0 = (int)floor(s->ua), i1 = (int)ceil(s->ub) - 1;
+    const double ua = pa + hp, ub = pb + hp;
+    int i0 = (int)floor(ua), i1 = (int)ceil(ub) - 1;
     if (i0 < 0) i0 = 0;
     if (i1 > s->np - 1) i1 = s->np - 1;
     if (i1 < i0) return;
     s->i0 = i0; s->i1 = i1;
     s->fwd = gp > 0.0;
-    s->jshift = s->nq / 2;
-    s->kshift = g->nz / 2;
-    s->cq = q0 + (hq - (double)s->jshift);
-    s->cw = w0 + (hw - (double)s->kshift);
+    s->i_c = (i0 + i1 + 1) / 2;
+    const double pc = (double)s->i_c - hp;
+    const double qfull = s->m * pc + (q0 + hq);
+    const double wfull = s->mz * pc + (w0 + hw);
+    const double qfl = floor(qfull), wfl = floor(wfull);
+    s->j_c = (int)qfl; s->k_c = (int)wfl;
+    s->cq = qfull - qfl;
+    s->cw = wfull - wfl;
+    s->ua = ua - (double)s->i_c;
+    s->ub = ub - (double)s->i_c;
     double am = fabs(s->m), amz = fabs(s->mz);
     s->inv_am = am > 0.0 ? 1.0 / am : DEXO_BIG;
     if (s->inv_am > DEXO_BIG) s->inv_am = DEXO_BIG;
@@ -359,43 +362,42 @@ static inline int64_t slab_voxel(const dexo_setup *g, const slab_ray *s, int i, 
 }
 
 /* One column visits up to three voxels (2-D: two).  piece order = order along increasing column coordinate;
- * the caller reverses it for rays travelling towards decreasing column index.                              */
+ * the caller reverses it for rays travelling towards decreasing column index.  j, k are ABSOLUTE indices here. */
 typedef struct { int j, k; double w; } slab_piece;
 
+static inline int iclamp(int x, int lo, int hi) { return x < lo ? lo : (x > hi ? hi : x); }
+
 #define SLAB_COLUMN(REAL, FMA, FLOOR, FMIN, FMAX)                                                           \
-    const REAL fi = (REAL)i;                                                                                \
+    const REAL fi = (REAL)(i - s->i_c);                                                                     \
     const REAL a = FMAX(fi, ua), b = FMIN(fi + (REAL)1, ub);                                                \
     const REAL wtot = b - a;                                                                                \
     int np_ = 0;                                                                                            \
     if (wtot > (REAL)0) {                                                                                   \
-        const REAL pa = a - halfp, pb = b - halfp;                                                          \
-        const REAL qa = FMA(m, pa, cq), qb = FMA(m, pb, cq);                                                \
+        const REAL qa = FMA(m, a, cq), qb = FMA(m, b, cq);                                                  \
         const REAL qmin = FMIN(qa, qb), qmax = FMAX(qa, qb);                                                \
-        const REAL jf = FLOOR(qmin);                                                                        \
-        const REAL qhi = FMIN(FMAX((qmax - (jf + (REAL)1)) * inv_am, (REAL)0), wtot);                       \
-        int j = (int)jf + s->jshift;                                                                        \
-        if (j < -1) j = -1;                                                                                 \
-        if (j > s->nq - 1) j = s->nq - 1;                                                                   \
+        int jr = (int)FLOOR(qmin);                                                                          \
+        const REAL qhi = FMIN(FMAX((qmax - (REAL)(jr + 1)) * inv_am, (REAL)0), wtot);                       \
+        jr = iclamp(jr, -1 - s->j_c, s->nq - 1 - s->j_c);                                                   \
+        const int j = jr + s->j_c;                                                                          \
         /* p-length before the minor crossing, and which voxel comes first along +p */                     \
         const REAL tq = (m >= (REAL)0) ? wtot - qhi : qhi;                                                  \
         const int jfirst = (m >= (REAL)0) ? j : j + 1, jsecond = (m >= (REAL)0) ? j + 1 : j;                \
         if (!is3d) {                                                                                        \
             const REAL w1 = (m >= (REAL)0) ? wtot - qhi : qhi, w2 = (m >= (REAL)0) ? qhi : wtot - qhi;      \
-            pc[0].j = jfirst; pc[0].k = 0; pc[0].w = (double)w1;                                            \
-            pc[1].j = jsecond; pc[1].k = 0; pc[1].w = (double)w2;                                           \
+            pc[0].j = jfirst; pc[0].k = s->k_c; pc[0].w = (double)w1;                                       \
+            pc[1].j = jsecond; pc[1].k = s->k_c; pc[1].w = (double)w2;                                      \
             np_ = 2;                                                                                        \
         } else {                                                                                            \
-            const REAL wa = FMA(mz, pa, cw), wb = FMA(mz, pb, cw);                                          \
+            const REAL wa = FMA(mz, a, cw), wb = FMA(mz, b, cw);                                            \
             const REAL wmin = FMIN(wa, wb), wmax = FMAX(wa, wb);                                            \
-            const REAL kf = FLOOR(wmin);                                                                    \
-            const REAL zhi = FMIN(FMAX((wmax - (kf + (REAL)1)) * inv_amz, (REAL)0), wtot);                  \
-            int k = (int)kf + s->kshift;                                                                    \
-            if (k < -1) k = -1;                                                                             \
-            if (k > nz_ - 1) k = nz_ - 1;                                                                   \
+            int kr = (int)FLOOR(wmin);                                                                      \
+            const REAL zhi = FMIN(FMAX((wmax - (REAL)(kr + 1)) * inv_amz, (REAL)0), wtot);                  \
+            kr = iclamp(kr, -1 - s->k_c, nz_ - 1 - s->k_c);                                                 \
+            const int k = kr + s->k_c;                                                                      \
             const REAL tz = (mz >= (REAL)0) ? wtot - zhi : zhi;                                             \
             const int kfirst = (mz >= (REAL)0) ? k : k + 1, ksecond = (mz >= (REAL)0) ? k + 1 : k;          \
             const REAL t1 = FMIN(tq, tz), t2 = FMAX(tq, tz);                                                \
-            const REAL w1 = t1, w3 = wtot - t2, w2 = t2 - t1;                                                   \
+            const REAL w1 = t1, w3 = wtot - t2, w2 = t2 - t1;                                               \
             pc[0].j = jfirst; pc[0].k = kfirst; pc[0].w = (double)w1;                                       \
             pc[1].j = (tq < tz) ? jsecond : jfirst; pc[1].k = (tq < tz) ? kfirst : ksecond;                 \
             pc[1].w = (double)w2;                                                                           \
@@ -408,7 +410,7 @@ typedef struct { int j, k; double w; } slab_piece;
 static int slab_column_f32(const slab_ray *s, int is3d, int nz_, int i, slab_piece pc[3])
 {
     const float m = (float)s->m, mz = (float)s->mz, cq = (float)s->cq, cw = (float)s->cw;
-    const float ua = (float)s->ua, ub = (float)s->ub, halfp = (float)s->halfp;
+    const float ua = (float)s->ua, ub = (float)s->ub;
     const float inv_am = (float)s->inv_am, inv_amz = (float)s->inv_amz;
     SLAB_COLUMN(float, fmaf, floorf, fminf, fmaxf)
 }
@@ -416,7 +418,7 @@ static int slab_column_f32(const slab_ray *s, int is3d, int nz_, int i, slab_pie
 static int slab_column_f64(const slab_ray *s, int is3d, int nz_, int i, slab_piece pc[3])
 {
     const double m = s->m, mz = s->mz, cq = s->cq, cw = s->cw;
-    const double ua = s->ua, ub = s->ub, halfp = s->halfp;
+    const double ua = s->ua, ub = s->ub;
     const double inv_am = s->inv_am, inv_amz = s->inv_amz;
     SLAB_COLUMN(double, fma, floor, fmin, fmax)
 }

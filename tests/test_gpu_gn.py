@@ -51,7 +51,9 @@ def test_f32_matches_reference_on_rounded_inputs(golden_dir, name):
     out = gn_decompose(d['g'], d['i0'], d['mus'], int(d['n_iters']), dtype=F32).cpu().numpy()
     assert scale_rel_err(out, ref) < 1e-5
     # and it still lands on the truth the golden file was synthesised from, to float32-conditioning accuracy
-    assert scale_rel_err(out, d['a_true']) < 2e-3
+    # (gn_c1_tables has four planted air pixels at the start of view 0 whose a_true is not what was measured)
+    skip = 4 if name == 'gn_c1_tables' else 0
+    assert scale_rel_err(out.reshape(-1, 2)[skip:], d['a_true'].reshape(-1, 2)[skip:]) < 2e-3
 
 
 def test_air_mask_and_dropin_entry_point(golden_dir):

@@ -97,10 +97,19 @@ def test_degenerate_rays_bit_exact():
             for rid, (vx, lb, ln) in zip(ids, pj.trace(ids, max_seg=512, dtype=dtype)):
                 w = sc.slab_trace(int(rid // n_ch), 0, int(rid % n_ch), dtype == F64)
                 assert np.array_equal(vx, w[0]) and np.array_equal(lb, w[1]) and np.array_equal(ln.astype(np.float64), w[2])
-        # and the float64 sequences are Siddon's on these rays up to zero-length corner touches: lengths agree
+        # and the float64 lengths are Siddon's -- except on rays that run ALONG a grid plane (within rounding of it), where
+        # which of the two adjacent voxel rows the ray "is in" is a coin toss for any implementation, the paper's
+        # midpoint rule included; there only the total is defined
         L = sc.slab_lengths(4, True)
         Lc, _ = sc.classic_lengths(4)
-        assert np.max(np.abs(L - Lc)) < 1e-10
+        assert np.max(np.abs(L.sum(-1) - Lc.sum(-1))) < 1e-10
+        for v in range(8):
+            for c in range(n_ch):
+                S_, T_ = sc.endpoints(v, 0, c)
+                grazing = any(abs(S_[a] - T_[a]) < 1e-9 and abs(S_[a] / vox + n / 2.0 - round(S_[a] / vox + n / 2.0)) < 1e-9
+                              for a in (0, 1))
+                if not grazing:
+                    assert np.max(np.abs(L[v, 0, c] - Lc[v, 0, c])) < 1e-10, (n, v, c)
 
 
 @pytest.mark.parametrize('dtype', [F32, F64])
