@@ -67,6 +67,69 @@ __global__ void repack_xm_kernel(const uint8_t *__restrict__ labels, int nx, int
     }
 }
 
+// Skip layouts (2-D scans).  One per (major axis, sign s of the minor slope), indexed like one plane of the pair layouts.
+// The word at (column i, jj = j + 1) tells a ray with 0 <= s*m <= 1 whose lower minor index inside column i is j what it
+// can meet from there on:
+//   bit 15 set  : voxels (i, j) and (i, j+1) carry the same label l = bits 0..6, and so does every voxel the ray can touch
+//                 in columns i .. i+S-1, S = bits 8..14 (1..127): the whole stretch is one Siddon run of label l and the
+//                 kernel accounts it in a single step;
+//   bit 15 clear: bits 0..6 = label(i, j), bits 8..14 = label(i, j+1) -- an ordinary column, split at the crossing.
+// "Can touch" is the cone of slopes [0, 1] (times s): at column i+1 the lower index is j or j+s, so
+//   S(i, j) = 1 + min(S'(i+1, j), S'(i+1, j+s)),  S' = S where the label is the same and 0 elsewhere,
+// a sweep from the last column to the first.  Labels must be < 128 for these layouts to be used (siddon_poly checks K).
+constexpr int SKIP_EPT = 4;          // entries per thread of the sweep
+constexpr int SKIP_THREADS = 1024;
+constexpr int SKIP_MAX_ENTRIES = SKIP_EPT * SKIP_THREADS;
+
+struct SkipBuildArgs {
+    const uint16_t *pairs[2];        // plane k = 0 of the x-major / y-major pair layout
+    uint16_t *out[4];
+    int np[2], nq[2], pitch[2];
+};
+
+__global__ void __launch_bounds__(SKIP_THREADS) skip_build_kernel(SkipBuildArgs A)
+{
+    extern __shared__ uint16_t sk_buf[];                   // [2][n_ent + 2]: (S << 8 | label), label 0xff = no run
+    const int lay = blockIdx.x, ax = lay >> 1, sgn = (lay & 1) ? -1 : 1;
+    const uint16_t *__restrict__ pairs = A.pairs[ax];
+    uint16_t *__restrict__ out = A.out[lay];
+    const int np = A.np[ax], n_ent = A.nq[ax] + 1, pitch = A.pitch[ax];
+    const int ld = n_ent + 2;                              // one guard entry on either side
+    uint16_t *prev = sk_buf + 1, *next = sk_buf + ld + 1;
+    for (int t = threadIdx.x; t < 2 * ld; t += blockDim.x) sk_buf[t] = 0x00ff;
+    unsigned cur[SKIP_EPT], nxt[SKIP_EPT];
+#pragma unroll
+    for (int u = 0; u < SKIP_EPT; ++u) {
+        const int jj = threadIdx.x + u * SKIP_THREADS;
+        cur[u] = jj < n_ent ? pairs[(long long)(np - 1) * pitch + jj] : 0u;
+    }
+    __syncthreads();
+    for (int i = np - 1; i >= 0; --i) {
+#pragma unroll
+        for (int u = 0; u < SKIP_EPT; ++u) {
+            const int jj = threadIdx.x + u * SKIP_THREADS;
+            nxt[u] = (i > 0 && jj < n_ent) ? pairs[(long long)(i - 1) * pitch + jj] : 0u;
+        }
+#pragma unroll
+        for (int u = 0; u < SKIP_EPT; ++u) {
+            const int jj = threadIdx.x + u * SKIP_THREADS;
+            if (jj < n_ent) {
+                const unsigned lo = cur[u] & 0x7f, hi = (cur[u] >> 8) & 0x7f;
+                const unsigned pa = prev[jj], pb = prev[jj + sgn];
+                const unsigned sa = (pa & 0xff) == lo ? pa >> 8 : 0u, sb = (pb & 0xff) == lo ? pb >> 8 : 0u;
+                const bool hom = lo == hi;
+                const unsigned S = hom ? min(1u + min(sa, sb), 127u) : 0u;
+                out[(long long)i * pitch + jj] = (uint16_t)(hom ? (0x8000u | (S << 8) | lo) : (lo | (hi << 8)));
+                next[jj] = (uint16_t)(hom ? ((S << 8) | lo) : 0x00ffu);
+            }
+        }
+        __syncthreads();
+        uint16_t *t = prev; prev = next; next = t;
+#pragma unroll
+        for (int u = 0; u < SKIP_EPT; ++u) cur[u] = nxt[u];
+    }
+}
+
 // ---------------------------------------------------------------------------------------------------------
 // Polyenergetic detection epilogue (forward model of matdecomp.py:116-118 with K materials):
 // counts_s = sum_e W[s][e] exp(-sum_m L_m mu[m][e]).
@@ -322,6 +385,128 @@ __global__ void __launch_bounds__(128) siddon_poly_kernel(SiddonParams P, int vi
     }
 }
 
+// ---------------------------------------------------------------------------------------------------------
+// 2-D production kernel over the skip layouts: one ray per thread, each lane walks its own ray and takes whole
+// homogeneous stretches in one step (about 28 steps per ray instead of 450 columns on the C2 phantom).
+
+// floor(x) as an integer and as a real, and small non-negative integers as reals, without the conversion unit in
+// single precision (the quarter-rate F2I/I2F would otherwise bound the loop): x + 1.5*2^23 rounded towards -inf has
+// floor(x) in its low mantissa bits, exactly, for |x| < 2^22.
+template <typename R> struct FastInt;
+template <> struct FastInt<float> {
+    static constexpr float MAGIC = 12582912.0f;
+    static __device__ __forceinline__ float bias(float x) { return __fadd_rd(x, MAGIC); }          // floor(x) + MAGIC
+    static __device__ __forceinline__ float unbias(float t) { return __fsub_rn(t, MAGIC); }
+    static __device__ __forceinline__ int to_int(float t) { return __float_as_int(t) - 0x4B400000; }
+    static __device__ __forceinline__ float biased(int j) { return __int_as_float(j + 0x4B400000); }
+    static __device__ __forceinline__ float real(int n) { return __fsub_rn(__int_as_float(n + 0x4B400000), MAGIC); }
+};
+template <> struct FastInt<double> {
+    static __device__ __forceinline__ double bias(double x) { return floor(x); }
+    static __device__ __forceinline__ double unbias(double t) { return t; }
+    static __device__ __forceinline__ int to_int(double t) { return __double2int_rd(t); }
+    static __device__ __forceinline__ double biased(int j) { return (double)j; }
+    static __device__ __forceinline__ double real(int n) { return (double)n; }
+};
+
+template <typename R>
+__device__ __forceinline__ void walk_skip(const RayLoop<R> &L, const uint16_t *__restrict__ W, int i0, int i1,
+                                          R *acc, int stride)
+{
+    typedef Rn<R> A;
+    typedef FastInt<R> F;
+    // W points at (column 0, row j_c) of this ray's skip layout
+    const R tmin = F::biased(L.jmin), tmax = F::biased(L.jmax);
+    int i = i0;
+    R fi = F::real(i0 - L.i_c + (1 << 20));                 // kept as a real; the offset keeps the argument non-negative
+    fi = A::sub(fi, (R)(1 << 20));
+    while (i <= i1) {
+        const R a = A::max(fi, L.ua);
+        const R b1 = A::min(A::add(fi, (R)1), L.ub);
+        const R qa = A::fma(L.m, a, L.cq), qb = A::fma(L.m, b1, L.cq);
+        const R qmin = A::min(qa, qb), qmax = A::max(qa, qb);
+        const R t = A::min(A::max(F::bias(qmin), tmin), tmax);      // clamp: memory safety only
+        const int j = F::to_int(t);
+        const unsigned w = W[(long long)i * L.pitch + j];
+        const bool hom = (w & 0x8000u) != 0;
+        const int f0 = w & 0x7f, f1 = (w >> 8) & 0x7f;
+        const int step = hom ? f1 : 1;
+        const R fstep = F::real(step);
+        const R fnext = A::add(fi, fstep);
+        const R b = A::min(fnext, L.ub);
+        const R wtot = A::max(A::sub(b, a), (R)0);
+        // share of the upper voxel (j+1): what lies beyond the crossing of minor plane j+1
+        R whi = A::min(A::max(A::mul(A::sub(qmax, A::add(F::unbias(t), (R)1)), L.inv_am), (R)0), wtot);
+        whi = hom ? (R)0 : whi;
+        const R wlo = A::sub(wtot, whi);
+        const int lab1 = hom ? f0 : f1;
+        R *p0 = acc + f0 * stride, *p1 = acc + lab1 * stride;
+        *p0 = A::add(*p0, wlo);
+        *p1 = A::add(*p1, whi);
+        i += step;
+        fi = fnext;
+    }
+}
+
+template <typename R, int KT>
+__global__ void __launch_bounds__(128) siddon_skip_kernel(SiddonParams P, int view_begin, long long n_rays, DetectArgs d)
+{
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    const int KP = KT > 0 ? KT : d.K;
+    R *acc_s = (R *)smem_raw;                              // [KP][blockDim]
+    R *mu_s = acc_s + (size_t)KP * blockDim.x;             // [KP][nE]
+    R *W_s = mu_s + (size_t)KP * d.nE;                     // [nSpec][nE]
+    R *air_s = W_s + (size_t)d.nSpec * d.nE;               // [nSpec]
+    stage_tables<R>(d, KP, mu_s, W_s, air_s);
+
+    const int tid = threadIdx.x;
+    for (int m = 0; m < KP; ++m) acc_s[m * blockDim.x + tid] = (R)0;
+
+    const long long ray = (long long)blockIdx.x * blockDim.x + tid;
+    if (ray >= n_rays) return;
+    const int c = (int)(ray % P.scan.n_ch);
+    const int v = view_begin + (int)(ray / P.scan.n_ch);
+
+    RaySetup s;
+    ray_setup(P, v, 0, c, s);
+    R seglen = (R)0;
+    if (s.hit) {
+        RayLoop<R> L;
+        L.init(P, s);
+        const uint16_t *W = P.skip[(s.xmajor ? 0 : 2) + (L.mpos ? 0 : 1)] + (s.j_c + 1);
+        walk_skip<R>(L, W, s.i0, s.i1, acc_s + tid, (int)blockDim.x);
+        seglen = (R)s.seglen;
+    }
+
+    R out[MAX_SPEC];
+    if (KT > 0) {
+        R Lr[KT > 0 ? KT : 1];
+#pragma unroll
+        for (int m = 0; m < (KT > 0 ? KT : 1); ++m) Lr[m] = acc_s[m * blockDim.x + tid] * seglen;
+        if (d.L_out) {
+            R *Lo = (R *)d.L_out + ray * d.K;
+#pragma unroll
+            for (int m = 0; m < (KT > 0 ? KT : 1); ++m)
+                if (m < d.K) Lo[m] = Lr[m];
+        }
+        detect_reg<R, (KT > 0 ? KT : 1)>(Lr, mu_s, W_s, d.nE, d.nSpec, out);
+    } else {
+        for (int m = 0; m < d.K; ++m) acc_s[m * blockDim.x + tid] *= seglen;
+        if (d.L_out) {
+            R *Lo = (R *)d.L_out + ray * d.K;
+            for (int m = 0; m < d.K; ++m) Lo[m] = acc_s[m * blockDim.x + tid];
+        }
+        detect<R>(acc_s + tid, blockDim.x, d.K, mu_s, W_s, d.nE, d.nSpec, out);
+    }
+#pragma unroll
+    for (int sp = 0; sp < MAX_SPEC; ++sp) {
+        if (sp < d.nSpec) {
+            ((R *)d.counts)[sp * n_rays + ray] = out[sp];
+            if (d.logs) ((R *)d.logs)[sp * n_rays + ray] = neg_log_ratio<R>(out[sp], air_s[sp]);
+        }
+    }
+}
+
 // Detection from stored lengths L [n_rays][K].
 template <typename R>
 __global__ void __launch_bounds__(128) poly_detect_kernel(const R *__restrict__ Lin, long long n_rays, DetectArgs d)
@@ -437,12 +622,9 @@ static int make_params(const DexctScan *scan, const DexctVolume *vol, const void
     P.zdet = (const double *)(w + L.off_zdet);
     P.xm = (const uint16_t *)(w + L.off_xm); P.ym = (const uint16_t *)(w + L.off_ym);
     P.pitch_xm = L.pitch_xm; P.pitch_ym = L.pitch_ym; P.plane_xm = L.plane_xm; P.plane_ym = L.plane_ym;
+    const bool skip = L.has_skip && vol->nx + 1 <= SKIP_MAX_ENTRIES && vol->ny + 1 <= SKIP_MAX_ENTRIES;
+    for (int a = 0; a < 4; ++a) P.skip[a] = skip ? (const uint16_t *)(w + L.off_skip[a]) : nullptr;
     return DEXCT_OK;
-}
-
-static bool scan_is_3d(const DexctScan &s, const DexctVolume &v)
-{
-    return v.nz > 1 || s.n_rows > 1 || s.z0 != 0.0;
 }
 
 template <typename R, bool IS3D, int KT>
@@ -455,7 +637,9 @@ static int launch_poly(const SiddonParams &P, int view_begin, long long n_rays, 
         set_error("material/energy tables need %zu bytes of shared memory (limit 200 KiB): K=%d nE=%d", smem, d.K, d.nE);
         return DEXCT_ECAPACITY;
     }
-    auto kern = siddon_poly_kernel<R, IS3D, KT>;
+    // 2-D scans with 7-bit labels walk the skip layouts
+    const bool use_skip = !IS3D && P.skip[0] != nullptr && d.K <= 128;
+    auto kern = use_skip ? siddon_skip_kernel<R, KT> : siddon_poly_kernel<R, IS3D, KT>;
     if (smem > 48 * 1024) DEXCT_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     const long long grid = (n_rays + block - 1) / block;
     kern<<<(unsigned)grid, block, smem, st>>>(P, view_begin, n_rays, d);
@@ -508,6 +692,17 @@ extern "C" int dexct_siddon_prepare(const DexctScan *scan, const DexctVolume *vo
     repack_xm_kernel<<<grid, dim3(32, 8), 0, st>>>(labels, vol->nx, vol->ny, vol->nz, (uint16_t *)(w + L.off_xm),
                                                   L.pitch_xm, L.plane_xm);
     DEXCT_CUDA_OK(cudaGetLastError());
+    if (P.skip[0]) {
+        SkipBuildArgs A;
+        A.pairs[0] = (const uint16_t *)(w + L.off_xm) + L.plane_xm;
+        A.pairs[1] = (const uint16_t *)(w + L.off_ym) + L.plane_ym;
+        for (int a = 0; a < 4; ++a) A.out[a] = (uint16_t *)(w + L.off_skip[a]);
+        A.np[0] = vol->nx; A.nq[0] = vol->ny; A.pitch[0] = L.pitch_xm;
+        A.np[1] = vol->ny; A.nq[1] = vol->nx; A.pitch[1] = L.pitch_ym;
+        const size_t smem = sizeof(uint16_t) * 2 * (size_t)(max(vol->nx, vol->ny) + 3);
+        skip_build_kernel<<<4, SKIP_THREADS, smem, st>>>(A);
+        DEXCT_CUDA_OK(cudaGetLastError());
+    }
     return DEXCT_OK;
 }
 

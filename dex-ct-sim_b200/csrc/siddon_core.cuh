@@ -19,12 +19,20 @@ namespace dexct {
 struct WsLayout {
     size_t off_cosb, off_sinb, off_cosg, off_sing, off_zdet;   // double tables
     size_t off_xm, off_ym;                                     // uint16 pair layouts (bytes from workspace start)
+    size_t off_skip[4];                                        // uint16 skip layouts (2-D scans only): x+, x-, y+, y-
+    bool has_skip;
     size_t total;
     int pitch_xm, pitch_ym;                                    // entries per column (nq + 2, rounded up)
     long long plane_xm, plane_ym;                              // entries per z plane
 };
 
 __host__ __device__ inline size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
+
+// 3-D column routine whenever anything can leave the z = 0 plane (decided per scan)
+inline bool scan_is_3d(const DexctScan &s, const DexctVolume &v)
+{
+    return v.nz > 1 || s.n_rows > 1 || s.z0 != 0.0;
+}
 
 inline WsLayout ws_layout(const DexctScan &s, const DexctVolume &v)
 {
@@ -41,6 +49,12 @@ inline WsLayout ws_layout(const DexctScan &s, const DexctVolume &v)
     L.plane_ym = (long long)v.ny * L.pitch_ym;
     L.off_xm = o; o = align_up(o + sizeof(uint16_t) * (size_t)L.plane_xm * (size_t)(v.nz + 2), 256);
     L.off_ym = o; o = align_up(o + sizeof(uint16_t) * (size_t)L.plane_ym * (size_t)(v.nz + 2), 256);
+    // skip layouts: same indexing as one plane of the pair layouts (no z apron), one per (major axis, sign of the slope)
+    L.has_skip = !scan_is_3d(s, v);
+    for (int a = 0; a < 4; ++a) {
+        L.off_skip[a] = o;
+        if (L.has_skip) o = align_up(o + sizeof(uint16_t) * (size_t)(a < 2 ? L.plane_xm : L.plane_ym), 256);
+    }
     L.total = o;
     return L;
 }
@@ -51,6 +65,7 @@ struct SiddonParams {
     DexctVolume vol;
     const double *cosb, *sinb, *cosg, *sing, *zdet;
     const uint16_t *xm, *ym;          // pair layouts; element (k, i, j) at ((k+1)*plane + i*pitch + (j+1))
+    const uint16_t *skip[4];          // skip layouts (2-D only; null otherwise); element (i, j) at (i*pitch + (j+1))
     int pitch_xm, pitch_ym;
     long long plane_xm, plane_ym;
 };
