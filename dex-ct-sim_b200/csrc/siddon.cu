@@ -1,6 +1,7 @@
 // Forward projection kernels: workspace preparation, Siddon traversal with fused polyenergetic detection,
 // detection from stored lengths, and the debug trace.  Replaces get_sino (/root/reference/main.py:120).
 #include "siddon_core.cuh"
+#include <algorithm>
 
 namespace dexct {
 
@@ -87,13 +88,17 @@ struct SkipBuildArgs {
     int np[2], nq[2], pitch[2];
 };
 
+// The layouts for NEGATIVE slopes are built on the image mirrored along the minor axis (row U = nq-1-j), where the
+// slope is positive again: the walk then needs no min/max of the two boundary positions.  Mirrored pair (U, U+1) is the
+// byte-swapped original pair (j-1, j) with j = nq-1-U.
 __global__ void __launch_bounds__(SKIP_THREADS) skip_build_kernel(SkipBuildArgs A)
 {
     extern __shared__ uint16_t sk_buf[];                   // [2][n_ent + 2]: (S << 8 | label), label 0xff = no run
-    const int lay = blockIdx.x, ax = lay >> 1, sgn = (lay & 1) ? -1 : 1;
+    const int lay = blockIdx.x, ax = lay >> 1;
+    const bool mirror = (lay & 1) != 0;
     const uint16_t *__restrict__ pairs = A.pairs[ax];
     uint16_t *__restrict__ out = A.out[lay];
-    const int np = A.np[ax], n_ent = A.nq[ax] + 1, pitch = A.pitch[ax];
+    const int np = A.np[ax], nq = A.nq[ax], n_ent = nq + 1, pitch = A.pitch[ax];
     const int ld = n_ent + 2;                              // one guard entry on either side
     uint16_t *prev = sk_buf + 1, *next = sk_buf + ld + 1;
     for (int t = threadIdx.x; t < 2 * ld; t += blockDim.x) sk_buf[t] = 0x00ff;
@@ -101,21 +106,22 @@ __global__ void __launch_bounds__(SKIP_THREADS) skip_build_kernel(SkipBuildArgs 
 #pragma unroll
     for (int u = 0; u < SKIP_EPT; ++u) {
         const int jj = threadIdx.x + u * SKIP_THREADS;
-        cur[u] = jj < n_ent ? pairs[(long long)(np - 1) * pitch + jj] : 0u;
+        cur[u] = jj < n_ent ? pairs[(long long)(np - 1) * pitch + (mirror ? nq - jj : jj)] : 0u;
     }
     __syncthreads();
     for (int i = np - 1; i >= 0; --i) {
 #pragma unroll
         for (int u = 0; u < SKIP_EPT; ++u) {
             const int jj = threadIdx.x + u * SKIP_THREADS;
-            nxt[u] = (i > 0 && jj < n_ent) ? pairs[(long long)(i - 1) * pitch + jj] : 0u;
+            nxt[u] = (i > 0 && jj < n_ent) ? pairs[(long long)(i - 1) * pitch + (mirror ? nq - jj : jj)] : 0u;
         }
 #pragma unroll
         for (int u = 0; u < SKIP_EPT; ++u) {
             const int jj = threadIdx.x + u * SKIP_THREADS;
             if (jj < n_ent) {
-                const unsigned lo = cur[u] & 0x7f, hi = (cur[u] >> 8) & 0x7f;
-                const unsigned pa = prev[jj], pb = prev[jj + sgn];
+                const unsigned b0 = cur[u] & 0x7f, b1 = (cur[u] >> 8) & 0x7f;
+                const unsigned lo = mirror ? b1 : b0, hi = mirror ? b0 : b1;
+                const unsigned pa = prev[jj], pb = prev[jj + 1];
                 const unsigned sa = (pa & 0xff) == lo ? pa >> 8 : 0u, sb = (pb & 0xff) == lo ? pb >> 8 : 0u;
                 const bool hom = lo == hi;
                 const unsigned S = hom ? min(1u + min(sa, sb), 127u) : 0u;
@@ -346,7 +352,7 @@ __global__ void __launch_bounds__(128) siddon_poly_kernel(SiddonParams P, int vi
     const int v = view_begin + (int)(line / P.scan.n_rows);
 
     RaySetup s;
-    ray_setup(P, v, r, c, s);
+    ray_setup<IS3D>(P, v, r, c, s);
     R seglen = (R)0;
     if (s.hit) {
         RayLoop<R> L;
@@ -409,100 +415,199 @@ template <> struct FastInt<double> {
     static __device__ __forceinline__ double real(int n) { return (double)n; }
 };
 
+// Packed single-precision pairs (FFMA2 on sm_100a: two FMAs per issue slot).
+typedef unsigned long long f32x2;
+__device__ __forceinline__ f32x2 pack2(float x, float y)
+{
+    f32x2 r;
+    asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(x), "f"(y));
+    return r;
+}
+__device__ __forceinline__ void unpack2(f32x2 v, float &x, float &y) { asm("mov.b64 {%0, %1}, %2;" : "=f"(x), "=f"(y) : "l"(v)); }
+__device__ __forceinline__ f32x2 ffma2(f32x2 a, f32x2 b, f32x2 c)
+{
+    f32x2 r;
+    asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r) : "l"(a), "l"(b), "l"(c));
+    return r;
+}
+
+// Single-precision detection with the tables packed by ENERGY PAIRS in shared memory:
+//   mu2 [nE2][KT]  float2 = mu_m * log2(e) at energies 2 e2, 2 e2 + 1  (rows of materials -> LDS.128 of two materials)
+//   W2  [nE2][NSP] float2 = W_s at energies 2 e2, 2 e2 + 1
+// An odd nE is padded with a zero-weight bin.  Per energy pair: KT FFMA2 + 2 MUFU.EX2 + NSP FFMA2.
+template <int KT, int NSP>
+__device__ __forceinline__ void detect_packed(const float (&Lr)[KT], const f32x2 *mu2, const f32x2 *W2, int nE2, float *out)
+{
+    f32x2 L2[KT], acc[NSP];
+#pragma unroll
+    for (int m = 0; m < KT; ++m) L2[m] = pack2(Lr[m], Lr[m]);
+#pragma unroll
+    for (int sp = 0; sp < NSP; ++sp) acc[sp] = 0ull;
+#pragma unroll 2
+    for (int e2 = 0; e2 < nE2; ++e2) {
+        const ulonglong2 *row = (const ulonglong2 *)(mu2 + (size_t)e2 * KT);
+        f32x2 t0 = 0ull, t1 = 0ull;
+#pragma unroll
+        for (int h = 0; h < KT / 2; ++h) {
+            const ulonglong2 q = row[h];
+            t0 = ffma2(L2[2 * h], q.x, t0);
+            t1 = ffma2(L2[2 * h + 1], q.y, t1);
+        }
+        float xa, ya, xb, yb;
+        unpack2(t0, xa, ya);
+        unpack2(t1, xb, yb);
+        const f32x2 att = pack2(DetMath<float>::att(xa + xb), DetMath<float>::att(ya + yb));
+        const ulonglong2 *wrow = (const ulonglong2 *)(W2 + (size_t)e2 * NSP);
+#pragma unroll
+        for (int h = 0; h < NSP / 2; ++h) {
+            const ulonglong2 q = wrow[h];
+            acc[2 * h] = ffma2(q.x, att, acc[2 * h]);
+            acc[2 * h + 1] = ffma2(q.y, att, acc[2 * h + 1]);
+        }
+    }
+#pragma unroll
+    for (int sp = 0; sp < MAX_SPEC; ++sp) {
+        float x = 0.f, y = 0.f;
+        if (sp < NSP) unpack2(acc[sp], x, y);
+        out[sp] = x + y;
+    }
+}
+
+template <int KT, int NSP>
+__device__ __forceinline__ void stage_packed(const DetectArgs &d, f32x2 *mu2, f32x2 *W2, float *air_s)
+{
+    const float *mu = (const float *)d.mu, *W = (const float *)d.W;
+    const int nE2 = (d.nE + 1) / 2;
+    for (int t = threadIdx.x; t < nE2 * KT; t += blockDim.x) {
+        const int e2 = t / KT, m = t % KT, e = 2 * e2;
+        const float a = (m < d.K) ? mu[m * d.nE + e] * DetMath<float>::scale : 0.f;
+        const float b = (m < d.K && e + 1 < d.nE) ? mu[m * d.nE + e + 1] * DetMath<float>::scale : 0.f;
+        mu2[t] = pack2(a, b);
+    }
+    for (int t = threadIdx.x; t < nE2 * NSP; t += blockDim.x) {
+        const int e2 = t / NSP, sp = t % NSP, e = 2 * e2;
+        const float a = (sp < d.nSpec) ? W[sp * d.nE + e] : 0.f;
+        const float b = (sp < d.nSpec && e + 1 < d.nE) ? W[sp * d.nE + e + 1] : 0.f;
+        W2[t] = pack2(a, b);
+    }
+    if (threadIdx.x < MAX_SPEC) {
+        float a = 0.f;
+        if (threadIdx.x < d.nSpec)
+            for (int e = 0; e < d.nE; ++e) a += W[threadIdx.x * d.nE + e];
+        air_s[threadIdx.x] = a;
+    }
+    __syncthreads();
+}
+
+// Walk of one ray over its skip layout.  Everything is expressed in the ray's own (possibly mirrored) minor coordinate,
+// in which the slope am = |m| is non-negative: q(p) = am p + c0, lower voxel j = floor(q(a)), upper voxel j + 1 entered
+// where q crosses j + 1.  W points at (column 0, mirrored row of j_c) of the layout for this ray's axis and slope sign.
+// No clamp on j: the ray is clipped to the volume, so j stays inside [-1, nq] -- the zero apron and the row padding of
+// the layout.
 template <typename R>
-__device__ __forceinline__ void walk_skip(const RayLoop<R> &L, const uint16_t *__restrict__ W, int i0, int i1,
-                                          R *acc, int stride)
+__device__ __forceinline__ void walk_skip(const uint16_t *__restrict__ W, int pitch, int i0, int i1, int i_c, R am, R c0,
+                                          R ua, R ub, R inv_am, R *acc, int stride)
 {
     typedef Rn<R> A;
     typedef FastInt<R> F;
-    // W points at (column 0, row j_c) of this ray's skip layout
-    const R tmin = F::biased(L.jmin), tmax = F::biased(L.jmax);
-    int i = i0;
-    R fi = F::real(i0 - L.i_c + (1 << 20));                 // kept as a real; the offset keeps the argument non-negative
-    fi = A::sub(fi, (R)(1 << 20));
-    while (i <= i1) {
-        const R a = A::max(fi, L.ua);
-        const R b1 = A::min(A::add(fi, (R)1), L.ub);
-        const R qa = A::fma(L.m, a, L.cq), qb = A::fma(L.m, b1, L.cq);
-        const R qmin = A::min(qa, qb), qmax = A::max(qa, qb);
-        const R t = A::min(A::max(F::bias(qmin), tmin), tmax);      // clamp: memory safety only
-        const int j = F::to_int(t);
-        const unsigned w = W[(long long)i * L.pitch + j];
-        const bool hom = (w & 0x8000u) != 0;
+    const R c0m1 = A::sub(c0, (R)1);
+    R fi = A::sub(F::real(i0 - i_c + (1 << 20)), (R)(1 << 20));          // column coordinate of column i, as a real
+    const R fend = A::sub(F::real(i1 - i_c + (1 << 20)), (R)(1 << 20));
+    int ofs = i0 * pitch;
+    while (fi <= fend) {
+        const R a = A::max(fi, ua);
+        const R b1 = A::min(A::add(fi, (R)1), ub);
+        const R qa = A::fma(am, a, c0);
+        const R qbm1 = A::fma(am, b1, c0m1);                              // q(b1) - 1
+        const R t = F::bias(qa);
+        const int w = (int)(short)W[ofs + F::to_int(t)];
+        const bool hom = w < 0;
         const int f0 = w & 0x7f, f1 = (w >> 8) & 0x7f;
         const int step = hom ? f1 : 1;
-        const R fstep = F::real(step);
-        const R fnext = A::add(fi, fstep);
-        const R b = A::min(fnext, L.ub);
-        const R wtot = A::max(A::sub(b, a), (R)0);
-        // share of the upper voxel (j+1): what lies beyond the crossing of minor plane j+1
-        R whi = A::min(A::max(A::mul(A::sub(qmax, A::add(F::unbias(t), (R)1)), L.inv_am), (R)0), wtot);
+        const R fnext = A::add(fi, F::real(step));
+        const R wtot = A::sub(A::min(fnext, ub), a);
+        // share of the upper voxel: the column length beyond the crossing of minor plane j + 1
+        R whi = A::max(A::mul(A::sub(qbm1, F::unbias(t)), inv_am), (R)0);
         whi = hom ? (R)0 : whi;
         const R wlo = A::sub(wtot, whi);
-        const int lab1 = hom ? f0 : f1;
-        R *p0 = acc + f0 * stride, *p1 = acc + lab1 * stride;
-        *p0 = A::add(*p0, wlo);
-        *p1 = A::add(*p1, whi);
-        i += step;
+        R *p0 = acc + f0 * stride, *p1 = acc + (hom ? f0 : f1) * stride;
+        const R v0 = *p0, v1 = *p1;
+        *p1 = A::add(v1, whi);                                            // p1 == p0 only when whi == 0: order matters
+        *p0 = A::add(v0, wlo);
+        ofs += step * pitch;
         fi = fnext;
     }
 }
 
-template <typename R, int KT>
+template <typename R, int KT, int NSP>
 __global__ void __launch_bounds__(128) siddon_skip_kernel(SiddonParams P, int view_begin, long long n_rays, DetectArgs d)
 {
+    constexpr bool PACKED = (sizeof(R) == 4) && KT > 0;
     extern __shared__ __align__(16) unsigned char smem_raw[];
     const int KP = KT > 0 ? KT : d.K;
-    R *acc_s = (R *)smem_raw;                              // [KP][blockDim]
-    R *mu_s = acc_s + (size_t)KP * blockDim.x;             // [KP][nE]
-    R *W_s = mu_s + (size_t)KP * d.nE;                     // [nSpec][nE]
-    R *air_s = W_s + (size_t)d.nSpec * d.nE;               // [nSpec]
-    stage_tables<R>(d, KP, mu_s, W_s, air_s);
-
     const int tid = threadIdx.x;
-    for (int m = 0; m < KP; ++m) acc_s[m * blockDim.x + tid] = (R)0;
-
-    const long long ray = (long long)blockIdx.x * blockDim.x + tid;
-    if (ray >= n_rays) return;
-    const int c = (int)(ray % P.scan.n_ch);
-    const int v = view_begin + (int)(ray / P.scan.n_ch);
-
-    RaySetup s;
-    ray_setup(P, v, 0, c, s);
-    R seglen = (R)0;
-    if (s.hit) {
-        RayLoop<R> L;
-        L.init(P, s);
-        const uint16_t *W = P.skip[(s.xmajor ? 0 : 2) + (L.mpos ? 0 : 1)] + (s.j_c + 1);
-        walk_skip<R>(L, W, s.i0, s.i1, acc_s + tid, (int)blockDim.x);
-        seglen = (R)s.seglen;
-    }
-
-    R out[MAX_SPEC];
-    if (KT > 0) {
-        R Lr[KT > 0 ? KT : 1];
-#pragma unroll
-        for (int m = 0; m < (KT > 0 ? KT : 1); ++m) Lr[m] = acc_s[m * blockDim.x + tid] * seglen;
-        if (d.L_out) {
-            R *Lo = (R *)d.L_out + ray * d.K;
-#pragma unroll
-            for (int m = 0; m < (KT > 0 ? KT : 1); ++m)
-                if (m < d.K) Lo[m] = Lr[m];
-        }
-        detect_reg<R, (KT > 0 ? KT : 1)>(Lr, mu_s, W_s, d.nE, d.nSpec, out);
+    R *acc_s = (R *)smem_raw;                              // [KP][blockDim]
+    unsigned char *tab = smem_raw + sizeof(R) * (size_t)KP * blockDim.x;
+    // generic tables
+    R *mu_s = (R *)tab, *W_s = mu_s + (size_t)KP * d.nE, *air_s = W_s + (size_t)d.nSpec * d.nE;
+    // packed tables (float, KT > 0)
+    const int nE2 = (d.nE + 1) / 2;
+    f32x2 *mu2 = (f32x2 *)tab, *W2 = mu2 + (size_t)nE2 * (KT > 0 ? KT : 1);
+    if (PACKED) {
+        air_s = (R *)(W2 + (size_t)nE2 * NSP);
+        stage_packed<(KT > 0 ? KT : 2), NSP>(d, mu2, W2, (float *)air_s);
     } else {
-        for (int m = 0; m < d.K; ++m) acc_s[m * blockDim.x + tid] *= seglen;
-        if (d.L_out) {
-            R *Lo = (R *)d.L_out + ray * d.K;
-            for (int m = 0; m < d.K; ++m) Lo[m] = acc_s[m * blockDim.x + tid];
-        }
-        detect<R>(acc_s + tid, blockDim.x, d.K, mu_s, W_s, d.nE, d.nSpec, out);
+        stage_tables<R>(d, KP, mu_s, W_s, air_s);
     }
+
+    const long long n_blk = (n_rays + blockDim.x - 1) / blockDim.x;
+    for (long long blk = blockIdx.x; blk < n_blk; blk += gridDim.x) {
+        const long long ray = blk * blockDim.x + tid;
+        if (ray >= n_rays) continue;
+        const int c = (int)(ray % P.scan.n_ch);
+        const int v = view_begin + (int)(ray / P.scan.n_ch);
+        for (int m = 0; m < KP; ++m) acc_s[m * blockDim.x + tid] = (R)0;
+
+        RaySetup s;
+        ray_setup<false>(P, v, 0, c, s);
+        R seglen = (R)0;
+        if (s.hit) {
+            const bool mpos = s.m >= 0.0;
+            const int pitch = s.xmajor ? P.pitch_xm : P.pitch_ym;
+            const uint16_t *W = P.skip[(s.xmajor ? 0 : 2) + (mpos ? 0 : 1)] + (mpos ? s.j_c : s.nq - 1 - s.j_c) + 1;
+            const double c0 = mpos ? s.cq : 1.0 - s.cq;
+            walk_skip<R>(W, pitch, s.i0, s.i1, s.i_c, (R)fabs(s.m), (R)c0, (R)s.ua, (R)s.ub, (R)s.inv_am, acc_s + tid,
+                         (int)blockDim.x);
+            seglen = (R)s.seglen;
+        }
+
+        R out[MAX_SPEC];
+        if (KT > 0) {
+            R Lr[KT > 0 ? KT : 1];
 #pragma unroll
-    for (int sp = 0; sp < MAX_SPEC; ++sp) {
-        if (sp < d.nSpec) {
-            ((R *)d.counts)[sp * n_rays + ray] = out[sp];
-            if (d.logs) ((R *)d.logs)[sp * n_rays + ray] = neg_log_ratio<R>(out[sp], air_s[sp]);
+            for (int m = 0; m < (KT > 0 ? KT : 1); ++m) Lr[m] = acc_s[m * blockDim.x + tid] * seglen;
+            if (d.L_out) {
+                R *Lo = (R *)d.L_out + ray * d.K;
+#pragma unroll
+                for (int m = 0; m < (KT > 0 ? KT : 1); ++m)
+                    if (m < d.K) Lo[m] = Lr[m];
+            }
+            if constexpr (PACKED) detect_packed<KT, NSP>(Lr, mu2, W2, nE2, out);
+            else detect_reg<R, (KT > 0 ? KT : 1)>(Lr, mu_s, W_s, d.nE, d.nSpec, out);
+        } else {
+            for (int m = 0; m < d.K; ++m) acc_s[m * blockDim.x + tid] *= seglen;
+            if (d.L_out) {
+                R *Lo = (R *)d.L_out + ray * d.K;
+                for (int m = 0; m < d.K; ++m) Lo[m] = acc_s[m * blockDim.x + tid];
+            }
+            detect<R>(acc_s + tid, blockDim.x, d.K, mu_s, W_s, d.nE, d.nSpec, out);
+        }
+#pragma unroll
+        for (int sp = 0; sp < MAX_SPEC; ++sp) {
+            if (sp < d.nSpec) {
+                ((R *)d.counts)[sp * n_rays + ray] = out[sp];
+                if (d.logs) ((R *)d.logs)[sp * n_rays + ray] = neg_log_ratio<R>(out[sp], air_s[sp]);
+            }
         }
     }
 }
@@ -575,7 +680,7 @@ __global__ void siddon_trace_kernel(SiddonParams P, const int64_t *__restrict__ 
     const int r = (int)(line % P.scan.n_rows);
     const int v = (int)(line / P.scan.n_rows);
     RaySetup s;
-    ray_setup(P, v, r, c, s);
+    ray_setup<IS3D>(P, v, r, c, s);
     int n = 0;
     if (s.hit) {
         RayLoop<R> L;
@@ -622,14 +727,44 @@ static int make_params(const DexctScan *scan, const DexctVolume *vol, const void
     P.zdet = (const double *)(w + L.off_zdet);
     P.xm = (const uint16_t *)(w + L.off_xm); P.ym = (const uint16_t *)(w + L.off_ym);
     P.pitch_xm = L.pitch_xm; P.pitch_ym = L.pitch_ym; P.plane_xm = L.plane_xm; P.plane_ym = L.plane_ym;
+    P.inv_dx = 1.0 / vol->dx; P.inv_dy = 1.0 / vol->dy; P.inv_dz = 1.0 / vol->dz;
     const bool skip = L.has_skip && vol->nx + 1 <= SKIP_MAX_ENTRIES && vol->ny + 1 <= SKIP_MAX_ENTRIES;
     for (int a = 0; a < 4; ++a) P.skip[a] = skip ? (const uint16_t *)(w + L.off_skip[a]) : nullptr;
+    return DEXCT_OK;
+}
+
+template <typename R, int KT, int NSP>
+static int launch_skip(const SiddonParams &P, int view_begin, long long n_rays, const DetectArgs &d, cudaStream_t st)
+{
+    const int block = 128;
+    const int KP = KT > 0 ? KT : d.K;
+    const bool packed = sizeof(R) == 4 && KT > 0;
+    const int nE2 = (d.nE + 1) / 2;
+    const size_t tab = packed ? 8 * (size_t)nE2 * (KT + NSP) + sizeof(R) * MAX_SPEC
+                              : sizeof(R) * ((size_t)KP * d.nE + (size_t)d.nSpec * d.nE + MAX_SPEC);
+    const size_t smem = sizeof(R) * (size_t)KP * block + tab;
+    if (smem > 200 * 1024) {
+        set_error("material/energy tables need %zu bytes of shared memory (limit 200 KiB): K=%d nE=%d", smem, d.K, d.nE);
+        return DEXCT_ECAPACITY;
+    }
+    auto kern = siddon_skip_kernel<R, KT, NSP>;
+    if (smem > 48 * 1024) DEXCT_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    int per_sm = 0;
+    DEXCT_CUDA_OK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, block, smem));
+    if (per_sm < 1) per_sm = 1;
+    const long long n_blk = (n_rays + block - 1) / block;
+    const long long grid = std::min<long long>(n_blk, (long long)sm_count() * per_sm);     // resident CTAs stride over ray blocks
+    kern<<<(unsigned)grid, block, smem, st>>>(P, view_begin, n_rays, d);
+    DEXCT_CUDA_OK(cudaGetLastError());
     return DEXCT_OK;
 }
 
 template <typename R, bool IS3D, int KT>
 static int launch_poly(const SiddonParams &P, int view_begin, long long n_rays, const DetectArgs &d, cudaStream_t st)
 {
+    // 2-D scans with 7-bit labels walk the skip layouts
+    if (!IS3D && P.skip[0] != nullptr && d.K <= 128)
+        return d.nSpec <= 2 ? launch_skip<R, KT, 2>(P, view_begin, n_rays, d, st) : launch_skip<R, KT, 4>(P, view_begin, n_rays, d, st);
     const int block = 128;
     const int KP = KT > 0 ? KT : d.K;
     const size_t smem = sizeof(R) * ((size_t)KP * block + (size_t)KP * d.nE + (size_t)d.nSpec * d.nE + MAX_SPEC);
@@ -637,9 +772,7 @@ static int launch_poly(const SiddonParams &P, int view_begin, long long n_rays, 
         set_error("material/energy tables need %zu bytes of shared memory (limit 200 KiB): K=%d nE=%d", smem, d.K, d.nE);
         return DEXCT_ECAPACITY;
     }
-    // 2-D scans with 7-bit labels walk the skip layouts
-    const bool use_skip = !IS3D && P.skip[0] != nullptr && d.K <= 128;
-    auto kern = use_skip ? siddon_skip_kernel<R, KT> : siddon_poly_kernel<R, IS3D, KT>;
+    auto kern = siddon_poly_kernel<R, IS3D, KT>;
     if (smem > 48 * 1024) DEXCT_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     const long long grid = (n_rays + block - 1) / block;
     kern<<<(unsigned)grid, block, smem, st>>>(P, view_begin, n_rays, d);

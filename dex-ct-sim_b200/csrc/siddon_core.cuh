@@ -68,6 +68,7 @@ struct SiddonParams {
     const uint16_t *skip[4];          // skip layouts (2-D only; null otherwise); element (i, j) at (i*pitch + (j+1))
     int pitch_xm, pitch_ym;
     long long plane_xm, plane_ym;
+    double inv_dx, inv_dy, inv_dz;    // 1/voxel size, rounded once on the host
 };
 
 // Per-ray constants, computed in double with one rounding per operation (the CPU twin does the same).
@@ -85,42 +86,56 @@ struct RaySetup {
 
 #define DEXCT_BIG 1e30
 
+// Divisions are few on purpose (one reciprocal of the major step, one of the slope, one for the length): everything else
+// multiplies by a reciprocal, in the same order as oracle/siddon_oracle.c slab_setup().  IS3D = false compiles the z part
+// out; the values it would produce for a single-slice scan (mz = 0, k_c = 0, cw = 1/2) are set directly.
+template <bool IS3D>
 __device__ __forceinline__ void ray_setup(const SiddonParams &P, int v, int r, int c, RaySetup &s)
 {
     typedef Rn<double> D;
     const double cb = P.cosb[v], sb = P.sinb[v], cg = P.cosg[c], sg = P.sing[c];
     const double ex = D::sub(D::mul(cb, cg), D::mul(sb, sg));
     const double ey = D::add(D::mul(sb, cg), D::mul(cb, sg));
-    const double Sx = D::mul(P.scan.sid, cb), Sy = D::mul(P.scan.sid, sb), Sz = 0.0;
-    const double Dx = -D::mul(P.scan.sdd, ex), Dy = -D::mul(P.scan.sdd, ey), Dz = P.zdet[r];
-    const double gx = D::div(Dx, P.vol.dx), gy = D::div(Dy, P.vol.dy), gz = D::div(Dz, P.vol.dz);
+    const double Sx = D::mul(P.scan.sid, cb), Sy = D::mul(P.scan.sid, sb);
+    const double Dx = -D::mul(P.scan.sdd, ex), Dy = -D::mul(P.scan.sdd, ey), Dz = IS3D ? P.zdet[r] : 0.0;
+    const double gx = D::mul(Dx, P.inv_dx), gy = D::mul(Dy, P.inv_dy), gz = IS3D ? D::mul(Dz, P.inv_dz) : 0.0;
     double gp, gq, pS, qS;
     s.hit = false;
     s.xmajor = fabs(gx) >= fabs(gy);
-    if (s.xmajor) { gp = gx; gq = gy; pS = D::div(Sx, P.vol.dx); qS = D::div(Sy, P.vol.dy); s.np = P.vol.nx; s.nq = P.vol.ny; }
-    else          { gp = gy; gq = gx; pS = D::div(Sy, P.vol.dy); qS = D::div(Sx, P.vol.dx); s.np = P.vol.ny; s.nq = P.vol.nx; }
-    const double wS = D::div(Sz, P.vol.dz);
-    s.m = D::div(gq, gp);
-    s.mz = D::div(gz, gp);
+    if (s.xmajor) { gp = gx; gq = gy; pS = D::mul(Sx, P.inv_dx); qS = D::mul(Sy, P.inv_dy); s.np = P.vol.nx; s.nq = P.vol.ny; }
+    else          { gp = gy; gq = gx; pS = D::mul(Sy, P.inv_dy); qS = D::mul(Sx, P.inv_dx); s.np = P.vol.ny; s.nq = P.vol.nx; }
+    const double inv_gp = D::div(1.0, gp);
+    s.m = D::mul(gq, inv_gp);
+    s.mz = IS3D ? D::mul(gz, inv_gp) : 0.0;
     const double q0 = D::sub(qS, D::mul(s.m, pS));
-    const double w0 = D::sub(wS, D::mul(s.mz, pS));
+    const double w0 = IS3D ? D::sub(0.0, D::mul(s.mz, pS)) : 0.0;         // the source sits in the z = 0 plane
     const double hp = D::mul(0.5, (double)s.np), hq = D::mul(0.5, (double)s.nq), hw = D::mul(0.5, (double)P.vol.nz);
     const double pe = D::add(pS, gp);
     double pa = pS < pe ? pS : pe, pb = pS < pe ? pe : pS;
     if (pa < -hp) pa = -hp;
     if (pb > hp) pb = hp;
+    s.inv_am = DEXCT_BIG;
+    s.inv_amz = DEXCT_BIG;
     if (s.m != 0.0) {
-        const double t1 = D::div(D::sub(-hq, q0), s.m), t2 = D::div(D::sub(hq, q0), s.m);
+        const double inv_m = D::div(1.0, s.m);
+        const double t1 = D::mul(D::sub(-hq, q0), inv_m), t2 = D::mul(D::sub(hq, q0), inv_m);
         const double lo = t1 < t2 ? t1 : t2, hi = t1 < t2 ? t2 : t1;
         if (lo > pa) pa = lo;
         if (hi < pb) pb = hi;
+        s.inv_am = fabs(inv_m);
+        if (s.inv_am > DEXCT_BIG) s.inv_am = DEXCT_BIG;
     } else if (!(q0 >= -hq && q0 < hq)) return;
-    if (s.mz != 0.0) {
-        const double t1 = D::div(D::sub(-hw, w0), s.mz), t2 = D::div(D::sub(hw, w0), s.mz);
-        const double lo = t1 < t2 ? t1 : t2, hi = t1 < t2 ? t2 : t1;
-        if (lo > pa) pa = lo;
-        if (hi < pb) pb = hi;
-    } else if (!(w0 >= -hw && w0 < hw)) return;
+    if (IS3D) {
+        if (s.mz != 0.0) {
+            const double inv_mz = D::div(1.0, s.mz);
+            const double t1 = D::mul(D::sub(-hw, w0), inv_mz), t2 = D::mul(D::sub(hw, w0), inv_mz);
+            const double lo = t1 < t2 ? t1 : t2, hi = t1 < t2 ? t2 : t1;
+            if (lo > pa) pa = lo;
+            if (hi < pb) pb = hi;
+            s.inv_amz = fabs(inv_mz);
+            if (s.inv_amz > DEXCT_BIG) s.inv_amz = DEXCT_BIG;
+        } else if (!(w0 >= -hw && w0 < hw)) return;
+    }
     if (!(pa < pb)) return;
     const double ua = D::add(pa, hp), ub = D::add(pb, hp);          // column coordinates in [0, np]
     int i0 = (int)floor(ua), i1 = (int)ceil(ub) - 1;
@@ -132,20 +147,22 @@ __device__ __forceinline__ void ray_setup(const SiddonParams &P, int v, int r, i
     s.i_c = (i0 + i1 + 1) / 2;
     const double pc = D::sub((double)s.i_c, hp);
     const double qfull = D::add(D::mul(s.m, pc), D::add(q0, hq));   // minor index coordinate at column boundary i_c
-    const double wfull = D::add(D::mul(s.mz, pc), D::add(w0, hw));
-    const double qfl = floor(qfull), wfl = floor(wfull);
-    s.j_c = (int)qfl; s.k_c = (int)wfl;
+    const double qfl = floor(qfull);
+    s.j_c = (int)qfl;
     s.cq = D::sub(qfull, qfl);
-    s.cw = D::sub(wfull, wfl);
+    if (IS3D) {
+        const double wfull = D::add(D::mul(s.mz, pc), D::add(w0, hw));
+        const double wfl = floor(wfull);
+        s.k_c = (int)wfl;
+        s.cw = D::sub(wfull, wfl);
+    } else {
+        s.k_c = 0;
+        s.cw = 0.5;
+    }
     s.ua = D::sub(ua, (double)s.i_c);
     s.ub = D::sub(ub, (double)s.i_c);
-    const double am = fabs(s.m), amz = fabs(s.mz);
-    s.inv_am = am > 0.0 ? D::div(1.0, am) : DEXCT_BIG;
-    if (s.inv_am > DEXCT_BIG) s.inv_am = DEXCT_BIG;
-    s.inv_amz = amz > 0.0 ? D::div(1.0, amz) : DEXCT_BIG;
-    if (s.inv_amz > DEXCT_BIG) s.inv_amz = DEXCT_BIG;
     const double len2 = D::add(D::add(D::mul(Dx, Dx), D::mul(Dy, Dy)), D::mul(Dz, Dz));
-    s.seglen = D::div(__dsqrt_rn(len2), fabs(gp));
+    s.seglen = D::mul(__dsqrt_rn(len2), fabs(inv_gp));
     s.hit = true;
 }
 

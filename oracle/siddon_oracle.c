@@ -297,38 +297,53 @@ typedef struct {
 
 #define DEXO_BIG 1e30
 
+/* Few divisions on purpose (the device pays ~15 instructions for each): one reciprocal of the major step, one of each
+ * slope, everything else multiplies by a reciprocal -- operation for operation as ray_setup() in siddon_core.cuh.     */
 static void slab_setup(const dexo_setup *g, int v, int r, int c, slab_ray *s)
 {
     double S[3], D[3];
     ray_endpoints(g, v, r, c, S, D);
-    const double gx = D[0] / g->dx, gy = D[1] / g->dy, gz = D[2] / g->dz;
+    const int is3d = scan_is_3d(g);
+    const double inv_dx = 1.0 / g->dx, inv_dy = 1.0 / g->dy, inv_dz = 1.0 / g->dz;
+    if (!is3d) D[2] = 0.0;
+    const double gx = D[0] * inv_dx, gy = D[1] * inv_dy, gz = is3d ? D[2] * inv_dz : 0.0;
     double gp, gq, pS, qS;
     s->hit = 0;
     s->xmajor = fabs(gx) >= fabs(gy);
-    if (s->xmajor) { gp = gx; gq = gy; pS = S[0] / g->dx; qS = S[1] / g->dy; s->np = g->nx; s->nq = g->ny; }
-    else           { gp = gy; gq = gx; pS = S[1] / g->dy; qS = S[0] / g->dx; s->np = g->ny; s->nq = g->nx; }
-    const double wS = S[2] / g->dz;
-    s->m = gq / gp;
-    s->mz = gz / gp;
+    if (s->xmajor) { gp = gx; gq = gy; pS = S[0] * inv_dx; qS = S[1] * inv_dy; s->np = g->nx; s->nq = g->ny; }
+    else           { gp = gy; gq = gx; pS = S[1] * inv_dy; qS = S[0] * inv_dx; s->np = g->ny; s->nq = g->nx; }
+    const double inv_gp = 1.0 / gp;
+    s->m = gq * inv_gp;
+    s->mz = is3d ? gz * inv_gp : 0.0;
     const double q0 = qS - s->m * pS;
-    const double w0 = wS - s->mz * pS;
+    const double w0 = is3d ? 0.0 - s->mz * pS : 0.0;
     const double hp = 0.5 * (double)s->np, hq = 0.5 * (double)s->nq, hw = 0.5 * (double)g->nz;
     double pe = pS + gp;
     double pa = pS < pe ? pS : pe, pb = pS < pe ? pe : pS;
     if (pa < -hp) pa = -hp;
     if (pb > hp) pb = hp;
+    s->inv_am = DEXO_BIG;
+    s->inv_amz = DEXO_BIG;
     if (s->m != 0.0) {
-        double t1 = (-hq - q0) / s->m, t2 = (hq - q0) / s->m;
+        const double inv_m = 1.0 / s->m;
+        double t1 = (-hq - q0) * inv_m, t2 = (hq - q0) * inv_m;
         double lo = t1 < t2 ? t1 : t2, hi = t1 < t2 ? t2 : t1;
         if (lo > pa) pa = lo;
         if (hi < pb) pb = hi;
+        s->inv_am = fabs(inv_m);
+        if (s->inv_am > DEXO_BIG) s->inv_am = DEXO_BIG;
     } else if (!(q0 >= -hq && q0 < hq)) return;
-    if (s->mz != 0.0) {
-        double t1 = (-hw - w0) / s->mz, t2 = (hw - w0) / s->mz;
-        double lo = t1 < t2 ? t1 : t2, hi = t1 < t2 ? t2 : t1;
-        if (lo > pa) pa = lo;
-        if (hi < pb) pb = hi;
-    } else if (!(w0 >= -hw && w0 < hw)) return;
+    if (is3d) {
+        if (s->mz != 0.0) {
+            const double inv_mz = 1.0 / s->mz;
+            double t1 = (-hw - w0) * inv_mz, t2 = (hw - w0) * inv_mz;
+            double lo = t1 < t2 ? t1 : t2, hi = t1 < t2 ? t2 : t1;
+            if (lo > pa) pa = lo;
+            if (hi < pb) pb = hi;
+            s->inv_amz = fabs(inv_mz);
+            if (s->inv_amz > DEXO_BIG) s->inv_amz = DEXO_BIG;
+        } else if (!(w0 >= -hw && w0 < hw)) return;
+    }
     if (!(pa < pb)) return;
     const double ua = pa + hp, ub = pb + hp;
     int i0 = (int)floor(ua), i1 = (int)ceil(ub) - 1;
@@ -340,19 +355,21 @@ static void slab_setup(const dexo_setup *g, int v, int r, int c, slab_ray *s)
     s->i_c = (i0 + i1 + 1) / 2;
     const double pc = (double)s->i_c - hp;
     const double qfull = s->m * pc + (q0 + hq);
-    const double wfull = s->mz * pc + (w0 + hw);
-    const double qfl = floor(qfull), wfl = floor(wfull);
-    s->j_c = (int)qfl; s->k_c = (int)wfl;
+    const double qfl = floor(qfull);
+    s->j_c = (int)qfl;
     s->cq = qfull - qfl;
-    s->cw = wfull - wfl;
+    if (is3d) {
+        const double wfull = s->mz * pc + (w0 + hw);
+        const double wfl = floor(wfull);
+        s->k_c = (int)wfl;
+        s->cw = wfull - wfl;
+    } else {
+        s->k_c = 0;
+        s->cw = 0.5;
+    }
     s->ua = ua - (double)s->i_c;
     s->ub = ub - (double)s->i_c;
-    double am = fabs(s->m), amz = fabs(s->mz);
-    s->inv_am = am > 0.0 ? 1.0 / am : DEXO_BIG;
-    if (s->inv_am > DEXO_BIG) s->inv_am = DEXO_BIG;
-    s->inv_amz = amz > 0.0 ? 1.0 / amz : DEXO_BIG;
-    if (s->inv_amz > DEXO_BIG) s->inv_amz = DEXO_BIG;
-    s->seglen = sqrt(D[0] * D[0] + D[1] * D[1] + D[2] * D[2]) / fabs(gp);
+    s->seglen = sqrt(D[0] * D[0] + D[1] * D[1] + D[2] * D[2]) * fabs(inv_gp);
     s->hit = 1;
 }
 
