@@ -12,6 +12,25 @@ void set_error(const char *fmt, ...);
 int check_device();          // DEXCT_OK or DEXCT_ENODEVICE (message set)
 int sm_count();
 
+// Exclusive use of one __constant__ table ("slot") of the library on the current device, across host threads and CUDA
+// streams: the constructor takes a host mutex and makes `stream` wait for the previous user of the slot; the caller then
+// enqueues  [fill staging] -> cudaMemcpyToSymbolAsync -> [kernel reading the table]  on `stream`; the destructor records
+// the completion event and releases the mutex.  staging() is a library-owned 64 KiB device buffer of that slot.
+enum { SLOT_GN = 0, SLOT_SIDDON = 1, SLOT_COUNT = 2 };
+constexpr size_t SLOT_STAGING_BYTES = 64 * 1024;
+class ConstSlot {
+public:
+    ConstSlot(int slot, cudaStream_t stream);
+    ~ConstSlot();
+    bool ok() const { return ok_; }
+    void *staging() const { return staging_; }
+private:
+    int slot_, dev_;
+    cudaStream_t stream_;
+    bool ok_;
+    void *staging_;
+};
+
 #define DEXCT_CUDA_OK(expr)                                                                        \
     do {                                                                                           \
         cudaError_t e__ = (expr);                                                                  \

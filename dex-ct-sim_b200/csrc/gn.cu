@@ -12,10 +12,28 @@
 // Every thread of a warp reads the same row (broadcast LDS.128), so the kernel is bound by the FP32 FMA pipe:
 // 14 FMA + 1 MUFU.EX2 per pixel, energy and iteration.  PX pixels per thread share each row load.
 #include "common.cuh"
+#include <stdlib.h>
 
 namespace dexct {
 
-constexpr int GN_ROW = 16;   // floats per table row (14 used), 64 B so a row is four LDS.128
+constexpr int GN_ROW = 16;
+
+// Packed single-precision pairs (FFMA2 on sm_100a: two FMAs per issue slot).
+typedef unsigned long long f32x2;
+__device__ __forceinline__ f32x2 pack2(float x, float y)
+{
+    f32x2 r;
+    asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(x), "f"(y));
+    return r;
+}
+__device__ __forceinline__ void unpack2(f32x2 v, float &x, float &y) { asm("mov.b64 {%0, %1}, %2;" : "=f"(x), "=f"(y) : "l"(v)); }
+template <typename T> __device__ __forceinline__ void unpack2(f32x2, T &, T &) {}      // never called: double path
+__device__ __forceinline__ f32x2 ffma2(f32x2 a, f32x2 b, f32x2 c)
+{
+    f32x2 r;
+    asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(r) : "l"(a), "l"(b), "l"(c));
+    return r;
+}   // floats per table row (14 used), 64 B so a row is four LDS.128
 
 template <typename R> struct GnMath;
 template <> struct GnMath<float> {
@@ -80,23 +98,58 @@ template <> __device__ __forceinline__ double decode_max<double>(const void *s)
     return __longlong_as_double(k);
 }
 
-template <typename R, int PX>
+// Single precision keeps the table in the constant bank: every thread of a warp reads the same row, and uniform loads
+// (LDCU.128 into uniform registers, consumed directly by FFMA2) cost no shared-memory bandwidth -- measured with
+// tools/microbench/fma_pipe.cu, four broadcast LDS.128 per row alone take as long as the row's twelve FFMA2.
+constexpr int GN_CTAB_ROWS = 512;                             // nE + 2 zero rows must fit: nE <= 510
+__constant__ ulonglong2 gn_ctab[GN_CTAB_ROWS * (GN_ROW / 4)];
+
+// Rows of the packed single-precision table (see the header comment), followed by two zero rows.
+__global__ void gn_table_kernel(const float *__restrict__ i0, const float *__restrict__ mus, int nE, float *__restrict__ tab)
+{
+    const int e = blockIdx.x * blockDim.x + threadIdx.x;
+    if (e >= nE + 2) return;
+    float *row = tab + e * GN_ROW;
+    if (e >= nE) {
+#pragma unroll
+        for (int q = 0; q < GN_ROW; ++q) row[q] = 0.f;
+        return;
+    }
+    const float m1 = mus[e], m2 = mus[nE + e], s1 = i0[e], s2 = i0[nE + e];
+    row[0] = -m1 * GnMath<float>::scale; row[1] = -m2 * GnMath<float>::scale;
+    const float f[6] = {1.f, m1, m2, m1 * m1, m1 * m2, m2 * m2};
+#pragma unroll
+    for (int q = 0; q < 6; ++q) { row[2 + 2 * q] = s1 * f[q]; row[3 + 2 * q] = s2 * f[q]; }
+    row[14] = 0.f; row[15] = 0.f;
+}
+
+template <typename R, int PX, bool CTAB>
 __global__ void __launch_bounds__(256) gn_kernel(const R *__restrict__ g, const R *__restrict__ i0, const R *__restrict__ mus,
                                                  int nE, long long P, int n_iters, R mask_thresh, const void *scratch,
                                                  R *__restrict__ a_out)
 {
     typedef GnMath<R> M;
+    constexpr bool PACKED = sizeof(R) == 4;
     extern __shared__ __align__(16) unsigned char smem_raw[];
     R *tab = (R *)smem_raw;                                   // [nE][GN_ROW]
-    for (int e = threadIdx.x; e < nE; e += blockDim.x) {
+    for (int e = threadIdx.x; !CTAB && e < nE; e += blockDim.x) {
         const R m1 = mus[e], m2 = mus[nE + e], s1 = i0[e], s2 = i0[nE + e];
         R *row = tab + e * GN_ROW;
         row[0] = -m1 * M::scale; row[1] = -m2 * M::scale;
-        row[2] = s1; row[3] = s1 * m1; row[4] = s1 * m2; row[5] = s1 * (m1 * m1); row[6] = s1 * (m1 * m2); row[7] = s1 * (m2 * m2);
-        row[8] = s2; row[9] = s2 * m1; row[10] = s2 * m2; row[11] = s2 * (m1 * m1); row[12] = s2 * (m1 * m2); row[13] = s2 * (m2 * m2);
+        const R f[6] = {(R)1, m1, m2, m1 * m1, m1 * m2, m2 * m2};
+        if (PACKED) {                     // (measurement 1, measurement 2) pairs: one FFMA2 per moment
+#pragma unroll
+            for (int q = 0; q < 6; ++q) { row[2 + 2 * q] = s1 * f[q]; row[3 + 2 * q] = s2 * f[q]; }
+        } else {
+#pragma unroll
+            for (int q = 0; q < 6; ++q) { row[2 + q] = s1 * f[q]; row[8 + q] = s2 * f[q]; }
+        }
         row[14] = (R)0; row[15] = (R)0;
     }
-    __syncthreads();
+    if (!CTAB) {
+        for (int t = threadIdx.x; t < 2 * GN_ROW; t += blockDim.x) tab[nE * GN_ROW + t] = (R)0;  // two zero rows (pipelined loop)
+        __syncthreads();
+    }
 
     const long long stride = (long long)gridDim.x * blockDim.x;
     const R thr = mask_thresh > (R)0 ? mask_thresh * decode_max<R>(scratch) : (R)INFINITY;
@@ -113,6 +166,72 @@ __global__ void __launch_bounds__(256) gn_kernel(const R *__restrict__ g, const 
         }
         for (int it = 0; it < n_iters; ++it) {
             R acc[PX][12];
+            if constexpr (PACKED) {
+                // FFMA2 (sm_100a): accumulator pair q = (measurement 1, measurement 2) of moment q; att is broadcast
+                f32x2 acc2[PX][6];
+#pragma unroll
+                for (int k = 0; k < PX; ++k)
+#pragma unroll
+                    for (int q = 0; q < 6; ++q) acc2[k][q] = 0ull;
+                // Software pipeline over energy pairs: the exponentials of the NEXT bin are issued before the twelve
+                // FFMA2 of the current one, so MUFU and LDS latency hide behind the FMA pipe.  The table carries two
+                // zero rows past nE (i0 = 0: no contribution), which keeps the loop free of tails and bounds checks.
+                const ulonglong2 *rows = (const ulonglong2 *)tab;
+                ulonglong2 rA[4], rB[4];
+                float attA[PX], attB[PX];
+                auto load_row = [&](int e, ulonglong2(&r)[4]) {
+#pragma unroll
+                    for (int q = 0; q < 4; ++q) r[q] = CTAB ? gn_ctab[e * (GN_ROW / 4) + q] : rows[e * (GN_ROW / 4) + q];
+                };
+                auto exps = [&](const ulonglong2(&r)[4], float(&att)[PX]) {
+                    float t0, t1;
+                    unpack2(r[0].x, t0, t1);
+#pragma unroll
+                    for (int k = 0; k < PX; ++k) att[k] = M::att(fmaf(a2[k], t1, a1[k] * t0));
+                };
+                auto accum = [&](const ulonglong2(&r)[4], const float(&att)[PX]) {
+#pragma unroll
+                    for (int k = 0; k < PX; ++k) {
+                        const f32x2 att2 = pack2(att[k], att[k]);
+                        acc2[k][0] = ffma2(r[0].y, att2, acc2[k][0]);
+                        acc2[k][1] = ffma2(r[1].x, att2, acc2[k][1]);
+                        acc2[k][2] = ffma2(r[1].y, att2, acc2[k][2]);
+                        acc2[k][3] = ffma2(r[2].x, att2, acc2[k][3]);
+                        acc2[k][4] = ffma2(r[2].y, att2, acc2[k][4]);
+                        acc2[k][5] = ffma2(r[3].x, att2, acc2[k][5]);
+                    }
+                };
+                if constexpr (CTAB) {
+                    // constant-bank rows live in uniform registers, which cannot be carried round the loop: take
+                    // the bins two at a time (the zero rows make an odd nE harmless) and let the other warps cover
+                    // the MUFU latency
+#pragma unroll 1
+                    for (int e = 0; e < nE; e += 2) {
+                        load_row(e, rA);
+                        load_row(e + 1, rB);
+                        exps(rA, attA);
+                        exps(rB, attB);
+                        accum(rA, attA);
+                        accum(rB, attB);
+                    }
+                } else {
+                    load_row(0, rA);
+                    exps(rA, attA);
+#pragma unroll 1
+                    for (int e = 0; e < nE; e += 2) {
+                        load_row(e + 1, rB);
+                        exps(rB, attB);
+                        accum(rA, attA);
+                        load_row(e + 2, rA);
+                        exps(rA, attA);
+                        accum(rB, attB);
+                    }
+                }
+#pragma unroll
+                for (int k = 0; k < PX; ++k)
+#pragma unroll
+                    for (int q = 0; q < 6; ++q) unpack2(acc2[k][q], acc[k][q], acc[k][6 + q]);
+            } else {
 #pragma unroll
             for (int k = 0; k < PX; ++k)
 #pragma unroll
@@ -129,6 +248,7 @@ __global__ void __launch_bounds__(256) gn_kernel(const R *__restrict__ g, const 
 #pragma unroll
                     for (int q = 0; q < 12; ++q) acc[k][q] = M::fma(t[2 + q], att, acc[k][q]);
                 }
+            }
             }
 #pragma unroll
             for (int k = 0; k < PX; ++k) {
@@ -185,12 +305,14 @@ static int launch_gn(const void *g, const void *i0, const void *mus, int nE, lon
                      void *a_out, void *scratch, bool have_max, cudaStream_t st)
 {
     const int block = 256;
-    const size_t smem = sizeof(R) * (size_t)nE * GN_ROW;
+    const bool ctab = sizeof(R) == 4 && nE + 2 <= GN_CTAB_ROWS;
+    const size_t smem = ctab ? 0 : sizeof(R) * (size_t)(nE + 2) * GN_ROW;
     if (smem > 200 * 1024) {
         set_error("GN table needs %zu bytes of shared memory (limit 200 KiB): nE=%d", smem, nE);
         return DEXCT_ECAPACITY;
     }
-    auto kern = gn_kernel<R, PX>;
+    void (*kern)(const R *, const R *, const R *, int, long long, int, R, const void *, R *) = gn_kernel<R, PX, false>;
+    if (ctab) kern = gn_kernel<R, PX, sizeof(R) == 4>;
     if (smem > 48 * 1024) DEXCT_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     int per_sm = 0;
     DEXCT_CUDA_OK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, block, smem));
@@ -200,6 +322,18 @@ static int launch_gn(const void *g, const void *i0, const void *mus, int nE, lon
     if (grid > want) grid = want;
     if (mask_thresh > 0 && !have_max) {
         if (int e = launch_max<R>(g, P, scratch, st)) return e;
+    }
+    if (ctab) {
+        ConstSlot slot(SLOT_GN, st);                          // exclusive use of gn_ctab until the kernel below has run
+        if (!slot.ok()) return DEXCT_ECUDA;
+        gn_table_kernel<<<(nE + 2 + 127) / 128, 128, 0, st>>>((const float *)i0, (const float *)mus, nE, (float *)slot.staging());
+        DEXCT_CUDA_OK(cudaGetLastError());
+        DEXCT_CUDA_OK(cudaMemcpyToSymbolAsync(gn_ctab, slot.staging(), sizeof(float) * (size_t)(nE + 2) * GN_ROW, 0,
+                                              cudaMemcpyDeviceToDevice, st));
+        kern<<<(unsigned)grid, block, smem, st>>>((const R *)g, (const R *)i0, (const R *)mus, nE, P, n_iters, (R)mask_thresh,
+                                                 scratch, (R *)a_out);
+        DEXCT_CUDA_OK(cudaGetLastError());
+        return DEXCT_OK;
     }
     kern<<<(unsigned)grid, block, smem, st>>>((const R *)g, (const R *)i0, (const R *)mus, nE, P, n_iters, (R)mask_thresh,
                                              scratch, (R *)a_out);
@@ -232,6 +366,13 @@ extern "C" int dexct_gn_decompose(const void *g, const void *i0, const void *mus
     if (P == 0) return DEXCT_OK;
     cudaStream_t st = (cudaStream_t)stream;
     const bool have = scratch_has_max != 0;
-    if (dtype == DEXCT_F32) return launch_gn<float, 2>(g, i0, mus, nE, P, n_iters, mask_thresh, a_out, scratch, have, st);
+    if (dtype == DEXCT_F32) {
+        const char *px = getenv("DEXCT_GN_PX");          // tuning knob (pixels per thread)
+        const int npx = px ? atoi(px) : 2;
+        if (npx == 1) return launch_gn<float, 1>(g, i0, mus, nE, P, n_iters, mask_thresh, a_out, scratch, have, st);
+        if (npx == 3) return launch_gn<float, 3>(g, i0, mus, nE, P, n_iters, mask_thresh, a_out, scratch, have, st);
+        if (npx == 4) return launch_gn<float, 4>(g, i0, mus, nE, P, n_iters, mask_thresh, a_out, scratch, have, st);
+        return launch_gn<float, 2>(g, i0, mus, nE, P, n_iters, mask_thresh, a_out, scratch, have, st);
+    }
     return launch_gn<double, 1>(g, i0, mus, nE, P, n_iters, mask_thresh, a_out, scratch, have, st);
 }

@@ -1,6 +1,7 @@
 // Error string, device checks and the version entry point of libdexct.so.
 #include "common.cuh"
 #include <string.h>
+#include <mutex>
 
 namespace dexct {
 
@@ -59,6 +60,45 @@ int sm_count()
         dev_cached = dev;
     }
     return sms;
+}
+
+namespace {
+constexpr int MAX_DEV = 64;
+struct SlotState {
+    std::mutex mtx;
+    cudaEvent_t ev[MAX_DEV] = {};
+    void *staging[MAX_DEV] = {};
+};
+SlotState g_slots[SLOT_COUNT];
+}  // namespace
+
+ConstSlot::ConstSlot(int slot, cudaStream_t stream) : slot_(slot), dev_(0), stream_(stream), ok_(false), staging_(nullptr)
+{
+    SlotState &S = g_slots[slot_];
+    S.mtx.lock();
+    if (cudaGetDevice(&dev_) != cudaSuccess || dev_ < 0 || dev_ >= MAX_DEV) {
+        set_error("ConstSlot: cannot identify the current device");
+        return;
+    }
+    if (!S.ev[dev_]) {
+        if (cudaEventCreateWithFlags(&S.ev[dev_], cudaEventDisableTiming) != cudaSuccess ||
+            cudaMalloc(&S.staging[dev_], SLOT_STAGING_BYTES) != cudaSuccess) {
+            set_error("ConstSlot: cannot create the table staging buffer: %s", cudaGetErrorString(cudaGetLastError()));
+            return;
+        }
+    } else if (cudaStreamWaitEvent(stream_, S.ev[dev_], 0) != cudaSuccess) {
+        set_error("ConstSlot: cudaStreamWaitEvent failed: %s", cudaGetErrorString(cudaGetLastError()));
+        return;
+    }
+    staging_ = S.staging[dev_];
+    ok_ = true;
+}
+
+ConstSlot::~ConstSlot()
+{
+    SlotState &S = g_slots[slot_];
+    if (ok_) cudaEventRecord(S.ev[dev_], stream_);
+    S.mtx.unlock();
 }
 
 }  // namespace dexct
