@@ -39,8 +39,11 @@ def test_version_and_workspace_size_need_no_gpu():
     scan = make_scan(1000, 900, 0.8230337, 60.0, 100.0)
     vol = N.DexctVolume(512, 512, 1, 0, 0.1, 0.1, 0.1)
     nbytes = L.dexct_siddon_workspace_bytes(C.byref(scan), C.byref(vol))
-    # two padded uint16 layouts of 3 planes each + small tables
-    assert 2 * 3 * 512 * 514 * 2 <= nbytes < 2 * 3 * 512 * 530 * 2 + 64 * 1024
+    # two padded uint16 pair layouts of 3 planes each + four one-plane skip layouts (2-D scan) + small tables
+    assert (2 * 3 + 4) * 512 * 514 * 2 <= nbytes < (2 * 3 + 4) * 512 * 530 * 2 + 64 * 1024
+    vol3 = N.DexctVolume(512, 512, 4, 0, 0.1, 0.1, 0.1)
+    n3 = L.dexct_siddon_workspace_bytes(C.byref(scan), C.byref(vol3))
+    assert 2 * 6 * 512 * 514 * 2 <= n3 < 2 * 6 * 512 * 530 * 2 + 64 * 1024      # 3-D: pair layouts only
     bad = N.DexctVolume(0, 512, 1, 0, 0.1, 0.1, 0.1)
     assert L.dexct_siddon_workspace_bytes(C.byref(scan), C.byref(bad)) == 0
 
