@@ -99,28 +99,34 @@ template <> __device__ __forceinline__ double decode_max<double>(const void *s)
 }
 
 // Single precision keeps the table in the constant bank: every thread of a warp reads the same row, and uniform loads
-// (LDCU.128 into uniform registers, consumed directly by FFMA2) cost no shared-memory bandwidth -- measured with
-// tools/microbench/fma_pipe.cu, four broadcast LDS.128 per row alone take as long as the row's twelve FFMA2.
+// (LDCU into uniform registers, consumed directly by FFMA2) cost no shared-memory bandwidth -- measured with
+// tools/microbench/gn_mix.cu (profiles/r01f_gn_mix_microbench.txt): a row fed from registers runs at 12-13 cycles per
+// (pixel, energy) and SMSP, from the constant bank at 17, from shared memory (four broadcast LDS.128) at 22.
+// Two tables, so that the exponentials of the NEXT bin can be issued ahead of the FFMA2 of the current one (software
+// pipeline, the microbenchmark's "pipelined" rows): the exponent pair of a bin, and its six moment pairs.
 constexpr int GN_CTAB_ROWS = 512;                             // nE + 2 zero rows must fit: nE <= 510
-__constant__ ulonglong2 gn_ctab[GN_CTAB_ROWS * (GN_ROW / 4)];
+constexpr int GN_CROW = 12;                                   // floats per moment row: 6 (measurement 1, measurement 2) pairs
+__constant__ ulonglong2 gn_ctab[GN_CTAB_ROWS * (GN_CROW / 4)];
+__constant__ f32x2 gn_cexp[GN_CTAB_ROWS];
 
-// Rows of the packed single-precision table (see the header comment), followed by two zero rows.
+// Staging image of both tables: [nE + 2][12] moment rows, then [nE + 2][2] exponent pairs; the two rows past nE are zero.
 __global__ void gn_table_kernel(const float *__restrict__ i0, const float *__restrict__ mus, int nE, float *__restrict__ tab)
 {
     const int e = blockIdx.x * blockDim.x + threadIdx.x;
     if (e >= nE + 2) return;
-    float *row = tab + e * GN_ROW;
+    float *row = tab + e * GN_CROW;
+    float *ex = tab + (nE + 2) * GN_CROW + 2 * e;
     if (e >= nE) {
 #pragma unroll
-        for (int q = 0; q < GN_ROW; ++q) row[q] = 0.f;
+        for (int q = 0; q < GN_CROW; ++q) row[q] = 0.f;
+        ex[0] = ex[1] = 0.f;
         return;
     }
     const float m1 = mus[e], m2 = mus[nE + e], s1 = i0[e], s2 = i0[nE + e];
-    row[0] = -m1 * GnMath<float>::scale; row[1] = -m2 * GnMath<float>::scale;
+    ex[0] = -m1 * GnMath<float>::scale; ex[1] = -m2 * GnMath<float>::scale;
     const float f[6] = {1.f, m1, m2, m1 * m1, m1 * m2, m2 * m2};
 #pragma unroll
-    for (int q = 0; q < 6; ++q) { row[2 + 2 * q] = s1 * f[q]; row[3 + 2 * q] = s2 * f[q]; }
-    row[14] = 0.f; row[15] = 0.f;
+    for (int q = 0; q < 6; ++q) { row[2 * q] = s1 * f[q]; row[2 * q + 1] = s2 * f[q]; }
 }
 
 template <typename R, int PX, bool CTAB>
@@ -151,11 +157,15 @@ __global__ void __launch_bounds__(256) gn_kernel(const R *__restrict__ g, const 
         __syncthreads();
     }
 
-    const long long stride = (long long)gridDim.x * blockDim.x;
     const R thr = mask_thresh > (R)0 ? mask_thresh * decode_max<R>(scratch) : (R)INFINITY;
 
-    // grid-stride over groups of PX pixels; pixel p_k = base + k*stride keeps every global access coalesced
-    for (long long base = (long long)blockIdx.x * blockDim.x + threadIdx.x; base < P; base += stride * PX) {
+    // CTA-stride over groups of blockDim * PX pixels; pixel p_k = base + k * blockDim keeps every global access coalesced.
+    // The loop bounds are uniform across the CTA on purpose: inside a loop whose trip count depends on the thread the
+    // compiler may not use the uniform datapath, and the table reads fall back from LDCU to per-thread LDC (2x slower).
+    const long long stride = blockDim.x;
+    const long long n_groups = (P + stride * PX - 1) / (stride * PX);
+    for (long long grp = blockIdx.x; grp < n_groups; grp += gridDim.x) {
+        const long long base = grp * stride * PX + threadIdx.x;
         R a1[PX], a2[PX], g1[PX], g2[PX];
 #pragma unroll
         for (int k = 0; k < PX; ++k) {
@@ -181,7 +191,7 @@ __global__ void __launch_bounds__(256) gn_kernel(const R *__restrict__ g, const 
                 float attA[PX], attB[PX];
                 auto load_row = [&](int e, ulonglong2(&r)[4]) {
 #pragma unroll
-                    for (int q = 0; q < 4; ++q) r[q] = CTAB ? gn_ctab[e * (GN_ROW / 4) + q] : rows[e * (GN_ROW / 4) + q];
+                    for (int q = 0; q < 4; ++q) r[q] = rows[e * (GN_ROW / 4) + q];
                 };
                 auto exps = [&](const ulonglong2(&r)[4], float(&att)[PX]) {
                     float t0, t1;
@@ -202,17 +212,41 @@ __global__ void __launch_bounds__(256) gn_kernel(const R *__restrict__ g, const 
                     }
                 };
                 if constexpr (CTAB) {
-                    // constant-bank rows live in uniform registers, which cannot be carried round the loop: take
-                    // the bins two at a time (the zero rows make an odd nE harmless) and let the other warps cover
-                    // the MUFU latency
+                    // pipelined over bins: exponentials of bin e + 1 first, then the FFMA2 of bin e on its moment row
+                    float att[PX], nxt[PX];
+                    {
+                        float t0, t1;
+                        unpack2(gn_cexp[0], t0, t1);
+#pragma unroll
+                        for (int k = 0; k < PX; ++k) att[k] = M::att(fmaf(a2[k], t1, a1[k] * t0));
+                    }
+                    auto exps_c = [&](int e, float(&o)[PX]) {
+                        float t0, t1;
+                        unpack2(gn_cexp[e], t0, t1);
+#pragma unroll
+                        for (int k = 0; k < PX; ++k) o[k] = M::att(fmaf(a2[k], t1, a1[k] * t0));
+                    };
+                    auto accum_c = [&](int e, const float(&w)[PX]) {
+                        const ulonglong2 r0 = gn_ctab[e * 3], r1 = gn_ctab[e * 3 + 1], r2 = gn_ctab[e * 3 + 2];
+#pragma unroll
+                        for (int k = 0; k < PX; ++k) {
+                            const f32x2 att2 = pack2(w[k], w[k]);
+                            acc2[k][0] = ffma2(r0.x, att2, acc2[k][0]);
+                            acc2[k][1] = ffma2(r0.y, att2, acc2[k][1]);
+                            acc2[k][2] = ffma2(r1.x, att2, acc2[k][2]);
+                            acc2[k][3] = ffma2(r1.y, att2, acc2[k][3]);
+                            acc2[k][4] = ffma2(r2.x, att2, acc2[k][4]);
+                            acc2[k][5] = ffma2(r2.y, att2, acc2[k][5]);
+                        }
+                    };
+                    // two bins per trip (the zero rows past nE make an odd nE harmless); a rolled loop with a uniform
+                    // counter keeps the table reads on the uniform datapath (LDCU), which an unrolled one loses to LDC
 #pragma unroll 1
                     for (int e = 0; e < nE; e += 2) {
-                        load_row(e, rA);
-                        load_row(e + 1, rB);
-                        exps(rA, attA);
-                        exps(rB, attB);
-                        accum(rA, attA);
-                        accum(rB, attB);
+                        exps_c(e + 1, nxt);
+                        accum_c(e, att);
+                        exps_c(e + 2, att);
+                        accum_c(e + 1, nxt);
                     }
                 } else {
                     load_row(0, rA);
@@ -304,7 +338,8 @@ template <typename R, int PX>
 static int launch_gn(const void *g, const void *i0, const void *mus, int nE, long long P, int n_iters, double mask_thresh,
                      void *a_out, void *scratch, bool have_max, cudaStream_t st)
 {
-    const int block = 256;
+    const char *bs = getenv("DEXCT_GN_BLOCK");         // tuning knob (threads per CTA: 128 or 256)
+    const int block = (bs && atoi(bs) == 128) ? 128 : 256;
     const bool ctab = sizeof(R) == 4 && nE + 2 <= GN_CTAB_ROWS;
     const size_t smem = ctab ? 0 : sizeof(R) * (size_t)(nE + 2) * GN_ROW;
     if (smem > 200 * 1024) {
@@ -328,8 +363,10 @@ static int launch_gn(const void *g, const void *i0, const void *mus, int nE, lon
         if (!slot.ok()) return DEXCT_ECUDA;
         gn_table_kernel<<<(nE + 2 + 127) / 128, 128, 0, st>>>((const float *)i0, (const float *)mus, nE, (float *)slot.staging());
         DEXCT_CUDA_OK(cudaGetLastError());
-        DEXCT_CUDA_OK(cudaMemcpyToSymbolAsync(gn_ctab, slot.staging(), sizeof(float) * (size_t)(nE + 2) * GN_ROW, 0,
+        DEXCT_CUDA_OK(cudaMemcpyToSymbolAsync(gn_ctab, slot.staging(), sizeof(float) * (size_t)(nE + 2) * GN_CROW, 0,
                                               cudaMemcpyDeviceToDevice, st));
+        DEXCT_CUDA_OK(cudaMemcpyToSymbolAsync(gn_cexp, (const float *)slot.staging() + (size_t)(nE + 2) * GN_CROW,
+                                              sizeof(float) * (size_t)(nE + 2) * 2, 0, cudaMemcpyDeviceToDevice, st));
         kern<<<(unsigned)grid, block, smem, st>>>((const R *)g, (const R *)i0, (const R *)mus, nE, P, n_iters, (R)mask_thresh,
                                                  scratch, (R *)a_out);
         DEXCT_CUDA_OK(cudaGetLastError());
@@ -368,11 +405,11 @@ extern "C" int dexct_gn_decompose(const void *g, const void *i0, const void *mus
     const bool have = scratch_has_max != 0;
     if (dtype == DEXCT_F32) {
         const char *px = getenv("DEXCT_GN_PX");          // tuning knob (pixels per thread)
-        const int npx = px ? atoi(px) : 2;
+        const int npx = px ? atoi(px) : 4;            // 4: the table row of a bin is fetched once for four pixels
         if (npx == 1) return launch_gn<float, 1>(g, i0, mus, nE, P, n_iters, mask_thresh, a_out, scratch, have, st);
         if (npx == 3) return launch_gn<float, 3>(g, i0, mus, nE, P, n_iters, mask_thresh, a_out, scratch, have, st);
-        if (npx == 4) return launch_gn<float, 4>(g, i0, mus, nE, P, n_iters, mask_thresh, a_out, scratch, have, st);
-        return launch_gn<float, 2>(g, i0, mus, nE, P, n_iters, mask_thresh, a_out, scratch, have, st);
+        if (npx == 2) return launch_gn<float, 2>(g, i0, mus, nE, P, n_iters, mask_thresh, a_out, scratch, have, st);
+        return launch_gn<float, 4>(g, i0, mus, nE, P, n_iters, mask_thresh, a_out, scratch, have, st);
     }
     return launch_gn<double, 1>(g, i0, mus, nE, P, n_iters, mask_thresh, a_out, scratch, have, st);
 }

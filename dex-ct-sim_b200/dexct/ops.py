@@ -203,3 +203,50 @@ def gn_decompose(g, i0, mus, n_iters, mask_thresh=0.0, dtype=F32, out=None, redu
         N.check(N.lib().dexct_gn_decompose(N.ptr(g), N.ptr(i0), N.ptr(mus), nE, P, int(n_iters), float(mask_thresh),
                                            N.ptr(out), N.ptr(scratch), have_max, code, N.stream_ptr()))
     return out
+
+
+def fbp_fan(scan, sino, n_matrix, fov, ramp, view_begin=0, dtype=F32, image=None, accumulate=False):
+    """Fan-beam FBP of the views ``[view_begin, view_begin + sino.shape[0])`` of ``scan`` (replaces the numerics of
+    get_recon, /root/reference/main.py:134,168).
+
+    sino: device tensor ``[views, n_ch]`` or ``[views, n_rows, n_ch]`` holding exactly those views.
+    Returns the image ``[n_rows, n_matrix, n_matrix]`` on the device (added to ``image`` when ``accumulate``).
+    """
+    N.require_device()
+    code = dtype_code(dtype)
+    td = _TORCH_DTYPE[code]
+    if not (isinstance(sino, torch.Tensor) and sino.is_cuda):
+        raise TypeError('sino must be a CUDA tensor')
+    dev = sino.device
+    if sino.dim() == 2:
+        sino = sino[:, None, :]
+    if sino.dim() != 3 or sino.shape[1] != scan.n_rows or sino.shape[2] != scan.n_ch:
+        raise ValueError(f'sino must be [views, {scan.n_rows}, {scan.n_ch}], got {tuple(sino.shape)}')
+    sino = sino.to(td).contiguous()
+    nv = sino.shape[0]
+    shape = (scan.n_rows, int(n_matrix), int(n_matrix))
+    if image is None:
+        if accumulate:
+            raise ValueError('accumulate needs an image to add to')
+        image = torch.empty(shape, dtype=td, device=dev)
+    elif tuple(image.shape) != shape or image.dtype != td or not image.is_contiguous():
+        raise ValueError(f'image must be a contiguous {td} tensor of shape {shape}')
+    with torch.cuda.device(dev):
+        nbytes = N.lib().dexct_fbp_workspace_bytes(C.byref(scan), max(nv, 1), code)
+        scratch = torch.empty(max(nbytes, 16), dtype=torch.uint8, device=dev)
+        N.check(N.lib().dexct_fbp_fan(C.byref(scan), N.ptr(sino), int(view_begin), nv, int(n_matrix), float(fov),
+                                      float(ramp), N.ptr(image), int(bool(accumulate)), N.ptr(scratch), code,
+                                      N.stream_ptr()))
+    return image
+
+
+def hounsfield(image, mu_water, dtype=F32, out=None):
+    """1000 (image - mu_water) / mu_water on the device."""
+    N.require_device()
+    code = dtype_code(dtype)
+    if image.dtype != _TORCH_DTYPE[code] or not image.is_contiguous():
+        raise ValueError('image must be a contiguous tensor of the compute dtype')
+    out = torch.empty_like(image) if out is None else out
+    with torch.cuda.device(image.device):
+        N.check(N.lib().dexct_fbp_hu(N.ptr(image), image.numel(), float(mu_water), N.ptr(out), code, N.stream_ptr()))
+    return out

@@ -41,15 +41,46 @@ def spectral_tables(ct, spec1, spec2):
     return ee, i0, mus
 
 
+def _counts_to_device(sinos, td):
+    """Two count sinograms (device tensors or host arrays of any float type) -> one device tensor [2, ...] of dtype
+    ``td``.  Host arrays are uploaded as they are (one DMA each when they sit in page-locked memory, as the arrays
+    returned by get_sino do) and converted on the device; nothing is stacked or converted on the host."""
+    dev = torch.device('cuda', torch.cuda.current_device())
+    first = sinos[0]
+    g = torch.empty((2,) + tuple(first.shape), dtype=td, device=dev)
+    for m, s in enumerate(sinos):
+        if not isinstance(s, torch.Tensor):
+            s = np.asarray(s)
+            if s.dtype not in (np.float32, np.float64) or not s.flags.c_contiguous:
+                s = np.ascontiguousarray(s, dtype=np.float64)
+            s = torch.from_numpy(s)
+        if tuple(s.shape) != tuple(first.shape):
+            raise ValueError('the two sinograms must have the same shape')
+        g[m].copy_(s, non_blocking=True)
+    return g
+
+
+def _host_f64(t):
+    """Device tensor -> float64 numpy array in page-locked memory (conversion on the device, one DMA)."""
+    h = torch.empty(t.shape, dtype=torch.float64, pin_memory=True)
+    h.copy_(t, non_blocking=True)
+    torch.cuda.current_stream().synchronize()
+    return h.numpy()
+
+
 def optimize_sino(Sino_gg, ee, i0, mus, n_iters, verbose=True, dtype=None, mask_thresh=0.0, to_host=True,
                   reduce_max_over_ranks=False):
     """GPU Newton iterations; signature of matdecomp.py:20 (``ee`` is unused there too).
 
-    Sino_gg [2, nViews, nBins] counts; i0 [2, nBins, nE] (all bins identical, matdecomp.py:151) or [2, nE];
-    mus [2, nE].  Returns [nViews, nBins, 2] -- float64 numpy by default, the device tensor with ``to_host=False``.
+    Sino_gg [2, nViews, nBins] counts (array, device tensor, or a pair of them); i0 [2, nBins, nE] (all bins identical,
+    matdecomp.py:151) or [2, nE]; mus [2, nE].  Returns [nViews, nBins, 2] -- float64 numpy by default, the device
+    tensor with ``to_host=False``.
     """
     del ee, verbose
+    from dexct import _native
+    _native.require_device()
     code = dtype_code(config.dtype if dtype is None else dtype)
+    td = torch.float32 if code == 0 else torch.float64
     i0 = np.asarray(i0, dtype=np.float64)
     if i0.ndim == 3:
         if i0.shape[1] > 1 and not np.array_equal(i0[:, :1, :].repeat(i0.shape[1], axis=1), i0):
@@ -59,9 +90,15 @@ def optimize_sino(Sino_gg, ee, i0, mus, n_iters, verbose=True, dtype=None, mask_
     mus = np.asarray(mus, dtype=np.float64)
     if mus.shape[0] != 2:
         raise NotImplementedError('two basis materials only (matdecomp.py:155)')
-    out = gn_decompose(Sino_gg, i0, mus, n_iters, mask_thresh=mask_thresh, dtype=code,
+    if isinstance(Sino_gg, torch.Tensor) and Sino_gg.is_cuda:
+        g = Sino_gg
+    else:
+        if len(Sino_gg) != 2:
+            raise ValueError('Sino_gg must hold two measurements')
+        g = _counts_to_device([Sino_gg[0], Sino_gg[1]], td)
+    out = gn_decompose(g, i0, mus, n_iters, mask_thresh=mask_thresh, dtype=code,
                        reduce_max_over_ranks=reduce_max_over_ranks)
-    return out.detach().cpu().numpy().astype(np.float64) if to_host else out
+    return _host_f64(out) if to_host else out
 
 
 # The reference keeps a CPU twin because its cupy version misbehaved (matdecomp.py:89-91); here both names run the
@@ -73,20 +110,16 @@ def do_matdecomp_gn(ct, sino1, sino2, spec1, spec2, n_iters, mask_thresh=0.0, to
     """matdecomp.py:130-164.  With a process group and ``config.shard_views`` the pixels are split by view range,
     decomposed without communication and the result all-gathered."""
     ee, i0, mus = spectral_tables(ct, spec1, spec2)
-    if isinstance(sino1, torch.Tensor):
-        g = torch.stack([sino1, sino2])
-    else:
-        g = np.stack([np.asarray(sino1, dtype=np.float64), np.asarray(sino2, dtype=np.float64)])
     rank, ws = dist.world() if config.shard_views else (0, 1)
     if ws > 1:
-        n_views = g.shape[1]
+        n_views = sino1.shape[0]
         v0, nv = dist.shard_range(n_views, rank, ws)
         # the air threshold needs the maximum over the whole sinogram: one integer MAX all-reduce between the shards
-        local = optimize_sino(g[:, v0:v0 + nv], ee, i0, mus, n_iters, mask_thresh=mask_thresh, to_host=False,
-                              reduce_max_over_ranks=True)
+        local = optimize_sino((sino1[v0:v0 + nv], sino2[v0:v0 + nv]), ee, i0, mus, n_iters, mask_thresh=mask_thresh,
+                              to_host=False, reduce_max_over_ranks=True)
         full = dist.all_gather_views(local, n_views, dim=0)
-        return full.detach().cpu().numpy().astype(np.float64) if to_host else full
-    return optimize_sino(g, ee, i0, mus, n_iters, mask_thresh=mask_thresh, to_host=to_host)
+        return _host_f64(full) if to_host else full
+    return optimize_sino((sino1, sino2), ee, i0, mus, n_iters, mask_thresh=mask_thresh, to_host=to_host)
 
 
 def get_basismat_sinos(ct, sino_raw_1, sino_raw_2, spec1, spec2, n_iters=30, mask_thresh=0.95):

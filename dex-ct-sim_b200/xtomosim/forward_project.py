@@ -79,11 +79,23 @@ def project_device(ct, phantom, specs, dtype=None, want_log=True):
     Returns (counts, logs) lists of tensors ``[views_local, n_rows, n_ch]`` -- the local view shard when a process group
     is initialised and ``config.shard_views`` is on, the whole scan otherwise -- plus (view_begin, view_count).
     """
+    groups, span = _project_groups(ct, phantom, specs, dtype, want_log)
+    counts_out, logs_out = [], []
+    for c, lg in groups:
+        for n in range(c.shape[0]):
+            counts_out.append(c[n])
+            logs_out.append(lg[n] if want_log else None)
+    return counts_out, logs_out, span
+
+
+def _project_groups(ct, phantom, specs, dtype=None, want_log=True):
+    """One fused traversal per group of spectra that share an energy grid: list of (counts, logs) tensors
+    ``[n_spectra_in_group, views_local, n_rows, n_ch]`` in the order of ``specs``."""
     code = dtype_code(config.dtype if dtype is None else dtype)
     st = _get_state(ct, phantom)
     rank, ws = dist.world() if config.shard_views else (0, 1)
     v0, nv = dist.shard_range(ct.N_proj, rank, ws)
-    counts_out, logs_out = [], []
+    out = []
     same_grid = all(len(s.E) == len(specs[0].E) and np.array_equal(s.E, specs[0].E) for s in specs)
     groups = [list(range(len(specs)))] if (same_grid and len(specs) <= 4) else [[i] for i in range(len(specs))]
     for grp in groups:
@@ -94,22 +106,36 @@ def project_device(ct, phantom, specs, dtype=None, want_log=True):
         if have_L:
             c, lg = poly_detect(st.L, mu, W, dtype=code, want_log=want_log)
         else:
+            # a single-shot call (all spectra at once) has no second call to serve from stored lengths
+            keep_L = config.cache_lengths and (len(groups) > 1 or len(specs) == 1)
             c, lg, L = st.projector.project(mu, W, view_begin=v0, view_count=nv, dtype=code, want_log=want_log,
-                                            want_L=config.cache_lengths)
-            if config.cache_lengths:
+                                            want_L=keep_L)
+            if keep_L:
                 st.L, st.L_dtype = L, code
-        for n, _ in enumerate(grp):
-            counts_out.append(c[n])
-            logs_out.append(lg[n] if want_log else None)
-    return counts_out, logs_out, (v0, nv)
+        out.append((c, lg))
+    return out, (v0, nv)
 
 
-def _to_host(t, ct):
-    """Gather view shards (NCCL all-gather, view axis outermost) and hand back float64 numpy like the reference."""
-    if config.shard_views:
-        t = dist.all_gather_views(t, ct.N_proj, dim=0)
-    a = t.detach().cpu().numpy().astype(np.float64)
-    return a[:, 0, :] if ct.N_rows == 1 else a
+def _to_host(tensors, ct):
+    """Device tensors ``[..., views_local, n_rows, n_ch]`` -> float64 numpy arrays like the reference's.
+
+    View shards are gathered first (NCCL all-gather).  The conversion to float64 runs on the device and the copy lands
+    in page-locked host memory (torch's caching host allocator: the block is recycled once the caller drops the array),
+    one DMA per tensor and a single synchronisation for all of them.
+    """
+    hosts = []
+    for t in tensors:
+        if config.shard_views:
+            t = dist.all_gather_views(t, ct.N_proj, dim=t.dim() - 3)
+        h = torch.empty(t.shape, dtype=torch.float64, pin_memory=True)
+        h.copy_(t, non_blocking=True)
+        hosts.append(h)
+    torch.cuda.current_stream().synchronize()
+    out = []
+    for h in hosts:
+        a = h.numpy()
+        out.append(a[..., 0, :] if ct.N_rows == 1 else a)
+    return out
 
 
 def get_sino(ct, phantom, spec):
@@ -118,12 +144,18 @@ def get_sino(ct, phantom, spec):
     Returns ``(sino_raw, sino_log)``: detected counts and ``-ln(counts / unattenuated counts)``, each a float64 numpy
     array ``[N_proj, N_channels]`` (``[N_proj, N_rows, N_channels]`` for multi-row scanners).
     """
-    counts, logs, _ = project_device(ct, phantom, [spec])
-    return _to_host(counts[0], ct), _to_host(logs[0], ct)
+    (c, lg), = _project_groups(ct, phantom, [spec])[0]
+    raw, log = _to_host([c[0], lg[0]], ct)
+    return raw, log
 
 
 def get_sinos(ct, phantom, specs):
     """Extension: all spectra of a multi-energy acquisition in one traversal (one fused kernel when they share an
     energy grid).  Returns a list of ``(sino_raw, sino_log)``."""
-    counts, logs, _ = project_device(ct, phantom, list(specs))
-    return [(_to_host(c, ct), _to_host(lg, ct)) for c, lg in zip(counts, logs)]
+    groups = _project_groups(ct, phantom, list(specs))[0]
+    flat = _to_host([t for c, lg in groups for t in (c, lg)], ct)      # [n_in_group, views, (rows,) ch] each
+    out = []
+    for g in range(len(groups)):
+        raw, log = flat[2 * g], flat[2 * g + 1]
+        out.extend((raw[n], log[n]) for n in range(raw.shape[0]))
+    return out

@@ -135,14 +135,24 @@ int dexct_gn_air_max(const void *g1, int64_t P, void *scratch, int32_t dtype, vo
 
 /* ---- fan-beam filtered back-projection: replaces get_recon (main.py:134,168) ------------------------------ */
 
-/* Equiangular fan-beam FBP of one sinogram row-set as a gather over views.
- *   sino [n_views][n_ch] (dtype);  image [n_matrix][n_matrix] (dtype), attenuation units of the sinogram per cm;
- *   fov  side of the reconstructed square [cm];  ramp  cut-off as a fraction of Nyquist (sinc window);
- *   scratch: dexct_fbp_workspace_bytes() of device memory.                                                    */
-size_t dexct_fbp_workspace_bytes(const DexctScan *scan, int32_t dtype);
+/* Equiangular fan-beam FBP (Kak & Slaney) of the views [view_begin, view_begin + view_count) of a full-rotation scan,
+ * as a gather over views: cosine pre-weight, ramp filter with a sinc window cut at
+ * ramp * Nyquist (input/params.txt:35), 1/L^2-weighted back-projection with linear interpolation between channels.
+ *   sino    [view_count][n_rows][n_ch] (dtype)   line integrals of THOSE views (a view shard starts at its own row 0)
+ *   image   [n_rows][n_matrix][n_matrix] (dtype) one slice per detector row, pixel (j, i) centred at
+ *           x = (i - (n-1)/2) fov/n, y = (j - (n-1)/2) fov/n -- the phantom's axes; units of the sinogram per cm
+ *   accumulate != 0: add to the image instead of overwriting it (view chunks, or partial images that ranks holding
+ *           different view ranges sum with an all-reduce)
+ *   scratch dexct_fbp_workspace_bytes(scan, view_count, dtype) bytes of device memory (filtered lines + tables)
+ * The whole square must lie inside the source circle (fov / sqrt(2) < SID).                                      */
+size_t dexct_fbp_workspace_bytes(const DexctScan *scan, int32_t view_count, int32_t dtype);
 int dexct_fbp_fan(const DexctScan *scan, const void *sino, int32_t view_begin, int32_t view_count,
                   int32_t n_matrix, double fov, double ramp, void *image, int32_t accumulate,
                   void *scratch, int32_t dtype, void *stream);
+
+/* hu[i] = 1000 (image[i] - mu_water) / mu_water: the Hounsfield image get_recon returns beside the raw one
+ * (main.py:134-140).  In place (hu == image) is allowed.                                                        */
+int dexct_fbp_hu(const void *image, int64_t n, double mu_water, void *hu, int32_t dtype, void *stream);
 
 #ifdef __cplusplus
 }

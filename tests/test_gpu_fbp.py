@@ -1,0 +1,138 @@
+"""Parity of the CUDA fan-beam FBP (csrc/fbp.cu, through the C ABI) with the float64 oracle (oracle/fbp_oracle.py).
+
+Tolerances (scale-relative, max|a - ref| / max|ref|): 1e-10 in f64 mode; 2e-5 in f32 mode -- the back-projection sums
+~10^3 interpolated samples of a filtered line whose neighbouring samples differ by O(1), and the single-precision
+channel coordinate (atan, 2^-24 relative) moves each sample by ~1e-5 of that difference.
+"""
+import numpy as np
+import pytest
+import torch
+
+from conftest import scale_rel_err
+from dexct import _native as N
+from dexct import synthetic as S
+from dexct.ops import F32, F64, fbp_fan, hounsfield, make_scan
+from oracle import fbp_oracle as FO
+
+pytestmark = pytest.mark.gpu
+
+FAN, SID, SDD = 0.8230337, 60.0, 100.0
+TOL = {F32: 2e-5, F64: 1e-10}
+TD = {F32: torch.float32, F64: torch.float64}
+
+
+def _case(n_ch=200, n_views=120, n_rows=1, seed=11, beta0=0.0):
+    scan = make_scan(n_views, n_ch, FAN, SID, SDD, n_rows=n_rows, h_iso=0.3, beta0=beta0)
+    beta = scan.beta0 + np.arange(n_views) * scan.dbeta
+    gam = scan.gamma0 + np.arange(n_ch) * scan.dgamma
+    r = np.random.default_rng(seed)
+    rows = []
+    for k in range(n_rows):
+        s = FO.disc_sinogram(beta, gam, SID, (3.0 - k, -2.0 + 0.5 * k), 8.0 - k, 0.2)
+        s += FO.disc_sinogram(beta, gam, SID, (-5.0, 4.0), 2.0, 0.35)
+        s += 0.01 * r.standard_normal(s.shape)            # noise: exercises the filter at every frequency
+        rows.append(s)
+    sino = np.stack(rows, axis=1)                          # [views, rows, ch]
+    return scan, beta, sino
+
+
+def _oracle(scan, beta, sino, n, fov, ramp):
+    return FO.fbp_fan(sino, beta, scan.gamma0, scan.dgamma, scan.dbeta, SID, n, fov, ramp)
+
+
+@pytest.mark.parametrize('dtype', [F32, F64])
+@pytest.mark.parametrize('ramp', [1.0, 0.8, 0.5])
+def test_image_matches_oracle(dtype, ramp):
+    scan, beta, sino = _case()
+    ref = _oracle(scan, beta, sino, 96, 40.0, ramp)
+    got = fbp_fan(scan, torch.as_tensor(sino, device='cuda'), 96, 40.0, ramp, dtype=dtype)
+    assert got.shape == (1, 96, 96) and got.dtype == TD[dtype]
+    assert scale_rel_err(got.cpu().numpy(), ref) < TOL[dtype]
+
+
+@pytest.mark.parametrize('dtype', [F32, F64])
+def test_multi_row_odd_sizes_and_start_angle(dtype):
+    scan, beta, sino = _case(n_ch=173, n_views=77, n_rows=3, beta0=0.3)
+    ref = _oracle(scan, beta, sino, 61, 33.0, 0.9)
+    got = fbp_fan(scan, torch.as_tensor(sino, device='cuda'), 61, 33.0, 0.9, dtype=dtype)
+    assert got.shape == (3, 61, 61)
+    assert scale_rel_err(got.cpu().numpy(), ref) < TOL[dtype]
+
+
+def test_view_chunks_accumulate_to_the_whole_scan():
+    """What view-sharded ranks do: partial images of disjoint view ranges sum to the image of the whole scan."""
+    scan, beta, sino = _case(n_views=90)
+    d = torch.as_tensor(sino, device='cuda')
+    whole = fbp_fan(scan, d, 64, 40.0, 0.8, dtype=F64)
+    img = torch.zeros_like(whole)
+    for v0, v1 in ((0, 31), (31, 31), (31, 90)):            # includes an empty range
+        fbp_fan(scan, d[v0:v1], 64, 40.0, 0.8, view_begin=v0, dtype=F64, image=img, accumulate=True)
+    assert scale_rel_err(img.cpu().numpy(), whole.cpu().numpy()) < 1e-13
+    parts = [fbp_fan(scan, d[a:b], 64, 40.0, 0.8, view_begin=a, dtype=F64) for a, b in ((0, 45), (45, 90))]
+    assert scale_rel_err((parts[0] + parts[1]).cpu().numpy(), whole.cpu().numpy()) < 1e-13
+
+
+def test_hounsfield_and_linearity():
+    scan, beta, sino = _case()
+    d = torch.as_tensor(sino, device='cuda')
+    a = fbp_fan(scan, d, 48, 40.0, 1.0, dtype=F64)
+    b = fbp_fan(scan, 2.5 * d, 48, 40.0, 1.0, dtype=F64)
+    assert scale_rel_err(b.cpu().numpy(), 2.5 * a.cpu().numpy()) < 1e-14
+    hu = hounsfield(a, 0.19, dtype=F64)
+    assert np.allclose(hu.cpu().numpy(), FO.hounsfield(a.cpu().numpy(), 0.19), rtol=1e-13, atol=1e-10)
+
+
+def test_argument_errors_are_reported():
+    scan, beta, sino = _case(n_ch=64, n_views=16)
+    d = torch.as_tensor(sino, device='cuda')
+    with pytest.raises(N.DexctError, match='ramp'):
+        fbp_fan(scan, d, 32, 40.0, 0.0)
+    with pytest.raises(N.DexctError, match='source circle'):
+        fbp_fan(scan, d, 32, 90.0, 1.0)
+    with pytest.raises(N.DexctError, match='view range'):
+        fbp_fan(scan, d, 32, 40.0, 1.0, view_begin=8)
+    with pytest.raises(ValueError):
+        fbp_fan(scan, d[:, :, :60], 32, 40.0, 1.0)
+
+
+def test_c2_pipeline_get_sino_then_get_recon_recovers_the_phantom():
+    """Full size (C2: 900 ch x 1000 views -> 512 x 512): project the synthetic phantom with a narrow spectrum and
+    reconstruct sino_log through the drop-in entry points; the soft-tissue body and the air around it come back at their
+    attenuation, and the f32 image agrees with the oracle on a strip of pixels (the oracle is too slow for all of them)."""
+    from xtomosim.back_project import effective_mu_water, get_recon
+    from xtomosim.forward_project import get_sino
+    ct, ph, lo, hi = S.make_config('C2')
+    mono = S.gaussian_spectrum('mono', 70.0, 0.4, lo.E)
+    raw, log = get_sino(ct, ph, mono)
+    rec, hu = get_recon(log, ct, mono, 512, 51.2, 0.8)
+    assert rec.shape == (512, 512) and rec.dtype == np.float64
+    mu70 = ph.mu_table(np.array([70.0]))[:, 0]
+    lab = ph.M[0]
+    from scipy.ndimage import binary_erosion
+    body = binary_erosion(lab == 1, iterations=6)
+    yy, xx = np.mgrid[0:512, 0:512] - 255.5
+    # the fan covers a disc of radius SID sin(fan/2) = 24 cm; the corners of the square are outside the scanned field
+    air = binary_erosion(lab == 0, iterations=6) & (np.hypot(xx, yy) * 0.1 < 22.0)
+    assert abs(rec[body].mean() - mu70[1]) < 0.01 * mu70[1]
+    assert abs(rec[air].mean()) < 0.01 * mu70[1]
+    mw = effective_mu_water(ct, mono)
+    assert np.allclose(hu, 1000.0 * (rec - mw) / mw, rtol=1e-5, atol=1e-2)
+    # strip parity against the oracle: 8 image rows through the middle
+    scan = make_scan(ct.N_proj, ct.N_channels, ct.gamma_fan, ct.SID, ct.SDD, rotation=ct.rotation)
+    beta = scan.beta0 + np.arange(ct.N_proj) * scan.dbeta
+    n, fov = 512, 51.2
+    q = FO.filter_lines(log, scan.gamma0, scan.dgamma, SID, 0.8)
+    qp = np.pad(q, ((0, 0), (1, 1)))
+    c = (np.arange(n) - 0.5 * (n - 1)) * (fov / n)
+    X, Y = np.meshgrid(c, c[252:260])
+    ref = np.zeros_like(X)
+    for v in range(ct.N_proj):
+        cb, sb = np.cos(beta[v]), np.sin(beta[v])
+        A = SID - (X * cb + Y * sb)
+        B = Y * cb - X * sb
+        u = np.clip((np.arctan2(-B, A) - scan.gamma0) / scan.dgamma, -1.0, float(ct.N_channels))
+        fl = np.minimum(np.floor(u), ct.N_channels - 1.0)
+        i0 = fl.astype(np.int64)
+        ref += (qp[v][i0 + 1] + (u - fl) * (qp[v][i0 + 2] - qp[v][i0 + 1])) / (A * A + B * B)
+    ref *= scan.dbeta
+    assert np.max(np.abs(rec[252:260] - ref)) / np.max(np.abs(rec)) < 5e-5
