@@ -376,7 +376,7 @@ def run_b200(args):
             'roofline_gn': {'bound': 'fp32_fma', 'achieved': gn_flops / (t_gn * 1e-3) / 1e12, 'peak': fma_peak, 'unit': 'TFLOP/s',
                             'frac': gn_flops / (t_gn * 1e-3) / 1e12 / fma_peak, 'kernel': 'gn_kernel',
                             'flop_per_pixel': 28.0 * nE * GN_ITERS},
-            'gpu_launches': 3 * args.steps, 'clocks': clocks,
+            'gpu_launches': 5 * args.steps, 'clocks': clocks,     # siddon_skip, gn_max, gn_table, gn_kernel, gn_fixup per step
         }
         if e2e:
             line['e2e'] = e2e

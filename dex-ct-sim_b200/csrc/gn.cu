@@ -17,6 +17,7 @@
 namespace dexct {
 
 constexpr int GN_ROW = 16;
+constexpr float GN_A_FLOOR = -20.0f;      // single precision hands pixels whose iterates go below this to the float64 pass
 
 // Packed single-precision pairs (FFMA2 on sm_100a: two FMAs per issue slot).
 typedef unsigned long long f32x2;
@@ -131,7 +132,7 @@ __global__ void gn_table_kernel(const float *__restrict__ i0, const float *__res
 
 template <typename R, int PX, bool CTAB>
 __global__ void __launch_bounds__(256) gn_kernel(const R *__restrict__ g, const R *__restrict__ i0, const R *__restrict__ mus,
-                                                 int nE, long long P, int n_iters, R mask_thresh, const void *scratch,
+                                                 int nE, long long P, int n_iters, R mask_thresh, void *scratch,
                                                  R *__restrict__ a_out)
 {
     typedef GnMath<R> M;
@@ -167,9 +168,11 @@ __global__ void __launch_bounds__(256) gn_kernel(const R *__restrict__ g, const 
     for (long long grp = blockIdx.x; grp < n_groups; grp += gridDim.x) {
         const long long base = grp * stride * PX + threadIdx.x;
         R a1[PX], a2[PX], g1[PX], g2[PX];
+        bool sane[PX];
 #pragma unroll
         for (int k = 0; k < PX; ++k) {
             const long long p = base + k * stride;
+            sane[k] = true;
             a1[k] = a2[k] = (R)1e-6;                                         // matdecomp.py:98
             g1[k] = p < P ? g[p] : (R)1;
             g2[k] = p < P ? g[P + p] : (R)1;
@@ -288,6 +291,13 @@ __global__ void __launch_bounds__(256) gn_kernel(const R *__restrict__ g, const 
             for (int k = 0; k < PX; ++k) {
                 const R *A = acc[k];                                          // A[0..5] meas 1, A[6..11] meas 2
                 const R nu1 = A[0], nu2 = A[6];
+                if (sizeof(R) == 4) {
+                    // single precision cannot follow the reference where its exponent clip (matdecomp.py:116) is what keeps
+                    // the sums finite: any sum beyond these bounds (inf and NaN included) sends the pixel to the float64 pass
+                    R big = fmax(fabs(A[3]), fabs(A[9]));
+                    big = fmax(big, fmax(fmax(fabs(A[4]), fabs(A[10])), fmax(fabs(A[5]), fabs(A[11]))));
+                    sane[k] = sane[k] && (nu1 < (R)1e18) && (nu2 < (R)1e18) && (big < (R)1e30) && (nu1 > (R)0) && (nu2 > (R)0);
+                }
                 const R r1 = g1[k] / nu1 - (R)1, r2 = g2[k] / nu2 - (R)1;      // g/nu - 1
                 const R s1 = g1[k] / (nu1 * nu1), s2 = g2[k] / (nu2 * nu2);    // g/nu^2
                 // grad_mp = -A[1+p]; the two minus signs of dF cancel, grad grad^T is sign-free
@@ -301,8 +311,14 @@ __global__ void __launch_bounds__(256) gn_kernel(const R *__restrict__ g, const 
                 const R err = M::fma(-h12, h12, w);
                 const R det = M::fma(h11, h22, -w) + err;
                 const R inv = (R)1 / det;
+                // an indefinite Hessian means the iterate has left the basin of the minimum: from there the Newton map
+                // is chaotic and single precision cannot retrace the reference's float64 trajectory
                 a1[k] -= (h22 * d1 - h12 * d2) * inv;
                 a2[k] -= (h11 * d2 - h12 * d1) * inv;
+                // ... and neither can it where a basis thickness runs far below zero (photon-starved pixels: the exponent
+                // a.mu is then a difference of huge terms).  GN_A_FLOOR [g/cm2] is far outside anything physical.
+                if (sizeof(R) == 4)
+                    sane[k] = sane[k] && det > (R)0 && h11 > (R)0 && fmin(a1[k], a2[k]) > (R)GN_A_FLOOR;
             }
         }
 #pragma unroll
@@ -314,12 +330,80 @@ __global__ void __launch_bounds__(256) gn_kernel(const R *__restrict__ g, const 
                 if (sizeof(R) == 4) {
                     float2 o = make_float2(masked ? 0.f : (float)a1[k], masked ? 0.f : (float)a2[k]);
                     ((float2 *)a_out)[p] = o;
+                    const bool finite = fabs(a1[k]) < (R)INFINITY && fabs(a2[k]) < (R)INFINITY;
+                    if (!masked && !(sane[k] && finite)) {                    // rare: hand the pixel to gn_fixup_kernel
+                        unsigned *fl = (unsigned *)scratch;
+                        fl[4 + atomicAdd(fl + 2, 1u)] = (unsigned)p;
+                    }
                 } else {
                     double2 o = make_double2(masked ? 0.0 : (double)a1[k], masked ? 0.0 : (double)a2[k]);
                     ((double2 *)a_out)[p] = o;
                 }
             }
         }
+    }
+}
+
+// Float64 pass over the pixels the single-precision kernel flagged (scratch: [2] = count, [4 ...] = pixel ids): the same
+// Newton iteration in double precision with the reference's exponent clip, on the same (float) inputs.  These are
+// photon-starved or metal-crossing pixels whose iterates leave the float range; the reference's float64 result for them is
+// finite, and a NaN left in a sinogram would spoil every pixel of the image reconstructed from it.
+__global__ void __launch_bounds__(128) gn_fixup_kernel(const float *__restrict__ g, const float *__restrict__ i0,
+                                                       const float *__restrict__ mus, int nE, long long P, int n_iters,
+                                                       const unsigned *__restrict__ flagged, float *__restrict__ a_out)
+{
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    double *tab = (double *)smem_raw;                                    // [nE][14]
+    const unsigned count = flagged[2];
+    if (count == 0) return;
+    for (int e = threadIdx.x; e < nE; e += blockDim.x) {
+        const double m1 = mus[e], m2 = mus[nE + e], s1 = i0[e], s2 = i0[nE + e];
+        double *row = tab + e * 14;
+        row[0] = -m1; row[1] = -m2;
+        const double f[6] = {1.0, m1, m2, m1 * m1, m1 * m2, m2 * m2};
+#pragma unroll
+        for (int q = 0; q < 6; ++q) { row[2 + q] = s1 * f[q]; row[8 + q] = s2 * f[q]; }
+    }
+    __syncthreads();
+    // one WARP per flagged pixel, the energy bins dealt round-robin to its lanes: a single thread would need ~0.2 ms for
+    // one pixel of a C2 scan, and one flagged pixel is enough to put that latency on the critical path
+    const int lane = threadIdx.x & 31;
+    const unsigned warp = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, n_warps = (gridDim.x * blockDim.x) >> 5;
+    for (unsigned t = warp; t < count; t += n_warps) {
+        const long long p = flagged[4 + t];
+        const double g1 = g[p], g2 = g[P + p];
+        double a1 = 1e-6, a2 = 1e-6;
+        for (int it = 0; it < n_iters; ++it) {
+            double A[12];
+#pragma unroll
+            for (int q = 0; q < 12; ++q) A[q] = 0.0;
+            for (int e = lane; e < nE; e += 32) {
+                const double *row = tab + e * 14;
+                const double att = GnMath<double>::att(fma(a2, row[1], a1 * row[0]));
+#pragma unroll
+                for (int q = 0; q < 12; ++q) A[q] = fma(row[2 + q], att, A[q]);
+            }
+            // xor butterfly: x + y is commutative, so every lane ends with bitwise the same twelve sums
+#pragma unroll
+            for (int q = 0; q < 12; ++q)
+#pragma unroll
+                for (int o = 16; o > 0; o >>= 1) A[q] += __shfl_xor_sync(0xffffffffu, A[q], o);
+            const double nu1 = A[0], nu2 = A[6];
+            const double r1 = g1 / nu1 - 1.0, r2 = g2 / nu2 - 1.0;
+            const double s1 = g1 / (nu1 * nu1), s2 = g2 / (nu2 * nu2);
+            const double d1 = r1 * A[1] + r2 * A[7];
+            const double d2 = r1 * A[2] + r2 * A[8];
+            const double h11 = -(r1 * A[3] + r2 * A[9]) + (s1 * A[1] * A[1] + s2 * A[7] * A[7]);
+            const double h12 = -(r1 * A[4] + r2 * A[10]) + (s1 * A[1] * A[2] + s2 * A[7] * A[8]);
+            const double h22 = -(r1 * A[5] + r2 * A[11]) + (s1 * A[2] * A[2] + s2 * A[8] * A[8]);
+            const double w = h12 * h12;
+            const double err = fma(-h12, h12, w);
+            const double det = fma(h11, h22, -w) + err;
+            const double inv = 1.0 / det;
+            a1 -= (h22 * d1 - h12 * d2) * inv;
+            a2 -= (h11 * d2 - h12 * d1) * inv;
+        }
+        if (lane == 0) ((float2 *)a_out)[p] = make_float2((float)a1, (float)a2);
     }
 }
 
@@ -346,7 +430,7 @@ static int launch_gn(const void *g, const void *i0, const void *mus, int nE, lon
         set_error("GN table needs %zu bytes of shared memory (limit 200 KiB): nE=%d", smem, nE);
         return DEXCT_ECAPACITY;
     }
-    void (*kern)(const R *, const R *, const R *, int, long long, int, R, const void *, R *) = gn_kernel<R, PX, false>;
+    void (*kern)(const R *, const R *, const R *, int, long long, int, R, void *, R *) = gn_kernel<R, PX, false>;
     if (ctab) kern = gn_kernel<R, PX, sizeof(R) == 4>;
     if (smem > 48 * 1024) DEXCT_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     int per_sm = 0;
@@ -358,6 +442,21 @@ static int launch_gn(const void *g, const void *i0, const void *mus, int nE, lon
     if (mask_thresh > 0 && !have_max) {
         if (int e = launch_max<R>(g, P, scratch, st)) return e;
     }
+    if (sizeof(R) == 4) DEXCT_CUDA_OK(cudaMemsetAsync((char *)scratch + 8, 0, 8, st));     // count of flagged pixels
+    // float64 pass over whatever the single-precision kernel flags (usually nothing: the kernel then returns at once)
+    auto fixup = [&]() -> int {
+        const size_t fsm = sizeof(double) * 14 * (size_t)nE;
+        if (fsm > 200 * 1024) {
+            set_error("GN table needs %zu bytes of shared memory (limit 200 KiB): nE=%d", fsm, nE);
+            return DEXCT_ECAPACITY;
+        }
+        if (fsm > 48 * 1024)
+            DEXCT_CUDA_OK(cudaFuncSetAttribute(gn_fixup_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)fsm));
+        gn_fixup_kernel<<<sm_count() * 4, 128, fsm, st>>>((const float *)g, (const float *)i0, (const float *)mus, nE, P,
+                                                          n_iters, (const unsigned *)scratch, (float *)a_out);
+        DEXCT_CUDA_OK(cudaGetLastError());
+        return DEXCT_OK;
+    };
     if (ctab) {
         ConstSlot slot(SLOT_GN, st);                          // exclusive use of gn_ctab until the kernel below has run
         if (!slot.ok()) return DEXCT_ECUDA;
@@ -370,17 +469,23 @@ static int launch_gn(const void *g, const void *i0, const void *mus, int nE, lon
         kern<<<(unsigned)grid, block, smem, st>>>((const R *)g, (const R *)i0, (const R *)mus, nE, P, n_iters, (R)mask_thresh,
                                                  scratch, (R *)a_out);
         DEXCT_CUDA_OK(cudaGetLastError());
-        return DEXCT_OK;
+        return fixup();
     }
     kern<<<(unsigned)grid, block, smem, st>>>((const R *)g, (const R *)i0, (const R *)mus, nE, P, n_iters, (R)mask_thresh,
                                              scratch, (R *)a_out);
     DEXCT_CUDA_OK(cudaGetLastError());
-    return DEXCT_OK;
+    return sizeof(R) == 4 ? fixup() : DEXCT_OK;
 }
 
 }  // namespace dexct
 
 using namespace dexct;
+
+extern "C" size_t dexct_gn_scratch_bytes(int64_t P, int32_t dtype)
+{
+    if (P < 0) return 0;
+    return dtype == DEXCT_F32 ? 16 + sizeof(unsigned) * (size_t)P : 16;
+}
 
 extern "C" int dexct_gn_air_max(const void *g1, int64_t P, void *scratch, int32_t dtype, void *stream)
 {
@@ -398,7 +503,9 @@ extern "C" int dexct_gn_decompose(const void *g, const void *i0, const void *mus
     if (int e = check_device()) return e;
     DEXCT_REQUIRE(nE >= 1 && P >= 0 && n_iters >= 0, "need nE >= 1, P >= 0, n_iters >= 0");
     DEXCT_REQUIRE(P == 0 || (g && i0 && mus && a_out), "g, i0, mus and a_out must be non-null");
-    DEXCT_REQUIRE(mask_thresh <= 0 || scratch, "scratch must be non-null when mask_thresh > 0");
+    DEXCT_REQUIRE(scratch || (mask_thresh <= 0 && dtype == DEXCT_F64),
+                  "scratch (dexct_gn_scratch_bytes) must be non-null in single precision or when mask_thresh > 0");
+    DEXCT_REQUIRE(P < (1ll << 32), "at most 2^32 - 1 pixels per call");
     DEXCT_REQUIRE(dtype == DEXCT_F32 || dtype == DEXCT_F64, "dtype must be DEXCT_F32 or DEXCT_F64");
     if (P == 0) return DEXCT_OK;
     cudaStream_t st = (cudaStream_t)stream;

@@ -191,17 +191,18 @@ def gn_decompose(g, i0, mus, n_iters, mask_thresh=0.0, dtype=F32, out=None, redu
     nE = i0.shape[1]
     if out is None:
         out = torch.empty(tuple(g.shape[1:]) + (2,), dtype=td, device=dev)
-    scratch = torch.empty(2, dtype=torch.int64, device=dev)
+    scratch = torch.empty(N.lib().dexct_gn_scratch_bytes(P, code), dtype=torch.uint8, device=dev)
     have_max = 0
     with torch.cuda.device(dev):
         if reduce_max_over_ranks and mask_thresh > 0:
             import torch.distributed as dist
             N.check(N.lib().dexct_gn_air_max(N.ptr(g), P, N.ptr(scratch), code, N.stream_ptr()))
-            key = scratch[:1] if code == F64 else scratch.view(torch.int32)[:1]
+            key = scratch[:8].view(torch.int64) if code == F64 else scratch[:4].view(torch.int32)
             dist.all_reduce(key, op=dist.ReduceOp.MAX)
             have_max = 1
         N.check(N.lib().dexct_gn_decompose(N.ptr(g), N.ptr(i0), N.ptr(mus), nE, P, int(n_iters), float(mask_thresh),
                                            N.ptr(out), N.ptr(scratch), have_max, code, N.stream_ptr()))
+    gn_decompose.last_scratch = scratch          # diagnostics: bytes 8..12 = pixels redone in float64 (single precision)
     return out
 
 

@@ -121,9 +121,14 @@ int dexct_siddon_trace(const DexctScan *scan, const DexctVolume *vol, const void
  *   g_2xP   [2][P] measured counts;  i0_2xE [2][nE] (the reference tiles it over channels, matdecomp.py:151);
  *   mus_2xE [2][nE] basis attenuation;  a_out [P][2].
  * mask_thresh > 0 additionally zeroes both outputs of pixels with g[0][p] >= mask_thresh * max_p g[0][p]
- * (get_basismat_sinos, matdecomp.py:195-205); scratch = >= 16 bytes of device memory for that maximum
- * (may be NULL when mask_thresh <= 0).  scratch_has_max != 0: scratch already holds the maximum as written by
- * dexct_gn_air_max (pixel-sharded runs reduce it over ranks first); 0: it is computed here from g[0][0..P).   */
+ * (get_basismat_sinos, matdecomp.py:195-205).
+ * scratch = dexct_gn_scratch_bytes(P, dtype) bytes of device memory: the air maximum and, in single precision, the list
+ * of pixels whose iterates left the float range (photon-starved or metal-crossing rays: the reference's exponent clip,
+ * matdecomp.py:116, is what keeps them finite in float64) -- those are redone in float64 inside the same call, so the
+ * result is finite wherever the reference's is.  May be NULL only for DEXCT_F64 with mask_thresh <= 0.
+ * scratch_has_max != 0: scratch already holds the maximum as written by dexct_gn_air_max (pixel-sharded runs reduce it
+ * over ranks first); 0: it is computed here from g[0][0..P).                                                     */
+size_t dexct_gn_scratch_bytes(int64_t P, int32_t dtype);
 int dexct_gn_decompose(const void *g_2xP, const void *i0_2xE, const void *mus_2xE, int32_t nE, int64_t P,
                        int32_t n_iters, double mask_thresh, void *a_out_Px2, void *scratch,
                        int32_t scratch_has_max, int32_t dtype, void *stream);

@@ -128,3 +128,43 @@ def test_c3_full_size_self_consistency():
     out = gn_decompose(g[:, :2], i0, mus, 20, dtype=F64).cpu().numpy()
     assert scale_rel_err(out, ref) < 1e-10
     assert scale_rel_err(out, a_true[:2]) < 1e-8
+
+
+def test_starved_pixels_stay_finite_in_single_precision():
+    """Photon-starved / metal-like pixels: the Newton iterates go where 2^x leaves the float range, and only the
+    reference's exponent clip (matdecomp.py:116) keeps its float64 sums finite.  The single-precision kernel hands such
+    pixels to its float64 pass: the result must be finite wherever the oracle's is, and equal to it to float accuracy
+    (same float-rounded inputs), while ordinary pixels are untouched."""
+    E = np.arange(1.0, 141.0)
+    lo, hi = S.gaussian_spectrum('lo', 55.0, 18.0, E, 1e8), S.gaussian_spectrum('hi', 95.0, 25.0, E, 1e8)
+    i0 = np.stack([lo.I0, hi.I0])
+    mus = np.stack([0.2 * (60.0 / E) ** 2.2 + 0.15, 0.9 * (60.0 / E) ** 2.9 + 0.12])      # steep at 1 keV like real mu/rho
+    r = np.random.default_rng(9)
+    a = np.stack([r.uniform(0, 25, 400), r.uniform(0, 4, 400)], axis=-1)
+    att = np.exp(-(a[:, 0:1] * mus[0] + a[:, 1:2] * mus[1]))
+    g = np.stack([att @ i0[0], att @ i0[1]])                   # [2, 400] consistent counts
+    g[1, :40] *= r.uniform(1e-9, 1e-3, 40)                     # starve the second measurement of 40 pixels
+    g[0, 40:60] *= r.uniform(5.0, 50.0, 20)                    # and make 20 more inconsistent the other way
+    r32 = lambda x: np.asarray(x).astype(np.float32).astype(np.float64)                  # noqa: E731
+    gq, i0q, musq = r32(g), r32(i0), r32(mus)
+    ref = np.full((400, 2), np.nan)
+    with np.errstate(all='ignore'):
+        for p in range(400):                                   # pixel by pixel: one singular Hessian must not abort the rest
+            try:
+                ref[p] = _oracle(gq[:, None, p:p + 1], i0q, musq, 30)[0, 0]
+            except np.linalg.LinAlgError:
+                pass
+    out32 = gn_decompose(gq, i0q, musq, 30, dtype=F32).cpu().numpy()
+    out64 = gn_decompose(gq, i0q, musq, 30, dtype=F64).cpu().numpy()
+    fin = np.isfinite(ref).all(axis=1)
+    assert fin[60:].all() and fin[:60].sum() >= 10            # the oracle itself loses some of the starved pixels
+    assert np.isfinite(out32[fin]).all() and np.isfinite(out64[fin]).all()
+    # ordinary pixels: the usual tolerances
+    assert scale_rel_err(out64[60:], ref[60:]) < 1e-9
+    assert scale_rel_err(out32[60:], ref[60:]) < 1e-4
+    # starved pixels: the Newton map is chaotic there (float64 results of two summation orders already differ in the
+    # 4th digit), so only the bulk is compared: the float64 pass of the single-precision kernel follows the float64
+    # kernel (it sums the bins in another order) on most of them
+    st = np.flatnonzero(fin[:60])
+    rel = np.abs(out32[st] - out64[st]).max(axis=1) / np.maximum(np.abs(out64[st]).max(axis=1), 1.0)
+    assert np.median(rel) < 1e-4
