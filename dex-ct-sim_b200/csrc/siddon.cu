@@ -136,6 +136,102 @@ __global__ void __launch_bounds__(SKIP_THREADS) skip_build_kernel(SkipBuildArgs 
     }
 }
 
+// 3-D skip layouts.  A cone-beam ray climbs at most mu_z = max |dz/dp| planes per column (about 0.07 for CT cone angles),
+// so over a run of S columns it stays within 1 + S mu_z planes of the plane it starts in.  The 2-D sweep above is therefore
+// run once per z plane on the labels ANDed over a slab of planes: at level l the word is homogeneous only if the 2 l + 3
+// planes k-l-1 .. k+l+1 carry the same label at both voxels of the pair, and runs of that level are capped at
+// cap_l = floor((l + 1) / mu_z) columns.  The word stores the longest run over the levels; its meaning for the walk is the
+// same as in 2-D (every voxel the ray can touch in the next S columns has label l), whatever its z slope.
+constexpr int SKIP_LEVELS = 4;       // z radii 1..4 planes
+
+// rz [k][i][j] = number of planes on BOTH sides of k (capped at SKIP_LEVELS) that carry the label of voxel (i, j, k);
+// outside the volume counts as label 0.  Reads the low bytes of a pair layout, so i is the layout's column (major) index.
+__global__ void rz_kernel(const uint16_t *__restrict__ pairs, int np, int nq, int nz, int pitch, long long plane,
+                          uint8_t *__restrict__ rz)
+{
+    const int j = blockIdx.x * blockDim.x + threadIdx.x, i = blockIdx.y;
+    if (j >= nq) return;
+    const uint16_t *src = pairs + plane + (long long)i * pitch + (j + 1);
+    uint8_t *dst = rz + (long long)i * nq + j;
+    const long long vplane = (long long)np * nq;
+    unsigned prev = 0, run = SKIP_LEVELS;                  // below the volume: air, homogeneous
+    for (int k = 0; k < nz; ++k) {
+        const unsigned l = src[k * plane] & 0xffu;
+        run = (l == prev) ? min(run + 1u, (unsigned)SKIP_LEVELS) : 0u;
+        dst[k * vplane] = (uint8_t)run;
+        prev = l;
+    }
+    prev = 0; run = SKIP_LEVELS;
+    for (int k = nz - 1; k >= 0; --k) {
+        const unsigned l = src[k * plane] & 0xffu;
+        run = (l == prev) ? min(run + 1u, (unsigned)SKIP_LEVELS) : 0u;
+        dst[k * vplane] = (uint8_t)min(run, (unsigned)dst[k * vplane]);
+        prev = l;
+    }
+}
+
+struct SkipBuild3Args {
+    const uint16_t *pairs[2];        // whole pair layouts (z aprons included)
+    const uint8_t *rz[2];            // [nz][np][nq] per axis
+    uint16_t *out[4];
+    int np[2], nq[2], pitch[2];
+    long long plane[2];
+    int cap[SKIP_LEVELS];
+};
+
+__global__ void __launch_bounds__(SKIP_THREADS) skip_build3_kernel(SkipBuild3Args A)
+{
+    extern __shared__ uint16_t sk_buf[];                   // [SKIP_LEVELS][2][n_ent + 2]
+    const int lay = blockIdx.x, ax = lay >> 1, k = blockIdx.y;
+    const bool mirror = (lay & 1) != 0;
+    const int np = A.np[ax], nq = A.nq[ax], n_ent = nq + 1, pitch = A.pitch[ax];
+    const uint16_t *__restrict__ pairs = A.pairs[ax] + (long long)(k + 1) * A.plane[ax];
+    const uint8_t *__restrict__ rz = A.rz[ax] + (long long)k * np * nq;
+    uint16_t *__restrict__ out = A.out[lay] + (long long)(k + 1) * A.plane[ax];
+    const int ld = n_ent + 2;
+    for (int t = threadIdx.x; t < 2 * SKIP_LEVELS * ld; t += blockDim.x) sk_buf[t] = 0x00ff;
+    __syncthreads();
+    int cur = 0;
+    for (int i = np - 1; i >= 0; --i) {
+        unsigned word[SKIP_EPT], rzp[SKIP_EPT];
+#pragma unroll
+        for (int u = 0; u < SKIP_EPT; ++u) {
+            const int jj = threadIdx.x + u * SKIP_THREADS;
+            word[u] = 0; rzp[u] = 0;
+            if (jj < n_ent) {
+                const int oj = mirror ? nq - jj : jj;      // entry of the un-mirrored layout: pair (oj - 1, oj)
+                word[u] = pairs[(long long)i * pitch + oj];
+                const unsigned ra = oj - 1 >= 0 ? rz[(long long)i * nq + oj - 1] : SKIP_LEVELS;
+                const unsigned rb = oj < nq ? rz[(long long)i * nq + oj] : SKIP_LEVELS;
+                rzp[u] = min(ra, rb);
+            }
+        }
+#pragma unroll
+        for (int u = 0; u < SKIP_EPT; ++u) {
+            const int jj = threadIdx.x + u * SKIP_THREADS;
+            if (jj < n_ent) {
+                const unsigned b0 = word[u] & 0x7f, b1 = (word[u] >> 8) & 0x7f;
+                const unsigned lo = mirror ? b1 : b0, hi = mirror ? b0 : b1;
+                unsigned best = 0;
+#pragma unroll
+                for (int l = 0; l < SKIP_LEVELS; ++l) {
+                    const uint16_t *prev = sk_buf + (2 * l + cur) * ld + 1;
+                    uint16_t *next = sk_buf + (2 * l + (cur ^ 1)) * ld + 1;
+                    const unsigned pa = prev[jj], pb = prev[jj + 1];
+                    const unsigned sa = (pa & 0xff) == lo ? pa >> 8 : 0u, sb = (pb & 0xff) == lo ? pb >> 8 : 0u;
+                    const bool hom = lo == hi && rzp[u] >= (unsigned)(l + 1);
+                    const unsigned S = hom ? min(1u + min(sa, sb), (unsigned)A.cap[l]) : 0u;
+                    next[jj] = (uint16_t)(hom ? ((S << 8) | lo) : 0x00ffu);
+                    best = max(best, S);
+                }
+                out[(long long)i * pitch + jj] = (uint16_t)(best > 0 ? (0x8000u | (best << 8) | lo) : (lo | (hi << 8)));
+            }
+        }
+        __syncthreads();
+        cur ^= 1;
+    }
+}
+
 // ---------------------------------------------------------------------------------------------------------
 // Polyenergetic detection epilogue (forward model of matdecomp.py:116-118 with K materials):
 // counts_s = sum_e W[s][e] exp(-sum_m L_m mu[m][e]).
@@ -612,6 +708,147 @@ __global__ void __launch_bounds__(128) siddon_skip_kernel(SiddonParams P, int vi
     }
 }
 
+// ---------------------------------------------------------------------------------------------------------
+// 3-D production kernel over the 3-D skip layouts (multi-row / cone-beam scans).  Same walk as walk_skip with the z
+// coordinate carried along: w(p) = mz p + cw, plane k = floor(min(w(a), w(b))).  A homogeneous word covers every plane the
+// ray can reach during its run (see skip_build3_kernel), so it is accounted in one step exactly as in 2-D; an ordinary
+// column is split at its minor-plane crossing and its z-plane crossing into at most three pieces, whose labels come from the
+// words of planes k and k + 1 (a homogeneous word of plane k + 1 simply names the label of both voxels of its pair).
+
+__device__ __forceinline__ void skip_labels(int w, int &lo, int &hi)
+{
+    lo = w & 0x7f;
+    hi = w < 0 ? lo : (w >> 8) & 0x7f;
+}
+
+template <typename R> __device__ __forceinline__ void acc_add(R *acc, int stride, int label, R w)
+{
+    R *p = acc + label * stride;
+    *p = Rn<R>::add(*p, w);
+}
+
+template <typename R>
+__device__ __forceinline__ void walk_skip3(const uint16_t *__restrict__ W, int pitch, int plane, int i0, int i1, int i_c, R am,
+                                           R c0, R mz, R cw, R ua, R ub, R inv_am, R inv_amz, R *acc, int stride)
+{
+    typedef Rn<R> A;
+    typedef FastInt<R> F;
+    const R c0m1 = A::sub(c0, (R)1);
+    const bool mzpos = mz >= (R)0;
+    R fi = A::sub(F::real(i0 - i_c + (1 << 20)), (R)(1 << 20));
+    const R fend = A::sub(F::real(i1 - i_c + (1 << 20)), (R)(1 << 20));
+    int ofs = i0 * pitch;
+    while (fi <= fend) {
+        const R a = A::max(fi, ua);
+        const R b1 = A::min(A::add(fi, (R)1), ub);
+        const R qa = A::fma(am, a, c0);
+        const R qbm1 = A::fma(am, b1, c0m1);
+        const R wa = A::fma(mz, a, cw), wb = A::fma(mz, b1, cw);
+        const R wmin = A::min(wa, wb), wmax = A::max(wa, wb);
+        const R tj = F::bias(qa), tk = F::bias(wmin);
+        const int o = ofs + F::to_int(tj) + F::to_int(tk) * plane;
+        const int w0 = (int)(short)W[o], w1 = (int)(short)W[o + plane];
+        const bool hom = w0 < 0;
+        const int step = hom ? (w0 >> 8) & 0x7f : 1;
+        const R fnext = A::add(fi, F::real(step));
+        const R wtot = A::sub(A::min(fnext, ub), a);
+        int l00, l01, l10, l11;                                            // label(j, k), (j+1, k), (j, k+1), (j+1, k+1)
+        skip_labels(w0, l00, l01);
+        skip_labels(w1, l10, l11);
+        // column length beyond the crossing of minor plane j + 1 / spent in plane k + 1
+        R qhi = A::min(A::max(A::mul(A::sub(qbm1, F::unbias(tj)), inv_am), (R)0), wtot);
+        R zhi = A::min(A::max(A::mul(A::sub(A::sub(wmax, (R)1), F::unbias(tk)), inv_amz), (R)0), wtot);
+        qhi = hom ? (R)0 : qhi;
+        zhi = hom ? (R)0 : zhi;
+        const R tq = A::sub(wtot, qhi);                                    // p-length before the minor crossing (am >= 0)
+        const R tz = mzpos ? A::sub(wtot, zhi) : zhi;                      // p-length before the z crossing
+        const R t1 = A::min(tq, tz), t2 = A::max(tq, tz);
+        const bool qfirst = tq < tz;
+        const int lA0 = mzpos ? l00 : l10, lA1 = mzpos ? l01 : l11;        // plane the ray is in first / second along +p
+        const int lB0 = mzpos ? l10 : l00, lB1 = mzpos ? l11 : l01;
+        acc_add<R>(acc, stride, hom ? l00 : lA0, t1);
+        acc_add<R>(acc, stride, hom ? l00 : (qfirst ? lA1 : lB0), A::sub(t2, t1));
+        acc_add<R>(acc, stride, hom ? l00 : lB1, A::sub(wtot, t2));
+        ofs += step * pitch;
+        fi = fnext;
+    }
+}
+
+template <typename R, int KT, int NSP>
+__global__ void __launch_bounds__(128) siddon_skip3_kernel(SiddonParams P, int view_begin, long long n_rays, DetectArgs d)
+{
+    constexpr bool PACKED = (sizeof(R) == 4) && KT > 0;
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    const int KP = KT > 0 ? KT : d.K;
+    const int tid = threadIdx.x;
+    R *acc_s = (R *)smem_raw;                              // [KP][blockDim]
+    unsigned char *tab = smem_raw + sizeof(R) * (size_t)KP * blockDim.x;
+    R *mu_s = (R *)tab, *W_s = mu_s + (size_t)KP * d.nE, *air_s = W_s + (size_t)d.nSpec * d.nE;
+    const int nE2 = (d.nE + 1) / 2;
+    f32x2 *mu2 = (f32x2 *)tab, *W2 = mu2 + (size_t)nE2 * (KT > 0 ? KT : 1);
+    if (PACKED) {
+        air_s = (R *)(W2 + (size_t)nE2 * NSP);
+        stage_packed<(KT > 0 ? KT : 2), NSP>(d, mu2, W2, (float *)air_s);
+    } else {
+        stage_tables<R>(d, KP, mu_s, W_s, air_s);
+    }
+
+    const long long n_blk = (n_rays + blockDim.x - 1) / blockDim.x;
+    for (long long blk = blockIdx.x; blk < n_blk; blk += gridDim.x) {
+        const long long ray = blk * blockDim.x + tid;
+        if (ray >= n_rays) continue;
+        const int c = (int)(ray % P.scan.n_ch);
+        const long long line = ray / P.scan.n_ch;
+        const int r = (int)(line % P.scan.n_rows);
+        const int v = view_begin + (int)(line / P.scan.n_rows);
+        for (int m = 0; m < KP; ++m) acc_s[m * blockDim.x + tid] = (R)0;
+
+        RaySetup s;
+        ray_setup<true>(P, v, r, c, s);
+        R seglen = (R)0;
+        if (s.hit) {
+            const bool mpos = s.m >= 0.0;
+            const int pitch = s.xmajor ? P.pitch_xm : P.pitch_ym;
+            const int plane = (int)(s.xmajor ? P.plane_xm : P.plane_ym);
+            const uint16_t *W = P.skip[(s.xmajor ? 0 : 2) + (mpos ? 0 : 1)] + (long long)(s.k_c + 1) * plane +
+                                (mpos ? s.j_c : s.nq - 1 - s.j_c) + 1;
+            const double c0 = mpos ? s.cq : 1.0 - s.cq;
+            walk_skip3<R>(W, pitch, plane, s.i0, s.i1, s.i_c, (R)fabs(s.m), (R)c0, (R)s.mz, (R)s.cw, (R)s.ua, (R)s.ub,
+                          (R)s.inv_am, (R)s.inv_amz, acc_s + tid, (int)blockDim.x);
+            seglen = (R)s.seglen;
+        }
+
+        R out[MAX_SPEC];
+        if (KT > 0) {
+            R Lr[KT > 0 ? KT : 1];
+#pragma unroll
+            for (int m = 0; m < (KT > 0 ? KT : 1); ++m) Lr[m] = acc_s[m * blockDim.x + tid] * seglen;
+            if (d.L_out) {
+                R *Lo = (R *)d.L_out + ray * d.K;
+#pragma unroll
+                for (int m = 0; m < (KT > 0 ? KT : 1); ++m)
+                    if (m < d.K) Lo[m] = Lr[m];
+            }
+            if constexpr (PACKED) detect_packed<KT, NSP>(Lr, mu2, W2, nE2, out);
+            else detect_reg<R, (KT > 0 ? KT : 1)>(Lr, mu_s, W_s, d.nE, d.nSpec, out);
+        } else {
+            for (int m = 0; m < d.K; ++m) acc_s[m * blockDim.x + tid] *= seglen;
+            if (d.L_out) {
+                R *Lo = (R *)d.L_out + ray * d.K;
+                for (int m = 0; m < d.K; ++m) Lo[m] = acc_s[m * blockDim.x + tid];
+            }
+            detect<R>(acc_s + tid, blockDim.x, d.K, mu_s, W_s, d.nE, d.nSpec, out);
+        }
+#pragma unroll
+        for (int sp = 0; sp < MAX_SPEC; ++sp) {
+            if (sp < d.nSpec) {
+                ((R *)d.counts)[sp * n_rays + ray] = out[sp];
+                if (d.logs) ((R *)d.logs)[sp * n_rays + ray] = neg_log_ratio<R>(out[sp], air_s[sp]);
+            }
+        }
+    }
+}
+
 // Detection from stored lengths L [n_rays][K].
 template <typename R>
 __global__ void __launch_bounds__(128) poly_detect_kernel(const R *__restrict__ Lin, long long n_rays, DetectArgs d)
@@ -730,10 +967,17 @@ static int make_params(const DexctScan *scan, const DexctVolume *vol, const void
     P.inv_dx = 1.0 / vol->dx; P.inv_dy = 1.0 / vol->dy; P.inv_dz = 1.0 / vol->dz;
     const bool skip = L.has_skip && vol->nx + 1 <= SKIP_MAX_ENTRIES && vol->ny + 1 <= SKIP_MAX_ENTRIES;
     for (int a = 0; a < 4; ++a) P.skip[a] = skip ? (const uint16_t *)(w + L.off_skip[a]) : nullptr;
+    // steepest z slope of any ray of the scan, in planes per column: |gz| / |gp| with |gp| >= SDD / sqrt(dx^2 + dy^2)
+    const double zmax = fmax(fabs(scan->z0), fabs(scan->z0 + (scan->n_rows - 1) * scan->dzdet));
+    const double muz = zmax / vol->dz * sqrt(vol->dx * vol->dx + vol->dy * vol->dy) / scan->sdd;
+    for (int l = 0; l < 4; ++l) {
+        double cap = muz > 0 ? floor((l + 1) / muz) : 127.0;
+        P.skip_cap[l] = (int)fmin(fmax(cap, 1.0), 127.0);
+    }
     return DEXCT_OK;
 }
 
-template <typename R, int KT, int NSP>
+template <typename R, bool IS3D, int KT, int NSP>
 static int launch_skip(const SiddonParams &P, int view_begin, long long n_rays, const DetectArgs &d, cudaStream_t st)
 {
     const int block = 128;
@@ -747,7 +991,8 @@ static int launch_skip(const SiddonParams &P, int view_begin, long long n_rays, 
         set_error("material/energy tables need %zu bytes of shared memory (limit 200 KiB): K=%d nE=%d", smem, d.K, d.nE);
         return DEXCT_ECAPACITY;
     }
-    auto kern = siddon_skip_kernel<R, KT, NSP>;
+    void (*kern)(SiddonParams, int, long long, DetectArgs) = siddon_skip_kernel<R, KT, NSP>;
+    if (IS3D) kern = siddon_skip3_kernel<R, KT, NSP>;
     if (smem > 48 * 1024) DEXCT_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     int per_sm = 0;
     DEXCT_CUDA_OK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, block, smem));
@@ -762,9 +1007,10 @@ static int launch_skip(const SiddonParams &P, int view_begin, long long n_rays, 
 template <typename R, bool IS3D, int KT>
 static int launch_poly(const SiddonParams &P, int view_begin, long long n_rays, const DetectArgs &d, cudaStream_t st)
 {
-    // 2-D scans with 7-bit labels walk the skip layouts
-    if (!IS3D && P.skip[0] != nullptr && d.K <= 128)
-        return d.nSpec <= 2 ? launch_skip<R, KT, 2>(P, view_begin, n_rays, d, st) : launch_skip<R, KT, 4>(P, view_begin, n_rays, d, st);
+    // scans with 7-bit labels walk the skip layouts
+    if (P.skip[0] != nullptr && d.K <= 128)
+        return d.nSpec <= 2 ? launch_skip<R, IS3D, KT, 2>(P, view_begin, n_rays, d, st)
+                            : launch_skip<R, IS3D, KT, 4>(P, view_begin, n_rays, d, st);
     const int block = 128;
     const int KP = KT > 0 ? KT : d.K;
     const size_t smem = sizeof(R) * ((size_t)KP * block + (size_t)KP * d.nE + (size_t)d.nSpec * d.nE + MAX_SPEC);
@@ -825,7 +1071,7 @@ extern "C" int dexct_siddon_prepare(const DexctScan *scan, const DexctVolume *vo
     repack_xm_kernel<<<grid, dim3(32, 8), 0, st>>>(labels, vol->nx, vol->ny, vol->nz, (uint16_t *)(w + L.off_xm),
                                                   L.pitch_xm, L.plane_xm);
     DEXCT_CUDA_OK(cudaGetLastError());
-    if (P.skip[0]) {
+    if (P.skip[0] && !L.skip_3d) {
         SkipBuildArgs A;
         A.pairs[0] = (const uint16_t *)(w + L.off_xm) + L.plane_xm;
         A.pairs[1] = (const uint16_t *)(w + L.off_ym) + L.plane_ym;
@@ -834,6 +1080,27 @@ extern "C" int dexct_siddon_prepare(const DexctScan *scan, const DexctVolume *vo
         A.np[1] = vol->ny; A.nq[1] = vol->nx; A.pitch[1] = L.pitch_ym;
         const size_t smem = sizeof(uint16_t) * 2 * (size_t)(max(vol->nx, vol->ny) + 3);
         skip_build_kernel<<<4, SKIP_THREADS, smem, st>>>(A);
+        DEXCT_CUDA_OK(cudaGetLastError());
+    } else if (P.skip[0]) {
+        SkipBuild3Args A;
+        A.pairs[0] = (const uint16_t *)(w + L.off_xm);
+        A.pairs[1] = (const uint16_t *)(w + L.off_ym);
+        A.rz[0] = (const uint8_t *)(w + L.off_rz[0]);
+        A.rz[1] = (const uint8_t *)(w + L.off_rz[1]);
+        for (int a = 0; a < 4; ++a) A.out[a] = (uint16_t *)(w + L.off_skip[a]);
+        A.np[0] = vol->nx; A.nq[0] = vol->ny; A.pitch[0] = L.pitch_xm; A.plane[0] = L.plane_xm;
+        A.np[1] = vol->ny; A.nq[1] = vol->nx; A.pitch[1] = L.pitch_ym; A.plane[1] = L.plane_ym;
+        for (int l = 0; l < SKIP_LEVELS; ++l) A.cap[l] = P.skip_cap[l];
+        for (int ax = 0; ax < 2; ++ax) {
+            const dim3 grid((A.nq[ax] + 127) / 128, A.np[ax]);
+            rz_kernel<<<grid, 128, 0, st>>>(A.pairs[ax], A.np[ax], A.nq[ax], vol->nz, A.pitch[ax], A.plane[ax],
+                                            (uint8_t *)(w + L.off_rz[ax]));
+            DEXCT_CUDA_OK(cudaGetLastError());
+        }
+        const size_t smem = sizeof(uint16_t) * 2 * SKIP_LEVELS * (size_t)(max(vol->nx, vol->ny) + 3);
+        if (smem > 48 * 1024)
+            DEXCT_CUDA_OK(cudaFuncSetAttribute(skip_build3_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        skip_build3_kernel<<<dim3(4, vol->nz), SKIP_THREADS, smem, st>>>(A);
         DEXCT_CUDA_OK(cudaGetLastError());
     }
     return DEXCT_OK;

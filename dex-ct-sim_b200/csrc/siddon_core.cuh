@@ -20,7 +20,8 @@ struct WsLayout {
     size_t off_cosb, off_sinb, off_cosg, off_sing, off_zdet;   // double tables
     size_t off_xm, off_ym;                                     // uint16 pair layouts (bytes from workspace start)
     size_t off_skip[4];                                        // uint16 skip layouts (2-D scans only): x+, x-, y+, y-
-    bool has_skip;
+    bool has_skip, skip_3d;
+    size_t off_rz[2];                                          // z-homogeneity radius volumes (3-D scans only)
     size_t total;
     int pitch_xm, pitch_ym;                                    // entries per column (nq + 2, rounded up)
     long long plane_xm, plane_ym;                              // entries per z plane
@@ -49,11 +50,22 @@ inline WsLayout ws_layout(const DexctScan &s, const DexctVolume &v)
     L.plane_ym = (long long)v.ny * L.pitch_ym;
     L.off_xm = o; o = align_up(o + sizeof(uint16_t) * (size_t)L.plane_xm * (size_t)(v.nz + 2), 256);
     L.off_ym = o; o = align_up(o + sizeof(uint16_t) * (size_t)L.plane_ym * (size_t)(v.nz + 2), 256);
-    // skip layouts: same indexing as one plane of the pair layouts (no z apron), one per (major axis, sign of the slope)
-    L.has_skip = !scan_is_3d(s, v);
+    // skip layouts, one per (major axis, sign of the minor slope).  2-D scans: one plane, indexed like one plane of the pair
+    // layouts.  3-D scans: indexed like the whole pair layout (z aprons included), plus two byte volumes of the per-voxel
+    // z-homogeneity radius that the sweep reads (rz [nz][ny][nx] and its in-plane transpose [nz][nx][ny]).
+    L.has_skip = true;
+    L.skip_3d = scan_is_3d(s, v);
+    const size_t planes = L.skip_3d ? (size_t)v.nz + 2 : 1;
     for (int a = 0; a < 4; ++a) {
         L.off_skip[a] = o;
-        if (L.has_skip) o = align_up(o + sizeof(uint16_t) * (size_t)(a < 2 ? L.plane_xm : L.plane_ym), 256);
+        o = align_up(o + sizeof(uint16_t) * (size_t)(a < 2 ? L.plane_xm : L.plane_ym) * planes, 256);
+    }
+    L.off_rz[0] = L.off_rz[1] = o;
+    if (L.skip_3d) {
+        for (int a = 0; a < 2; ++a) {
+            L.off_rz[a] = o;
+            o = align_up(o + (size_t)v.nx * v.ny * v.nz, 256);
+        }
     }
     L.total = o;
     return L;
@@ -65,7 +77,9 @@ struct SiddonParams {
     DexctVolume vol;
     const double *cosb, *sinb, *cosg, *sing, *zdet;
     const uint16_t *xm, *ym;          // pair layouts; element (k, i, j) at ((k+1)*plane + i*pitch + (j+1))
-    const uint16_t *skip[4];          // skip layouts (2-D only; null otherwise); element (i, j) at (i*pitch + (j+1))
+    const uint16_t *skip[4];          // skip layouts (null when unavailable); element (k, i, j) at ((k+1)*plane + i*pitch + (j+1))
+                                      // for 3-D scans, (i, j) at (i*pitch + (j+1)) for 2-D scans
+    int skip_cap[4];                  // 3-D: longest run allowed at z-homogeneity level l (radius l + 1 planes)
     int pitch_xm, pitch_ym;
     long long plane_xm, plane_ym;
     double inv_dx, inv_dy, inv_dz;    // 1/voxel size, rounded once on the host
