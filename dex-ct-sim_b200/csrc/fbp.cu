@@ -103,53 +103,82 @@ __global__ void __launch_bounds__(256) fbp_filter_kernel(const R *__restrict__ s
     for (int c = n_ch + 1 + threadIdx.x; c < q_pitch; c += blockDim.x) dst[c] = (R)0;
 }
 
-template <typename R> struct FbpMath;
-template <> struct FbpMath<float> {
-    static __device__ __forceinline__ float atan_ratio(float num, float den) { return atanf(num / den); }
-    static __device__ __forceinline__ float floor(float x) { return floorf(x); }
+// Channel coordinate and 1/L^2 of a pixel for one view.  FAST (single precision, fan half-angle below atan(0.85) = 40 deg):
+// reciprocal by MUFU.RCP plus one Newton step, atan by an odd degree-17 minimax polynomial on |t| <= 0.85 (absolute error
+// 6e-8 rad evaluated in float, against 4.5e-8 for a correctly rounded atanf); t is clamped to that range first -- beyond it
+// the ray misses the detector anyway.  Otherwise: IEEE division and atan2.
+constexpr float FBP_T0 = 0.85f;
+template <typename R, bool FAST> struct FbpMath {
+    static __device__ __forceinline__ R gamma(R negB, R A) { return atan2(negB, A); }
+    static __device__ __forceinline__ R inv(R x) { return (R)1 / x; }
 };
-template <> struct FbpMath<double> {
-    static __device__ __forceinline__ double atan_ratio(double num, double den) { return atan2(num, den); }
-    static __device__ __forceinline__ double floor(double x) { return ::floor(x); }
+template <> struct FbpMath<float, true> {
+    static __device__ __forceinline__ float rcp(float x)
+    {
+        float r;
+        asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x));
+        return r;
+    }
+    static __device__ __forceinline__ float gamma(float negB, float A)
+    {
+        const float r0 = rcp(A);
+        const float r = fmaf(r0, fmaf(-A, r0, 1.0f), r0);
+        const float t = fminf(fmaxf(negB * r, -FBP_T0), FBP_T0);
+        const float u = t * t;
+        float q = 0.0057596251515161295f;
+        q = fmaf(q, u, -0.02522639020233572f);
+        q = fmaf(q, u, 0.05444744168992351f);
+        q = fmaf(q, u, -0.08292680841837932f);
+        q = fmaf(q, u, 0.1093448867911483f);
+        q = fmaf(q, u, -0.142630518713619f);
+        q = fmaf(q, u, 0.19998517545978775f);
+        q = fmaf(q, u, -0.33333295659610157f);
+        return fmaf(t * u, q, t);
+    }
+    static __device__ __forceinline__ float inv(float x) { return rcp(x); }
 };
 
 // One image pixel per thread, all views of the range in a loop.  The 32 pixels of a warp are neighbours along x: for
 // one view they fall on a short run of channels, so the two gathers per pixel hit a couple of L1 lines of a filtered
 // line that lives in L2 for the whole launch.
-template <typename R>
+template <typename R, bool FAST>
 __global__ void __launch_bounds__(256) fbp_backproject_kernel(const R *__restrict__ q, int q_pitch, const R *__restrict__ cs,
                                                               int view_count, int n_rows, int n_ch, R sid, R gamma0,
                                                               R inv_dgamma, int n, R px, R scale, int accumulate,
                                                               R *__restrict__ image)
 {
+    typedef FbpMath<R, FAST> M;
     const int ix = blockIdx.x * blockDim.x + threadIdx.x;
     const int iy = blockIdx.y * blockDim.y + threadIdx.y;
     const int row = blockIdx.z;
     if (ix >= n || iy >= n) return;
     const R half = (R)0.5 * (R)(n - 1);
     const R x = ((R)ix - half) * px, y = ((R)iy - half) * px;
-    const R umax = (R)n_ch;
+    const R umax = (R)n_ch, ubias = -gamma0 * inv_dgamma;
     const R *line = q + (long long)row * q_pitch + 1;
     const long long view_stride = (long long)n_rows * q_pitch;
-    R acc = (R)0;
-#pragma unroll 2
-    for (int v = 0; v < view_count; ++v) {
+    R acc0 = (R)0, acc1 = (R)0;
+    auto one = [&](int v, R &acc) {
         const R cb = cs[2 * v], sb = cs[2 * v + 1];
-        const R A = sid - (x * cb + y * sb);
-        const R B = y * cb - x * sb;
-        const R gam = FbpMath<R>::atan_ratio(-B, A);
-        R u = (gam - gamma0) * inv_dgamma;
+        const R A = sid - fma(y, sb, x * cb);
+        const R negB = fma(x, sb, -(y * cb));
+        const R gam = M::gamma(negB, A);
+        R u = fma(gam, inv_dgamma, ubias);
         u = fmin(fmax(u, (R)-1), umax);
-        const R fl = fmin(FbpMath<R>::floor(u), umax - (R)1);
-        const int i0 = (int)fl;
+        const R fl = fmin(floor(u), umax - (R)1);
         const R f = u - fl;
-        const R *p = line + v * view_stride + i0;
+        const R *p = line + v * view_stride + (int)fl;
         const R q0 = p[0], q1 = p[1];
-        const R val = fma(f, q1 - q0, q0);
-        acc += val / fma(A, A, B * B);
+        acc = fma(fma(f, q1 - q0, q0), M::inv(fma(A, A, negB * negB)), acc);
+    };
+    int v = 0;
+    for (; v + 1 < view_count; v += 2) {              // two independent accumulation chains
+        one(v, acc0);
+        one(v + 1, acc1);
     }
+    if (v < view_count) one(v, acc0);
     R *out = image + ((long long)row * n + iy) * n + ix;
-    const R r = acc * scale;
+    const R r = (acc0 + acc1) * scale;
     *out = accumulate ? *out + r : r;
 }
 
@@ -182,8 +211,13 @@ static int fbp_run(const DexctScan &s, const void *sino, int view_begin, int vie
         (const R *)sino, s.n_ch, s.gamma0, s.dgamma, s.sid, taps, q, L.q_pitch);
     DEXCT_CUDA_OK(cudaGetLastError());
     const dim3 block(32, 8), grid((n + 31) / 32, (n + 7) / 8, s.n_rows);
-    fbp_backproject_kernel<R><<<grid, block, 0, st>>>(q, L.q_pitch, cs, view_count, s.n_rows, s.n_ch, (R)s.sid, (R)s.gamma0,
-                                                     (R)(1.0 / s.dgamma), n, (R)(fov / n), (R)s.dbeta, accumulate, (R *)image);
+    // fast path: the whole detector (plus the one-channel taper) inside the polynomial's range
+    const double gmax = fmax(fabs(s.gamma0), fabs(s.gamma0 + (s.n_ch - 1) * s.dgamma)) + 2.0 * s.dgamma;
+    const bool fast = sizeof(R) == 4 && gmax < atan((double)FBP_T0);
+    auto kern = fbp_backproject_kernel<R, false>;
+    if (fast) kern = fbp_backproject_kernel<R, sizeof(R) == 4>;
+    kern<<<grid, block, 0, st>>>(q, L.q_pitch, cs, view_count, s.n_rows, s.n_ch, (R)s.sid, (R)s.gamma0, (R)(1.0 / s.dgamma), n,
+                                 (R)(fov / n), (R)s.dbeta, accumulate, (R *)image);
     DEXCT_CUDA_OK(cudaGetLastError());
     return DEXCT_OK;
 }

@@ -241,3 +241,24 @@ def test_c4_slab_3d_parity_and_chords():
         assert scale_rel_err(L[2:3].cpu().numpy(), L_ref) < TOL[dtype]
         c_ref, _ = oracle.poly_detect(L_ref, mu, W, want_log=False)
         assert scale_rel_err(counts[:, 2].reshape(2, -1).cpu().numpy(), c_ref) < TOL[dtype]
+
+
+@pytest.mark.parametrize('dtype', [F32, F64])
+@pytest.mark.parametrize('h_iso,voxz', [(1.2, 51.2 / 96), (0.5, 0.2), (2.0, 1.0)])
+def test_steep_cone_on_anatomy_like_volume(dtype, h_iso, voxz):
+    """3-D skip layouts under stress: ellipsoidal body and inserts (long homogeneous runs in x, y AND z), wide cone angles
+    and anisotropic voxels, so that the run caps of every z-homogeneity level come into play."""
+    n, nz, n_rows, n_ch, n_views = 96, 48, 16, 110, 24
+    lab = S.phantom_labels(n, nz)
+    vox = 51.2 / n
+    voxel = (vox, vox, voxz)
+    scan = make_scan(n_views, n_ch, FAN, 60.0, 100.0, n_rows=n_rows, h_iso=h_iso, beta0=0.1)
+    pj = Projector(scan, lab, voxel)
+    sc = oracle.Scan(lab, voxel, 60.0, 100.0, pj.tables_host())
+    mu, W = _tables(S.K)
+    counts, logs, L = pj.project(mu, W, dtype=dtype, want_log=True, want_L=True)
+    L_ref, seg = sc.classic_lengths(S.K)
+    assert seg > 0
+    assert scale_rel_err(L.cpu().numpy(), L_ref) < TOL[dtype]
+    c_ref, l_ref, _ = sc.project_poly(mu, W)
+    assert scale_rel_err(counts.cpu().numpy(), c_ref) < TOL[dtype]
