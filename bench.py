@@ -55,6 +55,7 @@ def parse():
     ap.add_argument('--cpu-views', type=int, default=0, help='views in the CPU sample (0 = auto)')
     ap.add_argument('--no-cpu-baseline', action='store_true')
     ap.add_argument('--no-e2e', action='store_true')
+    ap.add_argument('--no-extra', action='store_true', help='skip the secondary measurements (3-D projector, FBP)')
     return ap.parse_args()
 
 
@@ -272,14 +273,20 @@ def run_b200(args):
         pj.project(mu, W, view_begin=v0, view_count=nv, dtype=code, want_log=True, counts=counts, logs=logs)
         if timers is not None:
             timers[1].record()
+        pending = []
+        if ws > 1:
+            # the sinogram gathers ride NCCL's stream behind the projection and overlap the decomposition, which only
+            # needs the local view shard
+            pending.append(dist.all_gather_into_tensor(g_counts, counts, async_op=True))
+            pending.append(dist.all_gather_into_tensor(g_logs, logs, async_op=True))
         gn_decompose(counts.view(2, -1), i0, mus, GN_ITERS, mask_thresh=MASK_THRESH, dtype=code, out=basis.view(-1, 2),
                      reduce_max_over_ranks=ws > 1)
         if timers is not None:
             timers[2].record()
         if ws > 1:
-            dist.all_gather_into_tensor(g_counts, counts)
-            dist.all_gather_into_tensor(g_logs, logs)
-            dist.all_gather_into_tensor(g_basis, basis)
+            pending.append(dist.all_gather_into_tensor(g_basis, basis, async_op=True))
+            for w in pending:
+                w.wait()
 
     def barrier():
         if ws > 1:
@@ -367,7 +374,7 @@ def run_b200(args):
             'data': 'synthetic',
             'config': {'workload': WORKLOAD, 'views_total': n_views, 'rays_per_step': rays_local * ws, 'gn_iters': GN_ITERS,
                        'l2': 'flushed between timed steps (256 MiB write)', 'parallelism': f'view-sharded x{ws}',
-                       'collective': 'all-gather of counts/logs/basis sinograms inside the step' if ws > 1 else 'none'},
+                       'collective': 'all-gather of counts/logs (overlapping the decomposition) and basis sinograms inside the step' if ws > 1 else 'none'},
             'kernel_ms': {'siddon_poly': t_sid, 'gn': t_gn},
             'siddon_rays_per_s': rays_local * ws / (t_sid * 1e-3), 'gn_pixels_per_s': rays_local * ws / (t_gn * 1e-3),
             'roofline': {'bound': 'hbm', 'achieved': ach, 'peak': hbm, 'unit': 'GB/s', 'frac': ach / hbm, 'traffic': None,
@@ -388,10 +395,73 @@ def run_b200(args):
             dtc = time.perf_counter() - t0
             arm.close()
             line['cpu_baseline'] = arm.describe(arm.n_views * N_CH / dtc)
+        if ws == 1 and not args.no_extra:
+            line['extra'] = extra_measurements(dev, args.dtype)
         print(json.dumps(line), flush=True)
     if ws > 1:
         dist.barrier()
         dist.destroy_process_group()
+
+
+def extra_measurements(dev, dtype):
+    """Secondary device timings, reported beside the headline (never part of `value`): the 3-D (cone-beam) projector on
+    two 48-view ranges of config C4 against the same bytes-per-ray roofline, and fan-beam FBP of one C2 sinogram."""
+    import torch
+    from dexct import synthetic as S
+    from dexct.ops import Projector, count_segments, fbp_fan, make_scan
+    from xtomosim import forward_project as FP
+    peaks = {}
+    try:
+        peaks = json.load(open(os.path.join(ROOT, 'MEASURED_PEAKS.json')))
+    except Exception:                                                     # noqa: BLE001
+        pass
+    hbm = float(peaks.get('hbm_gbs', 6650.0))
+    td = torch.float32 if dtype == 'f32' else torch.float64
+    esz = 4 if dtype == 'f32' else 8
+
+    def timed(fn, reps):
+        for _ in range(2):
+            fn()
+        torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for _ in range(reps):
+            fn()
+        e1.record()
+        torch.cuda.synchronize()
+        return e0.elapsed_time(e1) / reps
+
+    out = {}
+    ct, ph, lo, hi = S.make_config('C2')
+    scan = make_scan(ct.N_proj, ct.N_channels, ct.gamma_fan, ct.SID, ct.SDD, rotation=ct.rotation)
+    pj = Projector(scan, ph.M, (ph.dx, ph.dy, ph.dz), device=dev)
+    mu = torch.as_tensor(ph.mu_table(lo.E), dtype=td, device=dev)
+    W = torch.as_tensor(np.stack([FP.spectral_weights(ct, lo)]), dtype=td, device=dev)
+    _, logs, _ = pj.project(mu, W, dtype=dtype)
+    sino = logs[0, :, 0, :].contiguous()
+    t = timed(lambda: fbp_fan(scan, sino, 512, 51.2, 0.8, dtype=dtype), 10)
+    out['fbp_c2'] = {'ms': t, 'workload': '1000 views x 900 ch -> 512 x 512, ramp 0.8', 'pixel_views_per_s': 512 * 512 * 1000 / (t * 1e-3)}
+    out['prepare_c2_ms'] = timed(pj.prepare, 10)
+    del pj
+    n_views = 48
+    ct, ph, lo, hi = S.make_config('C4')
+    scan = make_scan(ct.N_proj, ct.N_channels, ct.gamma_fan, ct.SID, ct.SDD, n_rows=ct.N_rows, h_iso=ct.h_iso, rotation=ct.rotation)
+    pj = Projector(scan, ph.M, (ph.dx, ph.dy, ph.dz), device=dev)
+    out['prepare_c4_ms'] = timed(pj.prepare, 3)
+    mu = torch.as_tensor(ph.mu_table(lo.E), dtype=td, device=dev)
+    W = torch.as_tensor(np.stack([FP.spectral_weights(ct, lo), FP.spectral_weights(ct, hi)]), dtype=td, device=dev)
+    counts = torch.empty((2, n_views, ct.N_rows, ct.N_channels), dtype=td, device=dev)
+    logs = torch.empty_like(counts)
+    rays = n_views * ct.N_rows * ct.N_channels
+    out['siddon_3d_c4'] = []
+    for v0 in (0, 150):
+        t = timed(lambda: pj.project(mu, W, view_begin=v0, view_count=n_views, dtype=dtype, counts=counts, logs=logs), 5)
+        seg = count_segments(pj, v0, 4) / (4 * ct.N_rows * ct.N_channels)
+        ach = rays * (seg + 2 * esz) / (t * 1e-3) / 1e9
+        out['siddon_3d_c4'].append({'views': [v0, v0 + n_views], 'ms': t, 'rays_per_s': rays / (t * 1e-3), 'segments_per_ray': seg,
+                                    'roofline': {'bound': 'hbm', 'achieved': ach, 'peak': hbm, 'unit': 'GB/s', 'frac': ach / hbm}})
+    out['workload_c4'] = '512^3 phantom, 64 rows x 900 ch, 48 of 1200 views per range, 120 bins, 2 spectra fused'
+    return out
 
 
 def main():
