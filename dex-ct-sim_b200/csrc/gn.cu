@@ -131,7 +131,7 @@ __global__ void gn_table_kernel(const float *__restrict__ i0, const float *__res
 }
 
 template <typename R, int PX, bool CTAB>
-__global__ void __launch_bounds__(256) gn_kernel(const R *__restrict__ g, const R *__restrict__ i0, const R *__restrict__ mus,
+__global__ void __launch_bounds__(256, (PX == 4 && CTAB) ? 3 : 1) gn_kernel(const R *__restrict__ g, const R *__restrict__ i0, const R *__restrict__ mus,
                                                  int nE, long long P, int n_iters, R mask_thresh, void *scratch,
                                                  R *__restrict__ a_out)
 {

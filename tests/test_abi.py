@@ -43,7 +43,9 @@ def test_version_and_workspace_size_need_no_gpu():
     assert (2 * 3 + 4) * 512 * 514 * 2 <= nbytes < (2 * 3 + 4) * 512 * 530 * 2 + 64 * 1024
     vol3 = N.DexctVolume(512, 512, 4, 0, 0.1, 0.1, 0.1)
     n3 = L.dexct_siddon_workspace_bytes(C.byref(scan), C.byref(vol3))
-    assert 2 * 6 * 512 * 514 * 2 <= n3 < 2 * 6 * 512 * 530 * 2 + 64 * 1024      # 3-D: pair layouts only
+    # 3-D: two pair layouts and four skip layouts of nz + 2 planes each, plus two z-homogeneity radius volumes (1 B / voxel)
+    rz = 2 * 512 * 512 * 4
+    assert 6 * 6 * 512 * 514 * 2 + rz <= n3 < 6 * 6 * 512 * 530 * 2 + rz + 64 * 1024
     bad = N.DexctVolume(0, 512, 1, 0, 0.1, 0.1, 0.1)
     assert L.dexct_siddon_workspace_bytes(C.byref(scan), C.byref(bad)) == 0
 
