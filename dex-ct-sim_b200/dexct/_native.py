@@ -52,6 +52,9 @@ SIGNATURES = {
     'dexct_fbp_fan': (C.c_int, [C.POINTER(DexctScan), _P, C.c_int32, C.c_int32, C.c_int32, C.c_double, C.c_double,
                                 _P, C.c_int32, _P, C.c_int32, _P]),
     'dexct_fbp_hu': (C.c_int, [_P, C.c_int64, C.c_double, _P, C.c_int32, _P]),
+    'dexct_poisson_noise': (C.c_int, [_P, _P, C.c_int64, C.c_uint64, C.c_uint32, C.c_uint64, C.c_double, C.c_double,
+                                      C.c_int32, _P]),
+    'dexct_vmi': (C.c_int, [_P, _P, C.c_int64, C.c_double, C.c_double, C.c_double, C.c_int32, _P, C.c_int32, _P]),
 }
 
 _lib = None

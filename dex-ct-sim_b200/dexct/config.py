@@ -14,3 +14,12 @@ shard_views = os.environ.get('DEXCT_SHARD_VIEWS', '1') != '0'
 
 # Print progress the way the reference does (matdecomp.py:111-112)
 verbose = os.environ.get('DEXCT_VERBOSE', '0') != '0'
+
+# Poisson counting statistics on the simulated counts.  Off by default so that results are
+# deterministic functions of the inputs; a scanner object can override it (FanBeamGeometry(noise=...)).  The generator is
+# counter-based (Philox4x32-10 keyed by noise_seed, addressed by the element's index in the whole sinogram), so the
+# noise realisation does not depend on how views are sharded over GPUs.
+noise = os.environ.get('DEXCT_NOISE', '0') != '0'
+noise_seed = int(os.environ.get('DEXCT_NOISE_SEED', '20240'))
+# sino_log of a noisy scan is -ln(max(counts, noise_floor) / air counts): a pixel that detected nothing stays finite
+noise_floor = 0.5

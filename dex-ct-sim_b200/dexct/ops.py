@@ -251,3 +251,38 @@ def hounsfield(image, mu_water, dtype=F32, out=None):
     with torch.cuda.device(image.device):
         N.check(N.lib().dexct_fbp_hu(N.ptr(image), image.numel(), float(mu_water), N.ptr(out), code, N.stream_ptr()))
     return out
+
+
+def poisson_noise(counts, seed, stream_id=0, offset=0, logs=None, air_counts=1.0, floor_counts=0.5, dtype=F32):
+    """In place: every element of ``counts`` becomes a Poisson variate of that mean (the
+    spectra are scaled to photons per pixel per view at /root/reference/main.py:68).  ``offset`` is the index of
+    ``counts.view(-1)[0]`` in the whole sinogram, so view shards draw what a single GPU would.  ``logs`` (optional, same
+    shape) receives ``-ln(max(counts, floor_counts) / air_counts)``."""
+    N.require_device()
+    code = dtype_code(dtype)
+    if not (counts.is_cuda and counts.is_contiguous() and counts.dtype == _TORCH_DTYPE[code]):
+        raise ValueError('counts must be a contiguous CUDA tensor of the compute dtype')
+    if logs is not None and (logs.shape != counts.shape or logs.dtype != counts.dtype or not logs.is_contiguous()
+                             or logs.device != counts.device):
+        raise ValueError('logs must match counts in shape, dtype and device')
+    with torch.cuda.device(counts.device):
+        N.check(N.lib().dexct_poisson_noise(N.ptr(counts), N.ptr(logs) if logs is not None else None, counts.numel(),
+                                            int(seed) & 0xFFFFFFFFFFFFFFFF, int(stream_id) & 0xFFFFFFFF, int(offset),
+                                            float(air_counts), float(floor_counts), code, N.stream_ptr()))
+    return counts
+
+
+def vmi(m1, m2, u1, u2, u_water, hu=True, dtype=F32):
+    """Virtual monoenergetic image ``u1 m1 + u2 m2`` (in HU when ``hu``) from two basis-material images on the device;
+    float32 result like the reference's make_vmi (/root/reference/plots.py:136-144)."""
+    N.require_device()
+    code = dtype_code(dtype)
+    td = _TORCH_DTYPE[code]
+    if not (m1.is_cuda and m1.shape == m2.shape and m1.dtype == td and m2.dtype == td and m1.device == m2.device):
+        raise ValueError('m1 and m2 must be CUDA tensors of the compute dtype and equal shape')
+    m1, m2 = m1.contiguous(), m2.contiguous()
+    out = torch.empty(m1.shape, dtype=torch.float32, device=m1.device)
+    with torch.cuda.device(m1.device):
+        N.check(N.lib().dexct_vmi(N.ptr(m1), N.ptr(m2), m1.numel(), float(u1), float(u2), float(u_water), int(bool(hu)),
+                                  N.ptr(out), code, N.stream_ptr()))
+    return out

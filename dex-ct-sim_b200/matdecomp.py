@@ -131,3 +131,18 @@ def get_basismat_sinos(ct, sino_raw_1, sino_raw_2, spec1, spec2, n_iters=30, mas
     """
     a = do_matdecomp_gn(ct, sino_raw_1, sino_raw_2, spec1, spec2, n_iters, mask_thresh=mask_thresh)
     return a[..., 0], a[..., 1]
+
+
+def make_vmi(E0, M1, M2, HU=True, matcomp1=matcomp1, matcomp2=matcomp2):
+    """Virtual monoenergetic image at ``E0`` keV from the two basis-material images (the reference's helper of the same
+    name and signature, /root/reference/plots.py:136-144): ``u1 M1 + u2 M2``, in Hounsfield units when ``HU``; float32.
+    The three attenuation lookups stay on the host (three numbers); the image arithmetic is one kernel."""
+    from dexct.ops import vmi
+    E = np.array([E0]).astype(np.float64)
+    u1, u2 = float(xc.mixatten(matcomp1, E)[0]), float(xc.mixatten(matcomp2, E)[0])
+    uw = float(1.0 * xc.mixatten('H(11.2)O(88.8)', E)[0])
+    td = torch.float32 if config.dtype == 'f32' else torch.float64
+    dev = torch.device('cuda', torch.cuda.current_device())
+    m1 = torch.as_tensor(np.ascontiguousarray(M1), dtype=td, device=dev)
+    m2 = torch.as_tensor(np.ascontiguousarray(M2), dtype=td, device=dev)
+    return vmi(m1, m2, u1, u2, uw, hu=HU, dtype=dtype_code(config.dtype)).cpu().numpy()

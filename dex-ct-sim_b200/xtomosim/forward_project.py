@@ -14,7 +14,7 @@ import numpy as np
 import torch
 
 from dexct import config, dist
-from dexct.ops import Projector, make_scan, poly_detect, dtype_code
+from dexct.ops import Projector, make_scan, poisson_noise, poly_detect, dtype_code
 
 _state = {}      # (id(ct), id(phantom)) -> _ScanState
 
@@ -112,8 +112,29 @@ def _project_groups(ct, phantom, specs, dtype=None, want_log=True):
                                             want_L=keep_L)
             if keep_L:
                 st.L, st.L_dtype = L, code
+        if noise_enabled(ct):
+            _add_noise(ct, c, lg if want_log else None, W, v0, code)
         out.append((c, lg))
     return out, (v0, nv)
+
+
+def noise_enabled(ct):
+    flag = getattr(ct, 'noise', None)
+    return config.noise if flag is None else bool(flag)
+
+
+def _add_noise(ct, counts, logs, W, v0, code):
+    """Poisson statistics on the counts ``[n_spectra, views_local, n_rows, n_ch]`` of one group, in place; the log
+    sinograms are recomputed from the noisy counts.  Every acquisition (spectrum) takes the scanner's next random stream;
+    elements are addressed by their index in the whole scan, so the result is independent of the view sharding."""
+    seed = getattr(ct, 'noise_seed', None)
+    seed = config.noise_seed if seed is None else int(seed)
+    per_view = ct.N_rows * ct.N_channels
+    for n in range(counts.shape[0]):
+        stream_id = getattr(ct, 'noise_stream', 0)
+        poisson_noise(counts[n], seed, stream_id=stream_id, offset=v0 * per_view, logs=None if logs is None else logs[n],
+                      air_counts=float(np.sum(W[n])), floor_counts=config.noise_floor, dtype=code)
+        ct.noise_stream = stream_id + 1
 
 
 def _to_host(tensors, ct):

@@ -58,11 +58,15 @@ class FanBeamGeometry:
     """Third-generation equiangular fan-beam scanner (cone beam when N_rows > 1).
 
     Positional signature as used by the reference (plots.py:109-111).  Keyword extensions (not in the reference):
-    ``N_rows`` detector rows, ``rotation`` total gantry angle, ``beta0`` start angle.
+    ``N_rows`` detector rows, ``rotation`` total gantry angle, ``beta0`` start angle; ``noise`` (None = follow
+    ``dexct.config.noise``) switches Poisson counting statistics on for this scanner, ``noise_seed`` keys its generator.
     """
 
     def __init__(self, N_channels, N_proj, gamma_fan, SID, SDD, h_iso=1.0, eid=True, detector_file=None,
-                 N_rows=1, rotation=2.0 * np.pi, beta0=0.0, det_E=None, det_eta_E=None):
+                 N_rows=1, rotation=2.0 * np.pi, beta0=0.0, det_E=None, det_eta_E=None, noise=None, noise_seed=None):
+        self.noise = noise
+        self.noise_seed = noise_seed
+        self.noise_stream = 0                                # acquisitions simulated so far (one random stream each)
         self.N_channels = int(N_channels)
         self.N_proj = int(N_proj)
         self.N_rows = int(N_rows)
@@ -198,7 +202,8 @@ def read_parameter_file(path):
         ct = FanBeamGeometry(N_channels=p['N_channels'], N_proj=p['N_projections'], gamma_fan=p['fan_angle_total'],
                              SID=p['SID'], SDD=p['SDD'], h_iso=p.get('detector_px_height', 1.0),
                              eid=(p.get('detector_mode', 'eid') == 'eid'), detector_file=p.get('detector_filename'),
-                             N_rows=p.get('N_rows', 1), rotation=p.get('rotation_angle_total', 2.0 * np.pi))
+                             N_rows=p.get('N_rows', 1), rotation=p.get('rotation_angle_total', 2.0 * np.pi),
+                             noise=p.get('noise'), noise_seed=p.get('noise_seed'))
         phantom = VoxelPhantom(p.get('phantom_id', 'phantom'), p['phantom_filename'], p['matcomp_filename'],
                                p['Nx'], p['Ny'], p['Nz'], z_index=p.get('z_index', 0),
                                dx=p.get('dx', 0.1), dy=p.get('dy', 0.1), dz=p.get('dz', 0.1))

@@ -159,6 +159,23 @@ int dexct_fbp_fan(const DexctScan *scan, const void *sino, int32_t view_begin, i
  * (main.py:134-140).  In place (hu == image) is allowed.                                                        */
 int dexct_fbp_hu(const void *image, int64_t n, double mu_water, void *hu, int32_t dtype, void *stream);
 
+/* ---- quantum noise and virtual monoenergetic images -------------------------- */
+
+/* counts[i] <- one Poisson variate of mean counts[i], i in [0, n): the photon statistics of a scan whose spectra were
+ * scaled to photons per pixel per view (main.py:68).  Generator: Philox4x32-10 keyed by `seed`, counter
+ * (offset + i, block, stream_id) -- `offset` is the element's index in the WHOLE sinogram, so view-sharded ranks draw
+ * exactly the numbers a single GPU would; `stream_id` separates the acquisitions of one run (one per spectrum).
+ * Sampler: CDF inversion below mean 10, Hoermann's PTRS rejection above (exact at every mean).
+ * logs (same length) may be NULL; otherwise logs[i] <- -ln(max(counts[i], floor_counts) / air_counts).          */
+int dexct_poisson_noise(void *counts, void *logs, int64_t n, uint64_t seed, uint32_t stream_id, uint64_t offset,
+                        double air_counts, double floor_counts, int32_t dtype, void *stream);
+
+/* Virtual monoenergetic image from two basis-material images (make_vmi, plots.py:136-144):
+ * out[i] = u1 m1[i] + u2 m2[i], and with hu != 0 then 1000 (out[i] - u_water) / u_water; float32 out like the
+ * reference's .astype(np.float32).  u1, u2, u_water: mass attenuation of the bases and of water at the energy.   */
+int dexct_vmi(const void *m1, const void *m2, int64_t n, double u1, double u2, double u_water, int32_t hu,
+              float *out, int32_t dtype, void *stream);
+
 #ifdef __cplusplus
 }
 #endif
