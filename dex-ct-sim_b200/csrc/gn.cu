@@ -130,10 +130,14 @@ __global__ void gn_table_kernel(const float *__restrict__ i0, const float *__res
     for (int q = 0; q < 6; ++q) { row[2 * q] = s1 * f[q]; row[2 * q + 1] = s2 * f[q]; }
 }
 
+// Further copies of the result in peer memory (view-sharded scans, peer.cu): the epilogue stores every pixel to each of
+// them as well, so the basis sinograms are assembled on all ranks by the time the kernel ends -- no gather afterwards.
+struct GnMirrors { void *p[DEXCT_MAX_PEERS]; int n; };
+
 template <typename R, int PX, bool CTAB>
 __global__ void __launch_bounds__(256, (PX == 4 && CTAB) ? 3 : 1) gn_kernel(const R *__restrict__ g, const R *__restrict__ i0, const R *__restrict__ mus,
                                                  int nE, long long P, int n_iters, R mask_thresh, void *scratch,
-                                                 R *__restrict__ a_out)
+                                                 R *__restrict__ a_out, const GnMirrors mir)
 {
     typedef GnMath<R> M;
     constexpr bool PACKED = sizeof(R) == 4;
@@ -330,6 +334,7 @@ __global__ void __launch_bounds__(256, (PX == 4 && CTAB) ? 3 : 1) gn_kernel(cons
                 if (sizeof(R) == 4) {
                     float2 o = make_float2(masked ? 0.f : (float)a1[k], masked ? 0.f : (float)a2[k]);
                     ((float2 *)a_out)[p] = o;
+                    for (int d = 0; d < mir.n; ++d) ((float2 *)mir.p[d])[p] = o;
                     const bool finite = fabs(a1[k]) < (R)INFINITY && fabs(a2[k]) < (R)INFINITY;
                     if (!masked && !(sane[k] && finite)) {                    // rare: hand the pixel to gn_fixup_kernel
                         unsigned *fl = (unsigned *)scratch;
@@ -338,6 +343,7 @@ __global__ void __launch_bounds__(256, (PX == 4 && CTAB) ? 3 : 1) gn_kernel(cons
                 } else {
                     double2 o = make_double2(masked ? 0.0 : (double)a1[k], masked ? 0.0 : (double)a2[k]);
                     ((double2 *)a_out)[p] = o;
+                    for (int d = 0; d < mir.n; ++d) ((double2 *)mir.p[d])[p] = o;
                 }
             }
         }
@@ -350,7 +356,8 @@ __global__ void __launch_bounds__(256, (PX == 4 && CTAB) ? 3 : 1) gn_kernel(cons
 // finite, and a NaN left in a sinogram would spoil every pixel of the image reconstructed from it.
 __global__ void __launch_bounds__(128) gn_fixup_kernel(const float *__restrict__ g, const float *__restrict__ i0,
                                                        const float *__restrict__ mus, int nE, long long P, int n_iters,
-                                                       const unsigned *__restrict__ flagged, float *__restrict__ a_out)
+                                                       const unsigned *__restrict__ flagged, float *__restrict__ a_out,
+                                                       const GnMirrors mir)
 {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     double *tab = (double *)smem_raw;                                    // [nE][14]
@@ -403,7 +410,11 @@ __global__ void __launch_bounds__(128) gn_fixup_kernel(const float *__restrict__
             a1 -= (h22 * d1 - h12 * d2) * inv;
             a2 -= (h11 * d2 - h12 * d1) * inv;
         }
-        if (lane == 0) ((float2 *)a_out)[p] = make_float2((float)a1, (float)a2);
+        if (lane == 0) {
+            const float2 o = make_float2((float)a1, (float)a2);
+            ((float2 *)a_out)[p] = o;
+            for (int d = 0; d < mir.n; ++d) ((float2 *)mir.p[d])[p] = o;
+        }
     }
 }
 
@@ -420,7 +431,7 @@ static int launch_max(const void *g, long long P, void *scratch, cudaStream_t st
 
 template <typename R, int PX>
 static int launch_gn(const void *g, const void *i0, const void *mus, int nE, long long P, int n_iters, double mask_thresh,
-                     void *a_out, void *scratch, bool have_max, cudaStream_t st)
+                     void *a_out, void *scratch, bool have_max, cudaStream_t st, const GnMirrors &mir)
 {
     const char *bs = getenv("DEXCT_GN_BLOCK");         // tuning knob (threads per CTA: 128 or 256)
     const int block = (bs && atoi(bs) == 128) ? 128 : 256;
@@ -430,7 +441,7 @@ static int launch_gn(const void *g, const void *i0, const void *mus, int nE, lon
         set_error("GN table needs %zu bytes of shared memory (limit 200 KiB): nE=%d", smem, nE);
         return DEXCT_ECAPACITY;
     }
-    void (*kern)(const R *, const R *, const R *, int, long long, int, R, void *, R *) = gn_kernel<R, PX, false>;
+    void (*kern)(const R *, const R *, const R *, int, long long, int, R, void *, R *, const GnMirrors) = gn_kernel<R, PX, false>;
     if (ctab) kern = gn_kernel<R, PX, sizeof(R) == 4>;
     if (smem > 48 * 1024) DEXCT_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     int per_sm = 0;
@@ -453,7 +464,7 @@ static int launch_gn(const void *g, const void *i0, const void *mus, int nE, lon
         if (fsm > 48 * 1024)
             DEXCT_CUDA_OK(cudaFuncSetAttribute(gn_fixup_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)fsm));
         gn_fixup_kernel<<<sm_count() * 4, 128, fsm, st>>>((const float *)g, (const float *)i0, (const float *)mus, nE, P,
-                                                          n_iters, (const unsigned *)scratch, (float *)a_out);
+                                                          n_iters, (const unsigned *)scratch, (float *)a_out, mir);
         DEXCT_CUDA_OK(cudaGetLastError());
         return DEXCT_OK;
     };
@@ -467,12 +478,12 @@ static int launch_gn(const void *g, const void *i0, const void *mus, int nE, lon
         DEXCT_CUDA_OK(cudaMemcpyToSymbolAsync(gn_cexp, (const float *)slot.staging() + (size_t)(nE + 2) * GN_CROW,
                                               sizeof(float) * (size_t)(nE + 2) * 2, 0, cudaMemcpyDeviceToDevice, st));
         kern<<<(unsigned)grid, block, smem, st>>>((const R *)g, (const R *)i0, (const R *)mus, nE, P, n_iters, (R)mask_thresh,
-                                                 scratch, (R *)a_out);
+                                                 scratch, (R *)a_out, mir);
         DEXCT_CUDA_OK(cudaGetLastError());
         return fixup();
     }
     kern<<<(unsigned)grid, block, smem, st>>>((const R *)g, (const R *)i0, (const R *)mus, nE, P, n_iters, (R)mask_thresh,
-                                             scratch, (R *)a_out);
+                                             scratch, (R *)a_out, mir);
     DEXCT_CUDA_OK(cudaGetLastError());
     return sizeof(R) == 4 ? fixup() : DEXCT_OK;
 }
@@ -496,9 +507,9 @@ extern "C" int dexct_gn_air_max(const void *g1, int64_t P, void *scratch, int32_
     return dtype == DEXCT_F32 ? launch_max<float>(g1, P, scratch, st) : launch_max<double>(g1, P, scratch, st);
 }
 
-extern "C" int dexct_gn_decompose(const void *g, const void *i0, const void *mus, int32_t nE, int64_t P, int32_t n_iters,
-                                  double mask_thresh, void *a_out, void *scratch, int32_t scratch_has_max,
-                                  int32_t dtype, void *stream)
+static int gn_decompose_impl(const void *g, const void *i0, const void *mus, int32_t nE, int64_t P, int32_t n_iters,
+                             double mask_thresh, void *a_out, const GnMirrors &mir, void *scratch, int32_t scratch_has_max,
+                             int32_t dtype, void *stream)
 {
     if (int e = check_device()) return e;
     DEXCT_REQUIRE(nE >= 1 && P >= 0 && n_iters >= 0, "need nE >= 1, P >= 0, n_iters >= 0");
@@ -513,10 +524,34 @@ extern "C" int dexct_gn_decompose(const void *g, const void *i0, const void *mus
     if (dtype == DEXCT_F32) {
         const char *px = getenv("DEXCT_GN_PX");          // tuning knob (pixels per thread)
         const int npx = px ? atoi(px) : 4;            // 4: the table row of a bin is fetched once for four pixels
-        if (npx == 1) return launch_gn<float, 1>(g, i0, mus, nE, P, n_iters, mask_thresh, a_out, scratch, have, st);
-        if (npx == 3) return launch_gn<float, 3>(g, i0, mus, nE, P, n_iters, mask_thresh, a_out, scratch, have, st);
-        if (npx == 2) return launch_gn<float, 2>(g, i0, mus, nE, P, n_iters, mask_thresh, a_out, scratch, have, st);
-        return launch_gn<float, 4>(g, i0, mus, nE, P, n_iters, mask_thresh, a_out, scratch, have, st);
+        if (npx == 1) return launch_gn<float, 1>(g, i0, mus, nE, P, n_iters, mask_thresh, a_out, scratch, have, st, mir);
+        if (npx == 3) return launch_gn<float, 3>(g, i0, mus, nE, P, n_iters, mask_thresh, a_out, scratch, have, st, mir);
+        if (npx == 2) return launch_gn<float, 2>(g, i0, mus, nE, P, n_iters, mask_thresh, a_out, scratch, have, st, mir);
+        return launch_gn<float, 4>(g, i0, mus, nE, P, n_iters, mask_thresh, a_out, scratch, have, st, mir);
     }
-    return launch_gn<double, 1>(g, i0, mus, nE, P, n_iters, mask_thresh, a_out, scratch, have, st);
+    return launch_gn<double, 1>(g, i0, mus, nE, P, n_iters, mask_thresh, a_out, scratch, have, st, mir);
+}
+
+extern "C" int dexct_gn_decompose(const void *g, const void *i0, const void *mus, int32_t nE, int64_t P, int32_t n_iters,
+                                  double mask_thresh, void *a_out, void *scratch, int32_t scratch_has_max,
+                                  int32_t dtype, void *stream)
+{
+    GnMirrors mir{};
+    return gn_decompose_impl(g, i0, mus, nE, P, n_iters, mask_thresh, a_out, mir, scratch, scratch_has_max, dtype, stream);
+}
+
+extern "C" int dexct_gn_decompose_mirrored(const void *g, const void *i0, const void *mus, int32_t nE, int64_t P,
+                                           int32_t n_iters, double mask_thresh, void *a_out, void *const *mirrors_host,
+                                           int32_t n_mirrors, void *scratch, int32_t scratch_has_max, int32_t dtype,
+                                           void *stream)
+{
+    DEXCT_REQUIRE(n_mirrors >= 0 && n_mirrors <= DEXCT_MAX_PEERS && (n_mirrors == 0 || mirrors_host),
+                  "0 <= n_mirrors <= DEXCT_MAX_PEERS and a pointer table required");
+    GnMirrors mir{};
+    mir.n = n_mirrors;
+    for (int i = 0; i < n_mirrors; ++i) {
+        DEXCT_REQUIRE(mirrors_host[i] && ((uintptr_t)mirrors_host[i] & 15) == 0, "mirror %d is null or not 16-byte aligned", i);
+        mir.p[i] = mirrors_host[i];
+    }
+    return gn_decompose_impl(g, i0, mus, nE, P, n_iters, mask_thresh, a_out, mir, scratch, scratch_has_max, dtype, stream);
 }

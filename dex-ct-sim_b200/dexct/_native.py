@@ -54,6 +54,18 @@ SIGNATURES = {
     'dexct_fbp_hu': (C.c_int, [_P, C.c_int64, C.c_double, _P, C.c_int32, _P]),
     'dexct_poisson_noise': (C.c_int, [_P, _P, C.c_int64, C.c_uint64, C.c_uint32, C.c_uint64, C.c_double, C.c_double,
                                       C.c_int32, _P]),
+    'dexct_peer_ctrl_bytes': (C.c_size_t, []),
+    'dexct_peer_alloc': (C.c_int, [C.c_size_t, C.POINTER(C.c_void_p)]),
+    'dexct_peer_free': (C.c_int, [_P]),
+    'dexct_peer_export': (C.c_int, [_P, _P]),
+    'dexct_peer_open': (C.c_int, [_P, C.POINTER(C.c_void_p)]),
+    'dexct_peer_close': (C.c_int, [_P]),
+    'dexct_peer_barrier': (C.c_int, [_P, C.c_int32, C.c_int32, C.c_uint64, C.c_double, _P]),
+    'dexct_peer_max_key': (C.c_int, [_P, C.c_int32, C.c_int32, C.c_uint64, _P, C.c_int32, C.c_double, _P]),
+    'dexct_peer_status': (C.c_int, [_P, C.POINTER(C.c_int32), _P]),
+    'dexct_peer_push': (C.c_int, [_P, C.c_size_t, _P, C.c_int32, C.c_int32, C.c_int32, _P]),
+    'dexct_gn_decompose_mirrored': (C.c_int, [_P, _P, _P, C.c_int32, C.c_int64, C.c_int32, C.c_double, _P, _P, C.c_int32,
+                                              _P, C.c_int32, C.c_int32, _P]),
     'dexct_vmi': (C.c_int, [_P, _P, C.c_int64, C.c_double, C.c_double, C.c_double, C.c_int32, _P, C.c_int32, _P]),
 }
 

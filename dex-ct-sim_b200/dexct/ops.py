@@ -172,12 +172,15 @@ def poly_detect(L, mu, W, dtype=F32, want_log=True):
     return counts, logs
 
 
-def gn_decompose(g, i0, mus, n_iters, mask_thresh=0.0, dtype=F32, out=None, reduce_max_over_ranks=False):
+def gn_decompose(g, i0, mus, n_iters, mask_thresh=0.0, dtype=F32, out=None, reduce_max_over_ranks=False, peers=None,
+                 mirrors=None):
     """g [2, ...] counts (device tensor or array), i0 [2, nE], mus [2, nE] -> a [..., 2] device tensor.
 
     ``reduce_max_over_ranks``: the pixels are one shard of a larger sinogram; the air threshold then uses the maximum of the
     first measurement over ALL ranks (one 8-byte integer MAX all-reduce), as the unsharded reference does
-    (matdecomp.py:196)."""
+    (matdecomp.py:196) -- through ``peers`` (a dexct.peer.PeerGroup: flags in peer memory) when given, else NCCL.
+    ``mirrors``: ctypes table of further device addresses (peer copies of the basis sinogram, SymBuffer.table) that the
+    kernel's epilogue stores every pixel to as well."""
     N.require_device()
     code = dtype_code(dtype)
     td = _TORCH_DTYPE[code]
@@ -197,11 +200,19 @@ def gn_decompose(g, i0, mus, n_iters, mask_thresh=0.0, dtype=F32, out=None, redu
         if reduce_max_over_ranks and mask_thresh > 0:
             import torch.distributed as dist
             N.check(N.lib().dexct_gn_air_max(N.ptr(g), P, N.ptr(scratch), code, N.stream_ptr()))
-            key = scratch[:8].view(torch.int64) if code == F64 else scratch[:4].view(torch.int32)
-            dist.all_reduce(key, op=dist.ReduceOp.MAX)
+            if peers is not None:
+                peers.max_key(scratch, code)
+            else:
+                key = scratch[:8].view(torch.int64) if code == F64 else scratch[:4].view(torch.int32)
+                dist.all_reduce(key, op=dist.ReduceOp.MAX)
             have_max = 1
-        N.check(N.lib().dexct_gn_decompose(N.ptr(g), N.ptr(i0), N.ptr(mus), nE, P, int(n_iters), float(mask_thresh),
-                                           N.ptr(out), N.ptr(scratch), have_max, code, N.stream_ptr()))
+        if mirrors is not None and len(mirrors):
+            N.check(N.lib().dexct_gn_decompose_mirrored(N.ptr(g), N.ptr(i0), N.ptr(mus), nE, P, int(n_iters), float(mask_thresh),
+                                                        N.ptr(out), mirrors, len(mirrors), N.ptr(scratch), have_max, code,
+                                                        N.stream_ptr()))
+        else:
+            N.check(N.lib().dexct_gn_decompose(N.ptr(g), N.ptr(i0), N.ptr(mus), nE, P, int(n_iters), float(mask_thresh),
+                                               N.ptr(out), N.ptr(scratch), have_max, code, N.stream_ptr()))
     gn_decompose.last_scratch = scratch          # diagnostics: bytes 8..12 = pixels redone in float64 (single precision)
     return out
 

@@ -34,9 +34,11 @@ def mu_table(E_keV, materials=MATERIALS):
     return np.array([m['density'] * (m['c_C'] * kn + m['c_P'] * (E / 60.0) ** -3.0) for m in materials])
 
 
-def phantom_labels(n, nz=1, n_inserts=24, seed=SEED):
+def phantom_labels(n, nz=1, n_inserts=24, seed=SEED, device=None):
     """uint8 labels [nz, n, n]: air, a soft-tissue body ellipse/ellipsoid (semi-axes 0.42 n, 0.30 n voxels; 0.45 nz in z),
-    and ``n_inserts`` random ellipsoidal inserts of labels 2..7 inside the body."""
+    and ``n_inserts`` random ellipsoidal inserts of labels 2..7 inside the body.  With ``device`` the volume is rasterised
+    there with torch (same arithmetic, same result) and returned as a tensor: the 1024^3 phantom of config C5 takes minutes
+    in numpy."""
     rng = np.random.default_rng(seed)
     c = 0.5 * (n - 1)
     cz = 0.5 * (nz - 1)
@@ -54,6 +56,8 @@ def phantom_labels(n, nz=1, n_inserts=24, seed=SEED):
         czi = cz + rng.uniform(-0.3, 0.3) * nz
         rot = rng.uniform(0, np.pi)
         ins.append((lab, cx, cy, czi, rx, ry, rz, rot))
+    if device is not None:
+        return _labels_on_device(n, nz, ins, c, cz, az, device)
     out = np.zeros((nz, n, n), dtype=np.uint8)
     for k in range(nz):
         zz = ((k - cz) / az) ** 2 if nz > 1 else 0.0
@@ -71,9 +75,38 @@ def phantom_labels(n, nz=1, n_inserts=24, seed=SEED):
     return out
 
 
-def make_phantom(n=512, nz=1, voxel=0.1, seed=SEED, closed_form=True):
+def _labels_on_device(n, nz, ins, c, cz, az, device):
+    import torch
+    dev = torch.device(device)
+    f32, f64 = torch.float32, torch.float64
+    x = torch.arange(n, dtype=f32, device=dev)[None, None, :]
+    y = torch.arange(n, dtype=f32, device=dev)[None, :, None]
+    x64, y64 = x.to(f64), y.to(f64)
+    out = torch.empty((nz, n, n), dtype=torch.uint8, device=dev)
+    plane = ((x - c) / (0.42 * n)) ** 2 + ((y - c) / (0.30 * n)) ** 2          # float32 like the numpy path
+    step = max(1, min(nz, (1 << 26) // (n * n)))
+    for k0 in range(0, nz, step):
+        k = torch.arange(k0, min(k0 + step, nz), dtype=f64, device=dev)[:, None, None]
+        zz = (((k - cz) / az) ** 2).to(f32) if nz > 1 else torch.zeros_like(k, dtype=f32)
+        body = plane + zz < 1.0
+        sl = body.to(torch.uint8)
+        for lab, cx, cy, czi, rx, ry, rz, rot in ins:
+            dz2 = ((k - czi) / rz) ** 2 if nz > 1 else torch.zeros_like(k)
+            if not bool((dz2 < 1.0).any()):
+                continue
+            xr = (x64 - cx) * np.cos(rot) + (y64 - cy) * np.sin(rot)
+            yr = -(x64 - cx) * np.sin(rot) + (y64 - cy) * np.cos(rot)
+            hit = body & ((xr / rx) ** 2 + (yr / ry) ** 2 + dz2 < 1.0) & (dz2 < 1.0)
+            sl = torch.where(hit, torch.full_like(sl, lab), sl)
+        out[k0:k0 + sl.shape[0]] = sl
+    return out
+
+
+def make_phantom(n=512, nz=1, voxel=0.1, seed=SEED, closed_form=True, device=None):
+    """``device``: rasterise the labels there and keep them as a tensor (``VoxelPhantom.M`` is then a CUDA tensor, accepted
+    by dexct.ops.Projector; the numpy-facing drop-in entry points need the default host array)."""
     ph = VoxelPhantom(f'synthetic_{n}x{n}x{nz}', None, None, n, n, nz, z_index=nz // 2 if nz > 1 else 0,
-                      dx=voxel, dy=voxel, dz=voxel, labels=phantom_labels(n, nz, seed=seed), materials=MATERIALS)
+                      dx=voxel, dy=voxel, dz=voxel, labels=phantom_labels(n, nz, seed=seed, device=device), materials=MATERIALS)
     if closed_form:
         ph.mu_table = lambda E, _m=MATERIALS: mu_table(E, _m)      # bench configs use the closed-form tables
     return ph
@@ -104,7 +137,7 @@ CONFIGS = {
 }
 
 
-def make_config(name, n_views=None, nz=None, n=None):
+def make_config(name, n_views=None, nz=None, n=None, device=None):
     """(ct, phantom, spec_low, spec_high) of a named configuration; sizes can be overridden for small test cases."""
     c = dict(CONFIGS[name])
     if n_views is not None:
@@ -115,7 +148,7 @@ def make_config(name, n_views=None, nz=None, n=None):
         c['voxel'] = c['voxel'] * c['n'] / n
         c['n'] = n
     ct = make_scanner(c['n_ch'], c['n_views'], c['n_rows'], c['h_iso'])
-    ph = make_phantom(c['n'], c['nz'], c['voxel'])
+    ph = make_phantom(c['n'], c['nz'], c['voxel'], device=device)
     lo, hi = make_spectra(c['n_bins'])
     return ct, ph, lo, hi
 

@@ -137,11 +137,16 @@ class VoxelPhantom:
             if raw.size != self.Nx * self.Ny * self.Nz:
                 raise ValueError(f'{filename}: {raw.size} bytes, expected {self.Nx}x{self.Ny}x{self.Nz}')
             labels = raw.reshape(self.Nz, self.Ny, self.Nx)
-        labels = np.ascontiguousarray(labels, dtype=np.uint8)
+        if type(labels).__module__.startswith('torch'):      # device-resident labels (large synthetic volumes)
+            if str(labels.dtype) != 'torch.uint8':
+                raise ValueError('label tensors must be uint8')
+            labels = labels.contiguous()
+        else:
+            labels = np.ascontiguousarray(labels, dtype=np.uint8)
         if labels.ndim == 2:
             labels = labels[None]
-        if labels.shape != (self.Nz, self.Ny, self.Nx):
-            raise ValueError(f'labels have shape {labels.shape}, expected {(self.Nz, self.Ny, self.Nx)}')
+        if tuple(labels.shape) != (self.Nz, self.Ny, self.Nx):
+            raise ValueError(f'labels have shape {tuple(labels.shape)}, expected {(self.Nz, self.Ny, self.Nx)}')
         self.M = labels
         self.materials = read_materials(matcomp_filename) if materials is None else list(materials)
         if int(self.M.max()) >= len(self.materials):

@@ -40,6 +40,9 @@ extern "C" {
 #define DEXCT_ENODEVICE   (-3)   /* no sm_100 device: there is NO CPU fallback */
 #define DEXCT_ECAPACITY   (-4)   /* tables too large for on-chip staging */
 
+#define DEXCT_MAX_PEERS         16   /* ranks of one node whose memory a rank can map (peer section below) */
+#define DEXCT_PEER_HANDLE_BYTES 64   /* size of an exported memory handle */
+
 /* Scan geometry: third-generation equiangular fan (cone when n_rows > 1), source on a circle in the z = 0 plane.
  * Mirrors the fields of the reference's FanBeamGeometry(N_channels, N_proj, gamma_fan, SID, SDD, h_iso, ...)
  * (/root/reference/plots.py:109-111, input/params.txt:18-27).
@@ -175,6 +178,41 @@ int dexct_poisson_noise(void *counts, void *logs, int64_t n, uint64_t seed, uint
  * reference's .astype(np.float32).  u1, u2, u_water: mass attenuation of the bases and of water at the energy.   */
 int dexct_vmi(const void *m1, const void *m2, int64_t n, double u1, double u2, double u_water, int32_t hu,
               float *out, int32_t dtype, void *stream);
+
+/* ---- peer memory: view-sharded scans on one NVLink/NVSwitch node -------------------- *
+ * One process per GPU.  Each rank allocates its copy of a sinogram buffer with dexct_peer_alloc, exports it, and opens
+ * the handles of all other ranks (exchanged by the host program, e.g. torch.distributed.all_gather_object); results
+ * are then STORED into every rank's copy by the producing kernels -- dexct_gn_decompose_mirrored's epilogue, or
+ * dexct_peer_push for a finished buffer -- in place of an all-gather.  Synchronisation uses a small control block per
+ * rank (dexct_peer_ctrl_bytes, allocated and exchanged the same way, zero-initialised by dexct_peer_alloc):
+ * "ctrl_ptrs_host" below is the host array of the world_size control-block addresses AS MAPPED IN THE CALLING PROCESS,
+ * own block at index `rank`.  `epoch` must be 1, 2, 3, ... over successive calls, the same on every rank (separate
+ * sequences for dexct_peer_barrier and dexct_peer_max_key).  A wait longer than timeout_s gives up and is reported
+ * by dexct_peer_status (0 = healthy, r + 1 = rank r never arrived).                                               */
+size_t dexct_peer_ctrl_bytes(void);
+int dexct_peer_alloc(size_t bytes, void **ptr_host);          /* cudaMalloc + zero fill (exportable allocation) */
+int dexct_peer_free(void *ptr);
+int dexct_peer_export(const void *ptr, void *handle64_host);   /* DEXCT_PEER_HANDLE_BYTES bytes out */
+int dexct_peer_open(const void *handle64_host, void **ptr_host);
+int dexct_peer_close(void *ptr);
+/* All ranks' earlier work on `stream` (including stores into peer memory) is complete and visible when the barrier
+ * kernel of every rank has finished.                                                                             */
+int dexct_peer_barrier(void *const *ctrl_ptrs_host, int32_t rank, int32_t world_size, uint64_t epoch, double timeout_s,
+                       void *stream);
+/* Integer MAX all-reduce of the air-maximum key written by dexct_gn_air_max (key = its scratch, int32 for DEXCT_F32,
+ * int64 for DEXCT_F64), in place; then dexct_gn_decompose(..., scratch_has_max = 1).                               */
+int dexct_peer_max_key(void *const *ctrl_ptrs_host, int32_t rank, int32_t world_size, uint64_t epoch, void *key,
+                       int32_t dtype, double timeout_s, void *stream);
+int dexct_peer_status(const void *ctrl_local, int32_t *status_host, void *stream);   /* synchronises */
+/* Copy src[0, bytes) to dst_ptrs_host[d] for every d != skip (skip = -1: all); pointers 16-byte aligned, bytes a
+ * multiple of 16.  max_ctas bounds the grid (0 = one CTA per SM) so the copy can share the GPU with a compute kernel. */
+int dexct_peer_push(const void *src, size_t bytes, void *const *dst_ptrs_host, int32_t n_dst, int32_t skip,
+                    int32_t max_ctas, void *stream);
+/* dexct_gn_decompose whose epilogue also stores each pixel's result to the same index of n_mirrors further arrays
+ * (the other ranks' copies of the basis sinogram, offset to this rank's pixel range).                             */
+int dexct_gn_decompose_mirrored(const void *g_2xP, const void *i0_2xE, const void *mus_2xE, int32_t nE, int64_t P,
+                                int32_t n_iters, double mask_thresh, void *a_out_Px2, void *const *mirrors_host,
+                                int32_t n_mirrors, void *scratch, int32_t scratch_has_max, int32_t dtype, void *stream);
 
 #ifdef __cplusplus
 }
