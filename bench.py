@@ -45,6 +45,13 @@ WORKLOAD = ('C2: 512x512x1 phantom (K=8 materials), 900 ch x 1000 views per GPU,
             'GN 10 iters water/bone, air mask 0.95')
 
 
+# N > 1: the finished count/log shard goes to the peers through a store kernel on 16 CTAs beside the decomposition, whose
+# resident wave owns the rest of the SMs.  Measured at N = 8 (profiles/r01h_scaling.txt): 16 CTAs 0.855 ms per step,
+# 48 CTAs 0.876, 148 CTAs 0.920, copy engines (DEXCT_PUSH=dma) 0.905, NCCL all-gathers 1.195.
+PUSH_DMA = os.environ.get('DEXCT_PUSH', 'sm') == 'dma'
+PUSH_CTAS = int(os.environ.get('DEXCT_PUSH_CTAS', '16'))
+
+
 def parse():
     ap = argparse.ArgumentParser()
     ap.add_argument('--gpus', type=int, default=1)
@@ -56,6 +63,8 @@ def parse():
     ap.add_argument('--no-cpu-baseline', action='store_true')
     ap.add_argument('--no-e2e', action='store_true')
     ap.add_argument('--no-extra', action='store_true', help='skip the secondary measurements (3-D projector, FBP)')
+    ap.add_argument('--collective', default='peer', choices=['peer', 'nccl'],
+                    help='N > 1: assemble the sinograms by stores into peer memory (default) or by NCCL all-gathers')
     return ap.parse_args()
 
 
@@ -256,13 +265,40 @@ def run_b200(args):
     i0 = torch.as_tensor(i0_h, dtype=td, device=dev)
     mus = torch.as_tensor(mus_h, dtype=td, device=dev)
     rays_local = nv * N_CH
-    counts = torch.empty((2, nv, 1, N_CH), dtype=td, device=dev)
-    logs = torch.empty_like(counts)
-    basis = torch.empty((nv, 1, N_CH, 2), dtype=td, device=dev)
-    if ws > 1:
-        g_counts = torch.empty((ws, 2, nv, 1, N_CH), dtype=td, device=dev)
-        g_logs = torch.empty_like(g_counts)
-        g_basis = torch.empty((ws, nv, 1, N_CH, 2), dtype=td, device=dev)
+    # N > 1: every rank ends the step holding the whole view-major sinograms.  'peer': the buffers are symmetric
+    # allocations mapped into every rank (dexct/peer.py); the projection writes its shard in place, a store kernel on a
+    # side stream copies it into the 7 other copies while the decomposition runs, the decomposition's epilogue stores each
+    # basis pixel into all copies, and the air maximum is exchanged through flags in peer memory -- no NCCL call in the
+    # step.  'nccl': the same with three all-gathers and one all-reduce.
+    pg = None
+    collective = 'none'
+    if ws > 1 and args.collective == 'peer':
+        from dexct.peer import PeerGroup
+        try:
+            pg = PeerGroup()
+            collective = 'peer'
+        except Exception as exc:                                          # noqa: BLE001
+            if rank == 0:
+                print(f'bench.py: peer memory unavailable ({exc}); using NCCL all-gathers', file=sys.stderr)
+    if ws > 1 and pg is None:
+        collective = 'nccl'
+    esz = 4 if args.dtype == 'f32' else 8
+    if pg is not None:
+        slot_s, slot_b = 4 * nv * N_CH * esz, nv * N_CH * 2 * esz
+        sbuf, bbuf = pg.alloc(ws * slot_s), pg.alloc(ws * slot_b)
+        g_sino = sbuf.view(td, (ws, 4, nv, 1, N_CH))                      # [rank][counts lo, hi, logs lo, hi]
+        g_basis = bbuf.view(td, (ws, nv, 1, N_CH, 2))
+        counts, logs, basis = g_sino[rank, 0:2], g_sino[rank, 2:4], g_basis[rank]
+        mirrors = bbuf.table(rank * slot_b, exclude_self=True)
+        side = torch.cuda.Stream(device=dev)
+    else:
+        counts = torch.empty((2, nv, 1, N_CH), dtype=td, device=dev)
+        logs = torch.empty_like(counts)
+        basis = torch.empty((nv, 1, N_CH, 2), dtype=td, device=dev)
+        if ws > 1:
+            g_counts = torch.empty((ws, 2, nv, 1, N_CH), dtype=td, device=dev)
+            g_logs = torch.empty_like(g_counts)
+            g_basis = torch.empty((ws, nv, 1, N_CH, 2), dtype=td, device=dev)
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)      # > 126 MB L2
 
     ev = lambda: torch.cuda.Event(enable_timing=True)                   # noqa: E731
@@ -273,6 +309,18 @@ def run_b200(args):
         pj.project(mu, W, view_begin=v0, view_count=nv, dtype=code, want_log=True, counts=counts, logs=logs)
         if timers is not None:
             timers[1].record()
+        if pg is not None:
+            main = torch.cuda.current_stream()
+            side.wait_stream(main)
+            with torch.cuda.stream(side):
+                pg.push(g_sino[rank], sbuf, rank * slot_s, dma=PUSH_DMA, max_ctas=PUSH_CTAS)
+            gn_decompose(counts.reshape(2, -1), i0, mus, GN_ITERS, mask_thresh=MASK_THRESH, dtype=code, out=basis.view(-1, 2),
+                         reduce_max_over_ranks=True, peers=pg, mirrors=mirrors)
+            if timers is not None:
+                timers[2].record()
+            main.wait_stream(side)
+            pg.barrier()                                    # every rank's stores have landed in every copy
+            return
         pending = []
         if ws > 1:
             # the sinogram gathers ride NCCL's stream behind the projection and overlap the decomposition, which only
@@ -311,6 +359,16 @@ def run_b200(args):
         marks.append(t)
     barrier()
     clocks = sampler.finish() if sampler else None
+    peer_ok = None
+    if pg is not None:
+        # the peer-assembled buffers against NCCL's all-gather of the same shards (outside the timed region)
+        chk_s, chk_b = torch.empty_like(g_sino), torch.empty_like(g_basis)
+        dist.all_gather_into_tensor(chk_s, g_sino[rank].contiguous())
+        dist.all_gather_into_tensor(chk_b, g_basis[rank].contiguous())
+        ok = torch.tensor([int(torch.equal(chk_s, g_sino) and torch.equal(chk_b, g_basis))], device=dev)
+        dist.all_reduce(ok, op=dist.ReduceOp.MIN)
+        peer_ok = bool(int(ok[0]))
+        del chk_s, chk_b
     tot = sum(t[0].elapsed_time(t[3]) for t in marks)
     t_sid = sum(t[0].elapsed_time(t[1]) for t in marks) / args.steps
     t_gn = sum(t[1].elapsed_time(t[2]) for t in marks) / args.steps
@@ -374,8 +432,14 @@ def run_b200(args):
             'data': 'synthetic',
             'config': {'workload': WORKLOAD, 'views_total': n_views, 'rays_per_step': rays_local * ws, 'gn_iters': GN_ITERS,
                        'l2': 'flushed between timed steps (256 MiB write)', 'parallelism': f'view-sharded x{ws}',
-                       'collective': 'all-gather of counts/logs (overlapping the decomposition) and basis sinograms inside the step' if ws > 1 else 'none'},
+                       'collective': {'none': 'none',
+                                      'peer': 'none from a library: counts/logs pushed into the peers\' copies by a store kernel beside the '
+                                              'decomposition, basis sinograms stored to all copies by the GN epilogue, air maximum and end-of-step '
+                                              'barrier through flags in peer memory (CUDA IPC over NVLink)',
+                                      'nccl': 'all-gather of counts/logs (overlapping the decomposition) and basis sinograms + MAX all-reduce '
+                                              'inside the step'}[collective]},
             'kernel_ms': {'siddon_poly': t_sid, 'gn': t_gn},
+            **({'peer_buffers_equal_nccl_all_gather': peer_ok} if peer_ok is not None else {}),
             'siddon_rays_per_s': rays_local * ws / (t_sid * 1e-3), 'gn_pixels_per_s': rays_local * ws / (t_gn * 1e-3),
             'roofline': {'bound': 'hbm', 'achieved': ach, 'peak': hbm, 'unit': 'GB/s', 'frac': ach / hbm, 'traffic': None,
                          'kernel': 'siddon_poly_kernel', 'bytes_per_ray': bytes_per_ray, 'segments_per_ray': seg,
@@ -383,7 +447,8 @@ def run_b200(args):
             'roofline_gn': {'bound': 'fp32_fma', 'achieved': gn_flops / (t_gn * 1e-3) / 1e12, 'peak': fma_peak, 'unit': 'TFLOP/s',
                             'frac': gn_flops / (t_gn * 1e-3) / 1e12 / fma_peak, 'kernel': 'gn_kernel',
                             'flop_per_pixel': 28.0 * nE * GN_ITERS},
-            'gpu_launches': 5 * args.steps, 'clocks': clocks,     # siddon_skip, gn_max, gn_table, gn_kernel, gn_fixup per step
+            # per step: siddon_skip, gn_max, gn_table, gn_kernel, gn_fixup (+ peer_push, peer_max, peer_barrier at N > 1)
+            'gpu_launches': (8 if pg is not None else 5) * args.steps, 'clocks': clocks,
         }
         if e2e:
             line['e2e'] = e2e
@@ -398,6 +463,11 @@ def run_b200(args):
         if ws == 1 and not args.no_extra:
             line['extra'] = extra_measurements(dev, args.dtype)
         print(json.dumps(line), flush=True)
+    if pg is not None:
+        status = pg.status()
+        pg.close()
+        if status:
+            raise SystemExit(f'bench.py: rank {rank} waited in vain for rank {status - 1} (peer flags)')
     if ws > 1:
         dist.barrier()
         dist.destroy_process_group()

@@ -211,3 +211,19 @@ extern "C" int dexct_peer_push(const void *src, size_t bytes, void *const *dst_p
     DEXCT_CUDA_OK(cudaGetLastError());
     return DEXCT_OK;
 }
+
+// The same transfer on the copy engines: one device-to-device DMA per destination, no SM time at all -- the choice when
+// the copy runs beside a compute kernel that fills every SM (the decomposition's resident wave).
+extern "C" int dexct_peer_push_dma(const void *src, size_t bytes, void *const *dst_ptrs_host, int32_t n_dst, int32_t skip,
+                                   void *stream)
+{
+    if (int e = check_device()) return e;
+    if (bytes == 0) return DEXCT_OK;
+    DEXCT_REQUIRE(src && dst_ptrs_host && n_dst >= 1 && n_dst <= MAXP, "src and a table of 1..DEXCT_MAX_PEERS destinations required");
+    for (int d = 0; d < n_dst; ++d) {
+        if (d == skip) continue;
+        DEXCT_REQUIRE(dst_ptrs_host[d], "destination %d is null", d);
+        DEXCT_CUDA_OK(cudaMemcpyAsync(dst_ptrs_host[d], src, bytes, cudaMemcpyDeviceToDevice, (cudaStream_t)stream));
+    }
+    return DEXCT_OK;
+}

@@ -64,6 +64,7 @@ SIGNATURES = {
     'dexct_peer_max_key': (C.c_int, [_P, C.c_int32, C.c_int32, C.c_uint64, _P, C.c_int32, C.c_double, _P]),
     'dexct_peer_status': (C.c_int, [_P, C.POINTER(C.c_int32), _P]),
     'dexct_peer_push': (C.c_int, [_P, C.c_size_t, _P, C.c_int32, C.c_int32, C.c_int32, _P]),
+    'dexct_peer_push_dma': (C.c_int, [_P, C.c_size_t, _P, C.c_int32, C.c_int32, _P]),
     'dexct_gn_decompose_mirrored': (C.c_int, [_P, _P, _P, C.c_int32, C.c_int64, C.c_int32, C.c_double, _P, _P, C.c_int32,
                                               _P, C.c_int32, C.c_int32, _P]),
     'dexct_vmi': (C.c_int, [_P, _P, C.c_int64, C.c_double, C.c_double, C.c_double, C.c_int32, _P, C.c_int32, _P]),

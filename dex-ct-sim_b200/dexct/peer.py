@@ -124,8 +124,10 @@ class PeerGroup:
             N.check(N.lib().dexct_peer_max_key(self._ctrl_table, self.rank, self.world_size, self._max_epoch, N.ptr(scratch),
                                                int(code), self.timeout_s, N.stream_ptr()))
 
-    def push(self, src, buf, offset_bytes, max_ctas=0):
-        """Store the contiguous tensor ``src`` at ``offset_bytes`` of every OTHER rank's copy of ``buf``."""
+    def push(self, src, buf, offset_bytes, max_ctas=0, dma=False):
+        """Store the contiguous tensor ``src`` at ``offset_bytes`` of every OTHER rank's copy of ``buf`` -- with a store
+        kernel on at most ``max_ctas`` CTAs (0: one per SM), or, ``dma=True``, on the copy engines (no SM time: for a copy
+        that runs beside a kernel occupying every SM)."""
         if self.world_size == 1:
             return
         if not src.is_contiguous():
@@ -135,7 +137,10 @@ class PeerGroup:
             raise ValueError('push needs 16-byte aligned offset and size inside the buffer')
         tab = buf.table(offset_bytes, exclude_self=True)
         with torch.cuda.device(self.device):
-            N.check(N.lib().dexct_peer_push(N.ptr(src), nb, tab, len(tab), -1, int(max_ctas), N.stream_ptr()))
+            if dma:
+                N.check(N.lib().dexct_peer_push_dma(N.ptr(src), nb, tab, len(tab), -1, N.stream_ptr()))
+            else:
+                N.check(N.lib().dexct_peer_push(N.ptr(src), nb, tab, len(tab), -1, int(max_ctas), N.stream_ptr()))
 
     def status(self):
         """0 when every wait so far was answered in time, else 1 + the rank that never arrived (synchronises)."""

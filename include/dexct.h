@@ -208,6 +208,8 @@ int dexct_peer_status(const void *ctrl_local, int32_t *status_host, void *stream
  * multiple of 16.  max_ctas bounds the grid (0 = one CTA per SM) so the copy can share the GPU with a compute kernel. */
 int dexct_peer_push(const void *src, size_t bytes, void *const *dst_ptrs_host, int32_t n_dst, int32_t skip,
                     int32_t max_ctas, void *stream);
+/* The same transfer on the copy engines (one DMA per destination; no alignment requirement, no SM time). */
+int dexct_peer_push_dma(const void *src, size_t bytes, void *const *dst_ptrs_host, int32_t n_dst, int32_t skip, void *stream);
 /* dexct_gn_decompose whose epilogue also stores each pixel's result to the same index of n_mirrors further arrays
  * (the other ranks' copies of the basis sinogram, offset to this rank's pixel range).                             */
 int dexct_gn_decompose_mirrored(const void *g_2xP, const void *i0_2xE, const void *mus_2xE, int32_t nE, int64_t P,

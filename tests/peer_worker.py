@@ -33,7 +33,7 @@ def main():
     for step in range(1, 6):
         mine = torch.full((n,), float(100 * step + rank), device=dev)
         full[rank].copy_(mine)
-        pg.push(full[rank], buf, rank * n * 4, max_ctas=8)
+        pg.push(full[rank], buf, rank * n * 4, max_ctas=8, dma=(step % 2 == 0))
         pg.barrier()
         torch.cuda.synchronize()
         want = torch.tensor([100.0 * step + r for r in range(ws)], device=dev)[:, None].expand(ws, n)
