@@ -420,6 +420,12 @@ def run_b200(args):
             pass
         hbm = float(peaks.get('hbm_gbs', 6650.0))
         seg = count_segments(pj, v0, min(nv, 100)) / (min(nv, 100) * N_CH)
+        traffic, traffic_src = None, None
+        try:                                                              # measured under ncu, committed with its source
+            tr = json.load(open(os.path.join(ROOT, 'profiles', 'ncu_traffic.json')))['siddon_skip_kernel']
+            traffic, traffic_src = tr['dram_bytes_read'] + tr['dram_bytes_write'], tr['source']
+        except Exception:                                                 # noqa: BLE001
+            pass
         bytes_per_ray = seg * 1 + 2 * (4 if args.dtype == 'f32' else 8)
         ach = rays_local * bytes_per_ray / (t_sid * 1e-3) / 1e9
         sm_mhz = (clocks or {}).get('sm_mhz') or peaks.get('sm_max_mhz', 1965.0)
@@ -441,8 +447,9 @@ def run_b200(args):
             'kernel_ms': {'siddon_poly': t_sid, 'gn': t_gn},
             **({'peer_buffers_equal_nccl_all_gather': peer_ok} if peer_ok is not None else {}),
             'siddon_rays_per_s': rays_local * ws / (t_sid * 1e-3), 'gn_pixels_per_s': rays_local * ws / (t_gn * 1e-3),
-            'roofline': {'bound': 'hbm', 'achieved': ach, 'peak': hbm, 'unit': 'GB/s', 'frac': ach / hbm, 'traffic': None,
-                         'kernel': 'siddon_poly_kernel', 'bytes_per_ray': bytes_per_ray, 'segments_per_ray': seg,
+            'roofline': {'bound': 'hbm', 'achieved': ach, 'peak': hbm, 'unit': 'GB/s', 'frac': ach / hbm, 'traffic': traffic,
+                         'traffic_source': traffic_src, 'algorithmic_bytes_per_launch': rays_local * bytes_per_ray,
+                         'kernel': 'siddon_skip_kernel', 'bytes_per_ray': bytes_per_ray, 'segments_per_ray': seg,
                          'peak_source': 'MEASURED_PEAKS.json hbm_gbs' if peaks else 'fallback'},
             'roofline_gn': {'bound': 'fp32_fma', 'achieved': gn_flops / (t_gn * 1e-3) / 1e12, 'peak': fma_peak, 'unit': 'TFLOP/s',
                             'frac': gn_flops / (t_gn * 1e-3) / 1e12 / fma_peak, 'kernel': 'gn_kernel',

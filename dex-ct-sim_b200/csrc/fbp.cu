@@ -15,10 +15,14 @@
 namespace dexct {
 
 static inline size_t fbp_align(size_t x, size_t a) { return (x + a - 1) / a * a; }
+constexpr int FBP_RB_MAX = 16;   // detector rows one thread of the multi-row back-projection carries
+constexpr int FBP_WARPROWS_MIN = 24;                          // from here on lanes run along the rows (warprows kernel)
+static inline int fbp_rows_per_lane(int n_rows) { return n_rows >= 96 ? 4 : (n_rows >= 48 ? 2 : 1); }
 
 struct FbpLayout {
     size_t off_cs, off_taps, off_q, total;
     int q_pitch;                 // elements per filtered line: n_ch + 2 (one zero on either side), rounded up to 4
+    int row_pitch;               // rows per channel plane of the row-fastest layout: n_rows rounded up to FBP_RB_MAX
 };
 
 static FbpLayout fbp_layout(const DexctScan &s, int view_count, int dtype)
@@ -29,7 +33,12 @@ static FbpLayout fbp_layout(const DexctScan &s, int view_count, int dtype)
     L.off_cs = o;   o = fbp_align(o + 2 * esz * (size_t)view_count, 256);
     L.off_taps = o; o = fbp_align(o + esz * (size_t)(2 * s.n_ch - 1), 256);
     L.q_pitch = (int)fbp_align((size_t)s.n_ch + 2, 4);
-    L.off_q = o;    o = fbp_align(o + esz * (size_t)view_count * s.n_rows * L.q_pitch, 256);
+    // multi-row scans keep the filtered data row-fastest: [view][channel plane 0 .. n_ch+1][row_pitch] (see
+    // fbp_backproject_rows_kernel); the buffer is sized for whichever layout is larger
+    L.row_pitch = (int)fbp_align((size_t)s.n_rows, s.n_rows >= FBP_WARPROWS_MIN ? 32 * fbp_rows_per_lane(s.n_rows) : FBP_RB_MAX);
+    const size_t by_line = (size_t)view_count * s.n_rows * L.q_pitch;
+    const size_t by_row = (size_t)view_count * ((size_t)s.n_ch + 2) * L.row_pitch;
+    L.off_q = o;    o = fbp_align(o + esz * (by_line > by_row ? by_line : by_row), 256);
     L.total = o;
     return L;
 }
@@ -64,7 +73,8 @@ __global__ void fbp_setup_kernel(DexctScan s, int view_begin, int view_count, do
 // the line element is a broadcast.
 template <typename R>
 __global__ void __launch_bounds__(256) fbp_filter_kernel(const R *__restrict__ sino, int n_ch, double gamma0, double dgamma,
-                                                         double sid, const R *__restrict__ taps, R *__restrict__ q, int q_pitch)
+                                                         double sid, const R *__restrict__ taps, R *__restrict__ q, int q_pitch,
+                                                         int n_rows, int row_pitch)
 {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     R *line = (R *)smem_raw;                 // [n_ch]
@@ -75,7 +85,9 @@ __global__ void __launch_bounds__(256) fbp_filter_kernel(const R *__restrict__ s
         line[c] = src[c] * (R)(sid * cos(gamma0 + (double)c * dgamma));
     for (int t = threadIdx.x; t < 2 * n_ch - 1; t += blockDim.x) g[t] = taps[t];
     __syncthreads();
-    R *dst = q + ln * q_pitch;
+    // row_pitch == 0: line-major q[line][q_pitch]; else row-fastest q[view][plane][row_pitch] (plane = channel + 1)
+    const long long cstride = row_pitch ? row_pitch : 1;
+    R *dst = row_pitch ? q + (ln / n_rows) * (long long)(n_ch + 2) * row_pitch + (ln % n_rows) : q + ln * q_pitch;
     constexpr int U = 4;
     for (int c0 = threadIdx.x; c0 < n_ch; c0 += U * blockDim.x) {
         R acc[U];
@@ -96,11 +108,82 @@ __global__ void __launch_bounds__(256) fbp_filter_kernel(const R *__restrict__ s
 #pragma unroll
         for (int k = 0; k < U; ++k) {
             const int c = c0 + k * (int)blockDim.x;
-            if (c < n_ch) dst[1 + c] = acc[k] * (R)dgamma;
+            if (c < n_ch) dst[(1 + c) * cstride] = acc[k] * (R)dgamma;
         }
     }
     if (threadIdx.x == 0) dst[0] = (R)0;
-    for (int c = n_ch + 1 + threadIdx.x; c < q_pitch; c += blockDim.x) dst[c] = (R)0;
+    const int end = row_pitch ? n_ch + 2 : q_pitch;
+    for (int c = n_ch + 1 + threadIdx.x; c < end; c += blockDim.x) dst[c * cstride] = (R)0;
+}
+
+// Filter, sliding-window form: a CTA convolves 8 consecutive detector lines; thread (r, cb) produces the 8 channels
+// [8 cb, 8 cb + 8) of line r.  For 8 consecutive input channels c' it needs the 15 taps g[c - c'] of its window; moving on
+// by 8 shifts the window by 8, so each step loads 8 new taps and 8 line values (four 16-byte shared loads, all multicast
+// and conflict-free: the 8 lines sit 4 banks apart, the 4 channel blocks of a warp 8 banks apart) for 64 FMAs -- the
+// one-line kernel above spends 5 shared loads on 4 FMAs and is bound by shared-memory bandwidth.
+// Taps in shared memory: G[i] = g[n = i - off], off = n_chp + 7 (n_chp = n_ch rounded up to 8), zero outside |n| < n_ch.
+constexpr int FBP_FL = 8;                                     // lines per CTA
+template <typename R>
+__global__ void __launch_bounds__(256) fbp_filter8_kernel(const R *__restrict__ sino, long long n_lines, int n_ch, double gamma0,
+                                                          double dgamma, double sid, const R *__restrict__ taps,
+                                                          R *__restrict__ q, int q_pitch, int n_rows, int row_pitch)
+{
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    const int n_chp = (n_ch + 7) & ~7;
+    const int lstride = n_chp + 4 + ((32 - (n_chp & 31)) & 31);         // = 4 (mod 32): the 8 lines 4 banks apart
+    const int off = n_chp + 7;
+    R *line = (R *)smem_raw;                                             // [8][lstride]
+    R *G = line + FBP_FL * lstride;                                      // [2 n_chp + 8]
+    const long long ln0 = (long long)blockIdx.x * FBP_FL;
+    for (int i = threadIdx.x; i < FBP_FL * n_chp; i += blockDim.x) {
+        const int r = i / n_chp, c = i - r * n_chp;
+        R v = (R)0;
+        if (c < n_ch && ln0 + r < n_lines) v = sino[(ln0 + r) * n_ch + c] * (R)(sid * cos(gamma0 + (double)c * dgamma));
+        line[r * lstride + c] = v;
+    }
+    for (int i = threadIdx.x; i < 2 * n_chp + 8; i += blockDim.x) {
+        const int n = i - off;
+        G[i] = (n > -n_ch && n < n_ch) ? taps[n + n_ch - 1] : (R)0;
+    }
+    __syncthreads();
+    const int r = threadIdx.x & 7;
+    const long long ln = ln0 + r;
+    // row_pitch == 0: line-major q[line][q_pitch]; else row-fastest q[view][plane][row_pitch] (plane = channel + 1)
+    const long long cstride = row_pitch ? row_pitch : 1;
+    R *dst = nullptr;
+    if (ln < n_lines) dst = row_pitch ? q + (ln / n_rows) * (long long)(n_ch + 2) * row_pitch + (ln % n_rows) : q + ln * q_pitch;
+    const R *lr = line + r * lstride;
+    for (int cb = threadIdx.x >> 3; cb < (n_chp >> 3); cb += blockDim.x >> 3) {
+        const int c0 = cb << 3;
+        R acc[8], win[16];
+#pragma unroll
+        for (int k = 0; k < 8; ++k) acc[k] = (R)0;
+        // window for c' in [cp, cp + 8): win[m] = g[c0 - cp - 7 + m], m = 0 .. 14; it enters the loop holding its upper half
+        const R *gp = G + c0 + off - 7;                                  // &G[index of win[0] at cp = 0], a multiple of 8
+#pragma unroll
+        for (int m = 0; m < 8; ++m) win[8 + m] = gp[8 + m];
+        for (int cp = 0; cp < n_chp; cp += 8) {
+            R lv[8];
+#pragma unroll
+            for (int m = 0; m < 8; ++m) { win[m] = gp[m - cp]; lv[m] = lr[cp + m]; }
+#pragma unroll
+            for (int j = 0; j < 8; ++j)
+#pragma unroll
+                for (int k = 0; k < 8; ++k) acc[k] = fma(lv[j], win[k - j + 7], acc[k]);
+#pragma unroll
+            for (int m = 0; m < 8; ++m) win[8 + m] = win[m];
+        }
+        if (dst) {
+#pragma unroll
+            for (int k = 0; k < 8; ++k)
+                if (c0 + k < n_ch) dst[(1 + c0 + k) * cstride] = acc[k] * (R)dgamma;
+        }
+    }
+    if (dst && (threadIdx.x >> 3) == 0) {
+        dst[0] = (R)0;
+        const int end = row_pitch ? n_ch + 2 : q_pitch;
+        for (int c = n_ch + 1; c < end; ++c) dst[c * cstride] = (R)0;
+    }
 }
 
 // Channel coordinate and 1/L^2 of a pixel for one view.  FAST (single precision, fan half-angle below atan(0.85) = 40 deg):
@@ -182,6 +265,177 @@ __global__ void __launch_bounds__(256) fbp_backproject_kernel(const R *__restric
     *out = accumulate ? *out + r : r;
 }
 
+// Multi-row scans: every detector row is its own fan-beam slice with the SAME in-plane geometry, so the channel coordinate,
+// the interpolation weight and 1/L^2 of a (pixel, view) pair are computed once and applied to RB rows.  The filtered data
+// are row-fastest (q[view][plane][row_pitch], plane = channel + 1 with a zero plane on either side), so the RB values of
+// one channel are RB consecutive words: two 16-byte loads per four rows.  Per (pixel, view, row) this costs ~5 instructions
+// instead of ~22.
+template <typename R, int RB> struct FbpVec;
+template <int RB> struct FbpVec<float, RB> {
+    static __device__ __forceinline__ void load(const float *p, float (&v)[RB])
+    {
+#pragma unroll
+        for (int k = 0; k < RB; k += 4) {
+            const float4 t = __ldg((const float4 *)(p + k));
+            v[k] = t.x; v[k + 1] = t.y; v[k + 2] = t.z; v[k + 3] = t.w;
+        }
+    }
+};
+template <int RB> struct FbpVec<double, RB> {
+    static __device__ __forceinline__ void load(const double *p, double (&v)[RB])
+    {
+#pragma unroll
+        for (int k = 0; k < RB; k += 2) {
+            const double2 t = __ldg((const double2 *)(p + k));
+            v[k] = t.x; v[k + 1] = t.y;
+        }
+    }
+};
+
+template <typename R, bool FAST, int RB>
+__global__ void __launch_bounds__(256) fbp_backproject_rows_kernel(const R *__restrict__ q, int row_pitch, const R *__restrict__ cs,
+                                                                   int view_count, int n_rows, int n_ch, R sid, R gamma0,
+                                                                   R inv_dgamma, int n, R px, R scale, int accumulate,
+                                                                   R *__restrict__ image)
+{
+    typedef FbpMath<R, FAST> M;
+    const int ix = blockIdx.x * blockDim.x + threadIdx.x;
+    const int iy = blockIdx.y * blockDim.y + threadIdx.y;
+    const int r0 = blockIdx.z * RB;
+    if (ix >= n || iy >= n) return;
+    const R half = (R)0.5 * (R)(n - 1);
+    const R x = ((R)ix - half) * px, y = ((R)iy - half) * px;
+    const R umax = (R)n_ch, ubias = -gamma0 * inv_dgamma;
+    const long long view_stride = (long long)(n_ch + 2) * row_pitch;
+    const R *base = q + row_pitch + r0;                       // plane 1 = channel 0
+    R acc[RB];
+#pragma unroll
+    for (int k = 0; k < RB; ++k) acc[k] = (R)0;
+    for (int v = 0; v < view_count; ++v) {
+        const R cb = cs[2 * v], sb = cs[2 * v + 1];
+        const R A = sid - fma(y, sb, x * cb);
+        const R negB = fma(x, sb, -(y * cb));
+        const R gam = M::gamma(negB, A);
+        R u = fma(gam, inv_dgamma, ubias);
+        u = fmin(fmax(u, (R)-1), umax);
+        const R fl = fmin(floor(u), umax - (R)1);
+        const R f = u - fl;
+        const R w = M::inv(fma(A, A, negB * negB));
+        const R *p = base + v * view_stride + (long long)(int)fl * row_pitch;
+        R q0[RB], q1[RB];
+        FbpVec<R, RB>::load(p, q0);
+        FbpVec<R, RB>::load(p + row_pitch, q1);
+#pragma unroll
+        for (int k = 0; k < RB; ++k) acc[k] = fma(fma(f, q1[k] - q0[k], q0[k]), w, acc[k]);
+    }
+#pragma unroll
+    for (int k = 0; k < RB; ++k) {
+        if (r0 + k < n_rows) {
+            R *out = image + ((long long)(r0 + k) * n + iy) * n + ix;
+            const R r = acc[k] * scale;
+            *out = accumulate ? *out + r : r;
+        }
+    }
+}
+
+// Many rows (>= 24): lanes run along the detector ROWS.  A warp owns a strip of 16 pixels along x and 32 RPL rows; for
+// each view lanes 0..15 work out channel index, interpolation weight and 1/L^2 of "their" pixel and park them in shared
+// memory; then, pixel by pixel, every lane fetches the two filtered samples of its RPL rows -- one 128 RPL-byte run per
+// channel plane, i.e. fully coalesced -- and accumulates.  The thread-per-pixel kernels above touch 32 different cache
+// lines per load instruction (neighbouring pixels fall on different channels) and are bound by L1 tag throughput.
+template <typename R, int RPL> struct FbpRowVec;
+template <typename R> struct FbpRowVec<R, 1> { static __device__ __forceinline__ void load(const R *p, R (&v)[1]) { v[0] = __ldg(p); } };
+template <> struct FbpRowVec<float, 2> {
+    static __device__ __forceinline__ void load(const float *p, float (&v)[2]) { const float2 t = __ldg((const float2 *)p); v[0] = t.x; v[1] = t.y; }
+};
+template <> struct FbpRowVec<float, 4> {
+    static __device__ __forceinline__ void load(const float *p, float (&v)[4])
+    {
+        const float4 t = __ldg((const float4 *)p);
+        v[0] = t.x; v[1] = t.y; v[2] = t.z; v[3] = t.w;
+    }
+};
+template <> struct FbpRowVec<double, 2> {
+    static __device__ __forceinline__ void load(const double *p, double (&v)[2]) { const double2 t = __ldg((const double2 *)p); v[0] = t.x; v[1] = t.y; }
+};
+template <> struct FbpRowVec<double, 4> {
+    static __device__ __forceinline__ void load(const double *p, double (&v)[4])
+    {
+        const double2 a = __ldg((const double2 *)p), b = __ldg((const double2 *)p + 1);
+        v[0] = a.x; v[1] = a.y; v[2] = b.x; v[3] = b.y;
+    }
+};
+
+constexpr int FBP_WPX = 8;                                    // pixels of a warp's strip
+constexpr int FBP_VPI = 32 / FBP_WPX;                         // views per iteration: every lane computes one (pixel, view) pair
+template <typename R, bool FAST, int RPL>
+__global__ void __launch_bounds__(256) fbp_backproject_warprows_kernel(const R *__restrict__ q, int row_pitch, const R *__restrict__ cs,
+                                                                       int view_count, int n_rows, int n_ch, R sid, R gamma0,
+                                                                       R inv_dgamma, int n, R px, R scale, int accumulate,
+                                                                       R *__restrict__ image)
+{
+    typedef FbpMath<R, FAST> M;
+    struct Geo { long long off; R f, w; };
+    __shared__ Geo geo[8][32];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int ix0 = blockIdx.x * FBP_WPX, iy = blockIdx.y * 8 + warp;
+    const int r0 = blockIdx.z * 32 * RPL + lane * RPL;        // first row of this lane (row_pitch covers it)
+    if (iy >= n) return;                                      // warp-uniform
+    const R half = (R)0.5 * (R)(n - 1);
+    const R x = ((R)min(ix0 + (lane & (FBP_WPX - 1)), n - 1) - half) * px, y = ((R)iy - half) * px;
+    const int vsub = lane / FBP_WPX;
+    const R umax = (R)n_ch, ubias = -gamma0 * inv_dgamma;
+    const long long view_stride = (long long)(n_ch + 2) * row_pitch;
+    const R *base = q + row_pitch + r0;                       // plane 1 = channel 0
+    R acc[FBP_WPX][RPL];
+#pragma unroll
+    for (int j = 0; j < FBP_WPX; ++j)
+#pragma unroll
+        for (int k = 0; k < RPL; ++k) acc[j][k] = (R)0;
+    for (int v0 = 0; v0 < view_count; v0 += FBP_VPI) {
+        {
+            const int v = min(v0 + vsub, view_count - 1);
+            const R cb = cs[2 * v], sb = cs[2 * v + 1];
+            const R A = sid - fma(y, sb, x * cb);
+            const R negB = fma(x, sb, -(y * cb));
+            const R gam = M::gamma(negB, A);
+            R u = fma(gam, inv_dgamma, ubias);
+            u = fmin(fmax(u, (R)-1), umax);
+            const R fl = fmin(floor(u), umax - (R)1);
+            Geo g;
+            g.off = v * view_stride + (long long)((int)fl * row_pitch);
+            g.f = u - fl;
+            g.w = v0 + vsub < view_count ? M::inv(fma(A, A, negB * negB)) : (R)0;     // views past the end weigh nothing
+            geo[warp][lane] = g;
+        }
+        __syncwarp();
+#pragma unroll
+        for (int t = 0; t < 32; ++t) {
+            const Geo g = geo[warp][t];
+            const R *p = base + g.off;
+            R q0[RPL], q1[RPL];
+            FbpRowVec<R, RPL>::load(p, q0);
+            FbpRowVec<R, RPL>::load(p + row_pitch, q1);
+#pragma unroll
+            for (int k = 0; k < RPL; ++k)
+                acc[t % FBP_WPX][k] = fma(fma(g.f, q1[k] - q0[k], q0[k]), g.w, acc[t % FBP_WPX][k]);
+        }
+        __syncwarp();
+    }
+#pragma unroll
+    for (int j = 0; j < FBP_WPX; ++j) {
+        if (ix0 + j >= n) break;
+#pragma unroll
+        for (int k = 0; k < RPL; ++k) {
+            if (r0 + k < n_rows) {
+                R *out = image + ((long long)(r0 + k) * n + iy) * n + ix0 + j;
+                const R r = acc[j][k] * scale;
+                *out = accumulate ? *out + r : r;
+            }
+        }
+    }
+}
+
 template <typename R>
 __global__ void fbp_hu_kernel(const R *__restrict__ image, long long n, R mu_water, R *__restrict__ hu)
 {
@@ -207,13 +461,57 @@ static int fbp_run(const DexctScan &s, const void *sino, int view_begin, int vie
     }
     if (smem > 48 * 1024)
         DEXCT_CUDA_OK(cudaFuncSetAttribute(fbp_filter_kernel<R>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    fbp_filter_kernel<R><<<(unsigned)((long long)view_count * s.n_rows), 256, smem, st>>>(
-        (const R *)sino, s.n_ch, s.gamma0, s.dgamma, s.sid, taps, q, L.q_pitch);
+    // rows >= 8: row-fastest filtered data and the kernel that shares a (pixel, view)'s geometry between RB rows
+    const char *rb_env = getenv("DEXCT_FBP_RB");              // tuning knob: 0 forces the one-row kernel
+    int rb = s.n_rows >= 16 ? 16 : (s.n_rows >= 8 ? 8 : 0);
+    if (rb_env && atoi(rb_env) != 32) rb = atoi(rb_env) == 16 ? 16 : (atoi(rb_env) == 8 ? 8 : 0);   // 32: automatic choice
+    const int row_pitch = rb ? L.row_pitch : 0;
+    const bool warprows = rb && s.n_rows >= FBP_WARPROWS_MIN && !(rb_env && atoi(rb_env) != 32);
+    if (rb && s.n_rows % L.row_pitch)                         // rows of the last block that no line fills
+        DEXCT_CUDA_OK(cudaMemsetAsync(q, 0, sizeof(R) * (size_t)view_count * (s.n_ch + 2) * L.row_pitch, st));
+    {
+        const int n_chp = (s.n_ch + 7) & ~7;
+        const int lstride = n_chp + 4 + ((32 - (n_chp & 31)) & 31);
+        const size_t smem8 = sizeof(R) * ((size_t)FBP_FL * lstride + 2 * n_chp + 8);
+        const char *f_env = getenv("DEXCT_FBP_FILTER");       // tuning knob: 1 forces the one-line kernel
+        const long long n_lines = (long long)view_count * s.n_rows;
+        if (smem8 <= 200 * 1024 && !(f_env && atoi(f_env) == 1)) {
+            if (smem8 > 48 * 1024)
+                DEXCT_CUDA_OK(cudaFuncSetAttribute(fbp_filter8_kernel<R>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem8));
+            fbp_filter8_kernel<R><<<(unsigned)((n_lines + FBP_FL - 1) / FBP_FL), 256, smem8, st>>>(
+                (const R *)sino, n_lines, s.n_ch, s.gamma0, s.dgamma, s.sid, taps, q, L.q_pitch, s.n_rows, row_pitch);
+        } else {
+            fbp_filter_kernel<R><<<(unsigned)n_lines, 256, smem, st>>>(
+                (const R *)sino, s.n_ch, s.gamma0, s.dgamma, s.sid, taps, q, L.q_pitch, s.n_rows, row_pitch);
+        }
+    }
     DEXCT_CUDA_OK(cudaGetLastError());
-    const dim3 block(32, 8), grid((n + 31) / 32, (n + 7) / 8, s.n_rows);
     // fast path: the whole detector (plus the one-channel taper) inside the polynomial's range
     const double gmax = fmax(fabs(s.gamma0), fabs(s.gamma0 + (s.n_ch - 1) * s.dgamma)) + 2.0 * s.dgamma;
     const bool fast = sizeof(R) == 4 && gmax < atan((double)FBP_T0);
+    if (warprows) {
+        const int rpl = fbp_rows_per_lane(s.n_rows);
+        const dim3 grid((n + FBP_WPX - 1) / FBP_WPX, (n + 7) / 8, (s.n_rows + 32 * rpl - 1) / (32 * rpl));
+        auto kern = fbp_backproject_warprows_kernel<R, false, 1>;
+        if (rpl == 4) kern = fast ? fbp_backproject_warprows_kernel<R, sizeof(R) == 4, 4> : fbp_backproject_warprows_kernel<R, false, 4>;
+        else if (rpl == 2) kern = fast ? fbp_backproject_warprows_kernel<R, sizeof(R) == 4, 2> : fbp_backproject_warprows_kernel<R, false, 2>;
+        else if (fast) kern = fbp_backproject_warprows_kernel<R, sizeof(R) == 4, 1>;
+        kern<<<grid, 256, 0, st>>>(q, row_pitch, cs, view_count, s.n_rows, s.n_ch, (R)s.sid, (R)s.gamma0, (R)(1.0 / s.dgamma),
+                                   n, (R)(fov / n), (R)s.dbeta, accumulate, (R *)image);
+        DEXCT_CUDA_OK(cudaGetLastError());
+        return DEXCT_OK;
+    }
+    if (rb) {
+        const dim3 block(32, 8), grid((n + 31) / 32, (n + 7) / 8, (s.n_rows + rb - 1) / rb);
+        auto kern = fbp_backproject_rows_kernel<R, false, 8>;
+        if (rb == 16) kern = fast ? fbp_backproject_rows_kernel<R, sizeof(R) == 4, 16> : fbp_backproject_rows_kernel<R, false, 16>;
+        else if (fast) kern = fbp_backproject_rows_kernel<R, sizeof(R) == 4, 8>;
+        kern<<<grid, block, 0, st>>>(q, row_pitch, cs, view_count, s.n_rows, s.n_ch, (R)s.sid, (R)s.gamma0, (R)(1.0 / s.dgamma),
+                                     n, (R)(fov / n), (R)s.dbeta, accumulate, (R *)image);
+        DEXCT_CUDA_OK(cudaGetLastError());
+        return DEXCT_OK;
+    }
+    const dim3 block(32, 8), grid((n + 31) / 32, (n + 7) / 8, s.n_rows);
     auto kern = fbp_backproject_kernel<R, false>;
     if (fast) kern = fbp_backproject_kernel<R, sizeof(R) == 4>;
     kern<<<grid, block, 0, st>>>(q, L.q_pitch, cs, view_count, s.n_rows, s.n_ch, (R)s.sid, (R)s.gamma0, (R)(1.0 / s.dgamma), n,

@@ -28,7 +28,8 @@ def _case(n_ch=200, n_views=120, n_rows=1, seed=11, beta0=0.0):
     r = np.random.default_rng(seed)
     rows = []
     for k in range(n_rows):
-        s = FO.disc_sinogram(beta, gam, SID, (3.0 - k, -2.0 + 0.5 * k), 8.0 - k, 0.2)
+        m = k % 5                                         # five distinct slices, repeated
+        s = FO.disc_sinogram(beta, gam, SID, (3.0 - m, -2.0 + 0.5 * m), 8.0 - m, 0.2)
         s += FO.disc_sinogram(beta, gam, SID, (-5.0, 4.0), 2.0, 0.35)
         s += 0.01 * r.standard_normal(s.shape)            # noise: exercises the filter at every frequency
         rows.append(s)
@@ -57,6 +58,25 @@ def test_multi_row_odd_sizes_and_start_angle(dtype):
     got = fbp_fan(scan, torch.as_tensor(sino, device='cuda'), 61, 33.0, 0.9, dtype=dtype)
     assert got.shape == (3, 61, 61)
     assert scale_rel_err(got.cpu().numpy(), ref) < TOL[dtype]
+
+
+@pytest.mark.parametrize('dtype', [F32, F64])
+@pytest.mark.parametrize('n_rows', [8, 9, 16, 21, 24, 40, 50, 100])
+def test_many_rows_share_the_in_plane_geometry(dtype, n_rows):
+    """n_rows >= 8 takes the multi-row kernels (row-fastest filtered data): 8 or 16 rows per thread up to 23 rows, from 24
+    rows on lanes along the rows with 1, 2 or 4 rows per lane; 9, 21, 40, 50 and 100 leave a partly filled last row block.  Every slice must still match the oracle's slice-by-slice reconstruction, and view
+    chunks must accumulate."""
+    scan, beta, sino = _case(n_ch=131, n_views=45, n_rows=n_rows, beta0=-0.2)
+    ref = _oracle(scan, beta, sino, 50, 30.0, 0.8)
+    d = torch.as_tensor(sino, device='cuda')
+    got = fbp_fan(scan, d, 50, 30.0, 0.8, dtype=dtype)
+    assert got.shape == (n_rows, 50, 50)
+    err = [scale_rel_err(got[k].cpu().numpy(), ref[k]) for k in range(n_rows)]
+    assert max(err) < TOL[dtype], err
+    img = torch.zeros_like(got)
+    for v0, v1 in ((0, 20), (20, 45)):
+        fbp_fan(scan, d[v0:v1], 50, 30.0, 0.8, view_begin=v0, dtype=dtype, image=img, accumulate=True)
+    assert scale_rel_err(img.cpu().numpy(), got.cpu().numpy()) < (1e-6 if dtype == F32 else 1e-13)
 
 
 def test_view_chunks_accumulate_to_the_whole_scan():
