@@ -45,10 +45,12 @@ WORKLOAD = ('C2: 512x512x1 phantom (K=8 materials), 900 ch x 1000 views per GPU,
             'GN 10 iters water/bone, air mask 0.95')
 
 
-# N > 1: the finished count/log shard goes to the peers through a store kernel on 16 CTAs beside the decomposition, whose
-# resident wave owns the rest of the SMs.  Measured at N = 8 (profiles/r01h_scaling.txt): 16 CTAs 0.855 ms per step,
-# 48 CTAs 0.876, 148 CTAs 0.920, copy engines (DEXCT_PUSH=dma) 0.905, NCCL all-gathers 1.195.
-PUSH_DMA = os.environ.get('DEXCT_PUSH', 'sm') == 'dma'
+# N > 1: how the finished count/log shard reaches the peers' copies.  'fused' (default): the decomposition kernel's own
+# threads copy it, a slice per Newton iteration (dexct_gn_decompose_fused_push) -- spread over all SMs and over the kernel's
+# run time.  'sm': a separate store kernel on DEXCT_PUSH_CTAS CTAs on a side stream; 'dma': seven copy-engine transfers.
+# Measured at N = 8 (profiles/r01h_scaling.txt): sm/16 CTAs 0.855 ms per step, 48 CTAs 0.876, 148 CTAs 0.920, dma 0.905,
+# NCCL all-gathers 1.195.
+PUSH_MODE = os.environ.get('DEXCT_PUSH', 'fused')
 PUSH_CTAS = int(os.environ.get('DEXCT_PUSH_CTAS', '16'))
 
 
@@ -290,6 +292,7 @@ def run_b200(args):
         g_basis = bbuf.view(td, (ws, nv, 1, N_CH, 2))
         counts, logs, basis = g_sino[rank, 0:2], g_sino[rank, 2:4], g_basis[rank]
         mirrors = bbuf.table(rank * slot_b, exclude_self=True)
+        push_table = sbuf.table(rank * slot_s, exclude_self=True)
         side = torch.cuda.Stream(device=dev)
     else:
         counts = torch.empty((2, nv, 1, N_CH), dtype=td, device=dev)
@@ -310,15 +313,22 @@ def run_b200(args):
         if timers is not None:
             timers[1].record()
         if pg is not None:
-            main = torch.cuda.current_stream()
-            side.wait_stream(main)
-            with torch.cuda.stream(side):
-                pg.push(g_sino[rank], sbuf, rank * slot_s, dma=PUSH_DMA, max_ctas=PUSH_CTAS)
-            gn_decompose(counts.reshape(2, -1), i0, mus, GN_ITERS, mask_thresh=MASK_THRESH, dtype=code, out=basis.view(-1, 2),
-                         reduce_max_over_ranks=True, peers=pg, mirrors=mirrors)
-            if timers is not None:
-                timers[2].record()
-            main.wait_stream(side)
+            if PUSH_MODE == 'fused':
+                # one kernel: Newton iterations + the copy of the count/log shard into the peers, a slice per iteration
+                gn_decompose(counts.reshape(2, -1), i0, mus, GN_ITERS, mask_thresh=MASK_THRESH, dtype=code, out=basis.view(-1, 2),
+                             reduce_max_over_ranks=True, peers=pg, mirrors=mirrors, push=(g_sino[rank], push_table))
+                if timers is not None:
+                    timers[2].record()
+            else:
+                main = torch.cuda.current_stream()
+                side.wait_stream(main)
+                with torch.cuda.stream(side):
+                    pg.push(g_sino[rank], sbuf, rank * slot_s, dma=PUSH_MODE == 'dma', max_ctas=PUSH_CTAS)
+                gn_decompose(counts.reshape(2, -1), i0, mus, GN_ITERS, mask_thresh=MASK_THRESH, dtype=code, out=basis.view(-1, 2),
+                             reduce_max_over_ranks=True, peers=pg, mirrors=mirrors)
+                if timers is not None:
+                    timers[2].record()
+                main.wait_stream(side)
             pg.barrier()                                    # every rank's stores have landed in every copy
             return
         pending = []
@@ -455,7 +465,7 @@ def run_b200(args):
                             'frac': gn_flops / (t_gn * 1e-3) / 1e12 / fma_peak, 'kernel': 'gn_kernel',
                             'flop_per_pixel': 28.0 * nE * GN_ITERS},
             # per step: siddon_skip, gn_max, gn_table, gn_kernel, gn_fixup (+ peer_push, peer_max, peer_barrier at N > 1)
-            'gpu_launches': (8 if pg is not None else 5) * args.steps, 'clocks': clocks,
+            'gpu_launches': ((7 if PUSH_MODE == 'fused' else 8) if pg is not None else 5) * args.steps, 'clocks': clocks,
         }
         if e2e:
             line['e2e'] = e2e

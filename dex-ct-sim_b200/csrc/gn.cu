@@ -133,11 +133,24 @@ __global__ void gn_table_kernel(const float *__restrict__ i0, const float *__res
 // Further copies of the result in peer memory (view-sharded scans, peer.cu): the epilogue stores every pixel to each of
 // them as well, so the basis sinograms are assembled on all ranks by the time the kernel ends -- no gather afterwards.
 struct GnMirrors { void *p[DEXCT_MAX_PEERS]; int n; };
+// A finished buffer (the count/log shard the projection just wrote) that rides along: the threads of the decomposition
+// kernel copy it into the peers' copies a slice per Newton iteration, so the transfer is spread evenly over all SMs and
+// over the kernel's run time instead of competing for a few SMs as a separate copy kernel would (peer.cu).
+struct GnRider { const uint4 *src; long long n16; void *dst[DEXCT_MAX_PEERS]; int n; };
+
+__device__ __forceinline__ void gn_rider_slice(const GnRider &rd, int k, int nk)
+{
+    const long long nthreads = (long long)gridDim.x * blockDim.x;
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x + nthreads * k; i < rd.n16; i += nthreads * nk) {
+        const uint4 v = rd.src[i];
+        for (int d = 0; d < rd.n; ++d) ((uint4 *)rd.dst[d])[i] = v;
+    }
+}
 
 template <typename R, int PX, bool CTAB>
 __global__ void __launch_bounds__(256, (PX == 4 && CTAB) ? 3 : 1) gn_kernel(const R *__restrict__ g, const R *__restrict__ i0, const R *__restrict__ mus,
                                                  int nE, long long P, int n_iters, R mask_thresh, void *scratch,
-                                                 R *__restrict__ a_out, const GnMirrors mir)
+                                                 R *__restrict__ a_out, const GnMirrors mir, const GnRider rider)
 {
     typedef GnMath<R> M;
     constexpr bool PACKED = sizeof(R) == 4;
@@ -169,8 +182,10 @@ __global__ void __launch_bounds__(256, (PX == 4 && CTAB) ? 3 : 1) gn_kernel(cons
     // compiler may not use the uniform datapath, and the table reads fall back from LDCU to per-thread LDC (2x slower).
     const long long stride = blockDim.x;
     const long long n_groups = (P + stride * PX - 1) / (stride * PX);
+    if (rider.n && n_iters == 0) gn_rider_slice(rider, 0, 1);
     for (long long grp = blockIdx.x; grp < n_groups; grp += gridDim.x) {
         const long long base = grp * stride * PX + threadIdx.x;
+        const bool ride = rider.n && grp == blockIdx.x;       // CTA-uniform: the slices go out during the first group
         R a1[PX], a2[PX], g1[PX], g2[PX];
         bool sane[PX];
 #pragma unroll
@@ -182,6 +197,7 @@ __global__ void __launch_bounds__(256, (PX == 4 && CTAB) ? 3 : 1) gn_kernel(cons
             g2[k] = p < P ? g[P + p] : (R)1;
         }
         for (int it = 0; it < n_iters; ++it) {
+            if (ride) gn_rider_slice(rider, it, n_iters);
             R acc[PX][12];
             if constexpr (PACKED) {
                 // FFMA2 (sm_100a): accumulator pair q = (measurement 1, measurement 2) of moment q; att is broadcast
@@ -431,7 +447,7 @@ static int launch_max(const void *g, long long P, void *scratch, cudaStream_t st
 
 template <typename R, int PX>
 static int launch_gn(const void *g, const void *i0, const void *mus, int nE, long long P, int n_iters, double mask_thresh,
-                     void *a_out, void *scratch, bool have_max, cudaStream_t st, const GnMirrors &mir)
+                     void *a_out, void *scratch, bool have_max, cudaStream_t st, const GnMirrors &mir, const GnRider &rider)
 {
     const char *bs = getenv("DEXCT_GN_BLOCK");         // tuning knob (threads per CTA: 128 or 256)
     const int block = (bs && atoi(bs) == 128) ? 128 : 256;
@@ -441,7 +457,7 @@ static int launch_gn(const void *g, const void *i0, const void *mus, int nE, lon
         set_error("GN table needs %zu bytes of shared memory (limit 200 KiB): nE=%d", smem, nE);
         return DEXCT_ECAPACITY;
     }
-    void (*kern)(const R *, const R *, const R *, int, long long, int, R, void *, R *, const GnMirrors) = gn_kernel<R, PX, false>;
+    void (*kern)(const R *, const R *, const R *, int, long long, int, R, void *, R *, const GnMirrors, const GnRider) = gn_kernel<R, PX, false>;
     if (ctab) kern = gn_kernel<R, PX, sizeof(R) == 4>;
     if (smem > 48 * 1024) DEXCT_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     int per_sm = 0;
@@ -478,12 +494,12 @@ static int launch_gn(const void *g, const void *i0, const void *mus, int nE, lon
         DEXCT_CUDA_OK(cudaMemcpyToSymbolAsync(gn_cexp, (const float *)slot.staging() + (size_t)(nE + 2) * GN_CROW,
                                               sizeof(float) * (size_t)(nE + 2) * 2, 0, cudaMemcpyDeviceToDevice, st));
         kern<<<(unsigned)grid, block, smem, st>>>((const R *)g, (const R *)i0, (const R *)mus, nE, P, n_iters, (R)mask_thresh,
-                                                 scratch, (R *)a_out, mir);
+                                                 scratch, (R *)a_out, mir, rider);
         DEXCT_CUDA_OK(cudaGetLastError());
         return fixup();
     }
     kern<<<(unsigned)grid, block, smem, st>>>((const R *)g, (const R *)i0, (const R *)mus, nE, P, n_iters, (R)mask_thresh,
-                                             scratch, (R *)a_out, mir);
+                                             scratch, (R *)a_out, mir, rider);
     DEXCT_CUDA_OK(cudaGetLastError());
     return sizeof(R) == 4 ? fixup() : DEXCT_OK;
 }
@@ -508,8 +524,8 @@ extern "C" int dexct_gn_air_max(const void *g1, int64_t P, void *scratch, int32_
 }
 
 static int gn_decompose_impl(const void *g, const void *i0, const void *mus, int32_t nE, int64_t P, int32_t n_iters,
-                             double mask_thresh, void *a_out, const GnMirrors &mir, void *scratch, int32_t scratch_has_max,
-                             int32_t dtype, void *stream)
+                             double mask_thresh, void *a_out, const GnMirrors &mir, const GnRider &rider, void *scratch,
+                             int32_t scratch_has_max, int32_t dtype, void *stream)
 {
     if (int e = check_device()) return e;
     DEXCT_REQUIRE(nE >= 1 && P >= 0 && n_iters >= 0, "need nE >= 1, P >= 0, n_iters >= 0");
@@ -524,12 +540,12 @@ static int gn_decompose_impl(const void *g, const void *i0, const void *mus, int
     if (dtype == DEXCT_F32) {
         const char *px = getenv("DEXCT_GN_PX");          // tuning knob (pixels per thread)
         const int npx = px ? atoi(px) : 4;            // 4: the table row of a bin is fetched once for four pixels
-        if (npx == 1) return launch_gn<float, 1>(g, i0, mus, nE, P, n_iters, mask_thresh, a_out, scratch, have, st, mir);
-        if (npx == 3) return launch_gn<float, 3>(g, i0, mus, nE, P, n_iters, mask_thresh, a_out, scratch, have, st, mir);
-        if (npx == 2) return launch_gn<float, 2>(g, i0, mus, nE, P, n_iters, mask_thresh, a_out, scratch, have, st, mir);
-        return launch_gn<float, 4>(g, i0, mus, nE, P, n_iters, mask_thresh, a_out, scratch, have, st, mir);
+        if (npx == 1) return launch_gn<float, 1>(g, i0, mus, nE, P, n_iters, mask_thresh, a_out, scratch, have, st, mir, rider);
+        if (npx == 3) return launch_gn<float, 3>(g, i0, mus, nE, P, n_iters, mask_thresh, a_out, scratch, have, st, mir, rider);
+        if (npx == 2) return launch_gn<float, 2>(g, i0, mus, nE, P, n_iters, mask_thresh, a_out, scratch, have, st, mir, rider);
+        return launch_gn<float, 4>(g, i0, mus, nE, P, n_iters, mask_thresh, a_out, scratch, have, st, mir, rider);
     }
-    return launch_gn<double, 1>(g, i0, mus, nE, P, n_iters, mask_thresh, a_out, scratch, have, st, mir);
+    return launch_gn<double, 1>(g, i0, mus, nE, P, n_iters, mask_thresh, a_out, scratch, have, st, mir, rider);
 }
 
 extern "C" int dexct_gn_decompose(const void *g, const void *i0, const void *mus, int32_t nE, int64_t P, int32_t n_iters,
@@ -537,7 +553,20 @@ extern "C" int dexct_gn_decompose(const void *g, const void *i0, const void *mus
                                   int32_t dtype, void *stream)
 {
     GnMirrors mir{};
-    return gn_decompose_impl(g, i0, mus, nE, P, n_iters, mask_thresh, a_out, mir, scratch, scratch_has_max, dtype, stream);
+    GnRider rider{};
+    return gn_decompose_impl(g, i0, mus, nE, P, n_iters, mask_thresh, a_out, mir, rider, scratch, scratch_has_max, dtype, stream);
+}
+
+static int fill_mirrors(GnMirrors &mir, void *const *mirrors_host, int32_t n_mirrors)
+{
+    DEXCT_REQUIRE(n_mirrors >= 0 && n_mirrors <= DEXCT_MAX_PEERS && (n_mirrors == 0 || mirrors_host),
+                  "0 <= n_mirrors <= DEXCT_MAX_PEERS and a pointer table required");
+    mir.n = n_mirrors;
+    for (int i = 0; i < n_mirrors; ++i) {
+        DEXCT_REQUIRE(mirrors_host[i] && ((uintptr_t)mirrors_host[i] & 15) == 0, "mirror %d is null or not 16-byte aligned", i);
+        mir.p[i] = mirrors_host[i];
+    }
+    return DEXCT_OK;
 }
 
 extern "C" int dexct_gn_decompose_mirrored(const void *g, const void *i0, const void *mus, int32_t nE, int64_t P,
@@ -545,13 +574,33 @@ extern "C" int dexct_gn_decompose_mirrored(const void *g, const void *i0, const 
                                            int32_t n_mirrors, void *scratch, int32_t scratch_has_max, int32_t dtype,
                                            void *stream)
 {
-    DEXCT_REQUIRE(n_mirrors >= 0 && n_mirrors <= DEXCT_MAX_PEERS && (n_mirrors == 0 || mirrors_host),
-                  "0 <= n_mirrors <= DEXCT_MAX_PEERS and a pointer table required");
     GnMirrors mir{};
-    mir.n = n_mirrors;
-    for (int i = 0; i < n_mirrors; ++i) {
-        DEXCT_REQUIRE(mirrors_host[i] && ((uintptr_t)mirrors_host[i] & 15) == 0, "mirror %d is null or not 16-byte aligned", i);
-        mir.p[i] = mirrors_host[i];
+    GnRider rider{};
+    if (int e = fill_mirrors(mir, mirrors_host, n_mirrors)) return e;
+    return gn_decompose_impl(g, i0, mus, nE, P, n_iters, mask_thresh, a_out, mir, rider, scratch, scratch_has_max, dtype, stream);
+}
+
+extern "C" int dexct_gn_decompose_fused_push(const void *g, const void *i0, const void *mus, int32_t nE, int64_t P,
+                                             int32_t n_iters, double mask_thresh, void *a_out, void *const *mirrors_host,
+                                             int32_t n_mirrors, const void *push_src, size_t push_bytes,
+                                             void *const *push_dst_host, int32_t n_push_dst, void *scratch,
+                                             int32_t scratch_has_max, int32_t dtype, void *stream)
+{
+    GnMirrors mir{};
+    GnRider rider{};
+    if (int e = fill_mirrors(mir, mirrors_host, n_mirrors)) return e;
+    DEXCT_REQUIRE(n_push_dst >= 0 && n_push_dst <= DEXCT_MAX_PEERS, "0 <= n_push_dst <= DEXCT_MAX_PEERS");
+    if (n_push_dst > 0 && push_bytes > 0) {
+        DEXCT_REQUIRE(P > 0, "the push rides on the decomposition kernel: P must be positive");
+        DEXCT_REQUIRE(push_src && push_dst_host && push_bytes % 16 == 0 && ((uintptr_t)push_src & 15) == 0,
+                      "push_src must be non-null and 16-byte aligned, push_bytes a multiple of 16");
+        rider.src = (const uint4 *)push_src;
+        rider.n16 = (long long)(push_bytes / 16);
+        rider.n = n_push_dst;
+        for (int i = 0; i < n_push_dst; ++i) {
+            DEXCT_REQUIRE(push_dst_host[i] && ((uintptr_t)push_dst_host[i] & 15) == 0, "push destination %d is null or not 16-byte aligned", i);
+            rider.dst[i] = push_dst_host[i];
+        }
     }
-    return gn_decompose_impl(g, i0, mus, nE, P, n_iters, mask_thresh, a_out, mir, scratch, scratch_has_max, dtype, stream);
+    return gn_decompose_impl(g, i0, mus, nE, P, n_iters, mask_thresh, a_out, mir, rider, scratch, scratch_has_max, dtype, stream);
 }

@@ -5,6 +5,7 @@
 // (profiles/r01h_*); a store needs no rendezvous.  Synchronisation: epoch flags in peer memory, written with
 // system-scope release stores after a __threadfence_system and polled with system-scope acquire loads.
 #include "common.cuh"
+#include <stdlib.h>
 #include <string.h>
 
 namespace dexct {
@@ -204,10 +205,14 @@ extern "C" int dexct_peer_push(const void *src, size_t bytes, void *const *dst_p
     DEXCT_REQUIRE(src && bytes % 16 == 0 && ((uintptr_t)src & 15) == 0, "src must be non-null, 16-byte aligned, bytes a multiple of 16");
     for (int i = 0; i < n_dst; ++i) DEXCT_REQUIRE(((uintptr_t)pp.p[i] & 15) == 0, "destination %d is not 16-byte aligned", i);
     const long long n16 = (long long)(bytes / 16);
-    long long grid = (n16 + 511) / 512;
+    // Small CTAs on purpose: 128 threads x <= 32 registers fit into the register file beside three resident CTAs of the
+    // decomposition kernel (3 x 256 x 80 registers), so the copy never keeps one of them from starting.
+    const char *th = getenv("DEXCT_PUSH_THREADS");
+    const int block = th && atoi(th) >= 32 && atoi(th) <= 512 ? atoi(th) / 32 * 32 : 128;
+    long long grid = (n16 + block - 1) / block;
     const long long cap = max_ctas > 0 ? max_ctas : sm_count();
     if (grid > cap) grid = cap;
-    peer_push_kernel<<<(unsigned)grid, 512, 0, (cudaStream_t)stream>>>((const uint4 *)src, n16, pp, n_dst, skip);
+    peer_push_kernel<<<(unsigned)grid, block, 0, (cudaStream_t)stream>>>((const uint4 *)src, n16, pp, n_dst, skip);
     DEXCT_CUDA_OK(cudaGetLastError());
     return DEXCT_OK;
 }

@@ -67,6 +67,8 @@ SIGNATURES = {
     'dexct_peer_push_dma': (C.c_int, [_P, C.c_size_t, _P, C.c_int32, C.c_int32, _P]),
     'dexct_gn_decompose_mirrored': (C.c_int, [_P, _P, _P, C.c_int32, C.c_int64, C.c_int32, C.c_double, _P, _P, C.c_int32,
                                               _P, C.c_int32, C.c_int32, _P]),
+    'dexct_gn_decompose_fused_push': (C.c_int, [_P, _P, _P, C.c_int32, C.c_int64, C.c_int32, C.c_double, _P, _P, C.c_int32,
+                                                _P, C.c_size_t, _P, C.c_int32, _P, C.c_int32, C.c_int32, _P]),
     'dexct_vmi': (C.c_int, [_P, _P, C.c_int64, C.c_double, C.c_double, C.c_double, C.c_int32, _P, C.c_int32, _P]),
 }
 

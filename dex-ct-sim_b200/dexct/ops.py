@@ -173,14 +173,15 @@ def poly_detect(L, mu, W, dtype=F32, want_log=True):
 
 
 def gn_decompose(g, i0, mus, n_iters, mask_thresh=0.0, dtype=F32, out=None, reduce_max_over_ranks=False, peers=None,
-                 mirrors=None):
+                 mirrors=None, push=None):
     """g [2, ...] counts (device tensor or array), i0 [2, nE], mus [2, nE] -> a [..., 2] device tensor.
 
     ``reduce_max_over_ranks``: the pixels are one shard of a larger sinogram; the air threshold then uses the maximum of the
     first measurement over ALL ranks (one 8-byte integer MAX all-reduce), as the unsharded reference does
     (matdecomp.py:196) -- through ``peers`` (a dexct.peer.PeerGroup: flags in peer memory) when given, else NCCL.
     ``mirrors``: ctypes table of further device addresses (peer copies of the basis sinogram, SymBuffer.table) that the
-    kernel's epilogue stores every pixel to as well."""
+    kernel's epilogue stores every pixel to as well.  ``push``: ``(src_tensor, table)`` -- a finished contiguous buffer
+    (the count/log shard) that the same kernel copies to the addresses in ``table`` while it computes."""
     N.require_device()
     code = dtype_code(dtype)
     td = _TORCH_DTYPE[code]
@@ -206,7 +207,16 @@ def gn_decompose(g, i0, mus, n_iters, mask_thresh=0.0, dtype=F32, out=None, redu
                 key = scratch[:8].view(torch.int64) if code == F64 else scratch[:4].view(torch.int32)
                 dist.all_reduce(key, op=dist.ReduceOp.MAX)
             have_max = 1
-        if mirrors is not None and len(mirrors):
+        if push is not None and len(push[1]):
+            src, tab = push
+            if not src.is_contiguous():
+                raise ValueError('push source must be contiguous')
+            nm = 0 if mirrors is None else len(mirrors)
+            N.check(N.lib().dexct_gn_decompose_fused_push(N.ptr(g), N.ptr(i0), N.ptr(mus), nE, P, int(n_iters), float(mask_thresh),
+                                                          N.ptr(out), mirrors if nm else None, nm, N.ptr(src),
+                                                          src.numel() * src.element_size(), tab, len(tab), N.ptr(scratch),
+                                                          have_max, code, N.stream_ptr()))
+        elif mirrors is not None and len(mirrors):
             N.check(N.lib().dexct_gn_decompose_mirrored(N.ptr(g), N.ptr(i0), N.ptr(mus), nE, P, int(n_iters), float(mask_thresh),
                                                         N.ptr(out), mirrors, len(mirrors), N.ptr(scratch), have_max, code,
                                                         N.stream_ptr()))

@@ -215,6 +215,13 @@ int dexct_peer_push_dma(const void *src, size_t bytes, void *const *dst_ptrs_hos
 int dexct_gn_decompose_mirrored(const void *g_2xP, const void *i0_2xE, const void *mus_2xE, int32_t nE, int64_t P,
                                 int32_t n_iters, double mask_thresh, void *a_out_Px2, void *const *mirrors_host,
                                 int32_t n_mirrors, void *scratch, int32_t scratch_has_max, int32_t dtype, void *stream);
+/* ... and that also carries a finished buffer to the peers: the kernel's threads copy push_src[0, push_bytes) into each
+ * push_dst_host[d] (the other ranks' copies of the count/log shard, 16-byte aligned) one slice per Newton iteration, so
+ * the transfer is spread over all SMs and over the kernel's run time -- one kernel computes and communicates.       */
+int dexct_gn_decompose_fused_push(const void *g_2xP, const void *i0_2xE, const void *mus_2xE, int32_t nE, int64_t P,
+                                  int32_t n_iters, double mask_thresh, void *a_out_Px2, void *const *mirrors_host,
+                                  int32_t n_mirrors, const void *push_src, size_t push_bytes, void *const *push_dst_host,
+                                  int32_t n_push_dst, void *scratch, int32_t scratch_has_max, int32_t dtype, void *stream);
 
 #ifdef __cplusplus
 }

@@ -60,11 +60,18 @@ def main():
         v0, nv = ddist.shard_range(8 * ws, rank, ws)
         local = torch.as_tensor(g[:, v0:v0 + nv], dtype=td, device=dev).contiguous()
         off = v0 * 96 * 2 * esz
-        gn_decompose(local, i0, mus, 12, mask_thresh=0.9, dtype=code, out=basis[v0:v0 + nv], reduce_max_over_ranks=True,
-                     peers=pg, mirrors=bbuf.table(off, exclude_self=True))
+        # ... and the same kernel carries this rank's count shard into the peers' copies of the count sinogram
+        cbuf = pg.alloc(2 * 8 * ws * 96 * esz)
+        csino = cbuf.view(td, (ws, 2, 8, 96))
+        csino[rank].copy_(local)
+        coff = rank * 2 * 8 * 96 * esz
+        gn_decompose(csino[rank], i0, mus, 12, mask_thresh=0.9, dtype=code, out=basis[v0:v0 + nv], reduce_max_over_ranks=True,
+                     peers=pg, mirrors=bbuf.table(off, exclude_self=True), push=(csino[rank], cbuf.table(coff, exclude_self=True)))
         pg.barrier()
         torch.cuda.synchronize()
         assert torch.equal(basis, whole), f'rank {rank} dtype {code}: max diff {(basis - whole).abs().max()}'
+        want = torch.as_tensor(g, dtype=td, device=dev).view(2, ws, 8, 96).permute(1, 0, 2, 3)
+        assert torch.equal(csino, want), f'rank {rank} dtype {code}: pushed counts differ'
         assert bool((basis[0, :7] == 0).all(dim=-1).any())    # masked on every rank, whoever owns the maximum
     assert pg.status() == 0
     dist.barrier()

@@ -40,6 +40,14 @@ def test_single_rank_group_and_mirrored_decomposition():
         tab = (C.c_void_p * 2)(m1.data_ptr(), m2.data_ptr())
         again = gn_decompose(gd, i0, mus, 15, mask_thresh=0.95, dtype=code, mirrors=tab)
         assert torch.equal(again, plain) and torch.equal(m1, plain) and torch.equal(m2, plain)
+        # the same kernel can carry a finished buffer along (here: its own input) to further addresses
+        for iters in (15, 1, 0):
+            d1, d2, m3 = torch.zeros_like(gd), torch.zeros_like(gd), torch.zeros_like(plain)
+            out = gn_decompose(gd, i0, mus, iters, mask_thresh=0.95, dtype=code, mirrors=(C.c_void_p * 1)(m3.data_ptr()),
+                               push=(gd, (C.c_void_p * 2)(d1.data_ptr(), d2.data_ptr())))
+            assert torch.equal(d1, gd) and torch.equal(d2, gd) and torch.equal(m3, out)
+            if iters == 15:
+                assert torch.equal(out, plain)
     assert pg.status() == 0
     pg.close()
 
