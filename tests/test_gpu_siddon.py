@@ -262,3 +262,55 @@ def test_steep_cone_on_anatomy_like_volume(dtype, h_iso, voxz):
     assert scale_rel_err(L.cpu().numpy(), L_ref) < TOL[dtype]
     c_ref, l_ref, _ = sc.project_poly(mu, W)
     assert scale_rel_err(counts.cpu().numpy(), c_ref) < TOL[dtype]
+
+
+@pytest.mark.parametrize('name', ['C4', 'C5'])
+def test_c4_c5_full_size_properties(name):
+    """Configs C4 (512^3, 64 rows x 900 ch x 1200 views) and C5 (1024^3, 128 x 1800 x 2400) at FULL volume and detector size,
+    on view ranges spread over the rotation (the phantom is rasterised on the device; the CPU oracle traces one detector
+    view of it): sum_m L_m is the chord of the ray with the volume's bounding box; the lengths of a view match Siddon 1985;
+    doubling W doubles the counts exactly; a view range projected on its own equals the same views inside a larger range
+    (what view-sharded ranks rely on)."""
+    from xtomosim.forward_project import spectral_weights
+    ct, ph, lo, hi = S.make_config(name, device='cuda')
+    assert tuple(ph.M.shape) == (S.CONFIGS[name]['nz'], S.CONFIGS[name]['n'], S.CONFIGS[name]['n'])
+    scan = make_scan(ct.N_proj, ct.N_channels, ct.gamma_fan, ct.SID, ct.SDD, n_rows=ct.N_rows, h_iso=ct.h_iso,
+                     rotation=ct.rotation)
+    pj = Projector(scan, ph.M, (ph.dx, ph.dy, ph.dz))
+    mu = ph.mu_table(lo.E)
+    W = np.stack([spectral_weights(ct, lo), spectral_weights(ct, hi)])
+    tabs = pj.tables_host()
+    half = np.array([ph.Nx * ph.dx, ph.Ny * ph.dy, ph.Nz * ph.dz]) / 2
+    nv = 3
+    for v0 in (0, ct.N_proj // 8 + 1, ct.N_proj // 2 + 5, ct.N_proj - nv):
+        counts, logs, L = pj.project(mu, W, view_begin=v0, view_count=nv, want_L=True)
+        # chords with the box, from the device's own angle tables
+        cb, sb = tabs['cos_beta'][v0:v0 + nv, None, None], tabs['sin_beta'][v0:v0 + nv, None, None]
+        cg, sg = tabs['cos_gamma'][None, None, :], tabs['sin_gamma'][None, None, :]
+        z = tabs['zdet'][None, :, None]
+        src = np.stack(np.broadcast_arrays(ct.SID * cb, ct.SID * sb, 0 * z + 0 * cg))
+        d = np.stack(np.broadcast_arrays(-ct.SDD * (cb * cg - sb * sg), -ct.SDD * (sb * cg + cb * sg), z + 0 * cb + 0 * cg))
+        with np.errstate(divide='ignore', invalid='ignore'):
+            t1 = (-half[:, None, None, None] - src) / d
+            t2 = (half[:, None, None, None] - src) / d
+        t_lo = np.nanmax(np.minimum(t1, t2), axis=0).clip(0, 1)
+        t_hi = np.nanmin(np.maximum(t1, t2), axis=0).clip(0, 1)
+        chord = np.maximum(t_hi - t_lo, 0) * np.sqrt((d ** 2).sum(0))
+        Ls = L.sum(-1).cpu().numpy()
+        assert np.max(np.abs(Ls - chord)) < 3e-4, (name, v0, np.max(np.abs(Ls - chord)))
+        c2, _, _ = pj.project(mu, 2.0 * W, view_begin=v0, view_count=nv, want_log=False)
+        assert torch.equal(c2, 2.0 * counts)
+        lo_v = max(0, v0 - 2)
+        c_big, l_big, _ = pj.project(mu, W, view_begin=lo_v, view_count=min(nv + 4, ct.N_proj - lo_v))
+        assert torch.equal(c_big[:, v0 - lo_v:v0 - lo_v + nv], counts) and torch.equal(l_big[:, v0 - lo_v:v0 - lo_v + nv], logs)
+    # one view against Siddon 1985 on the host copy of the volume
+    v = ct.N_proj // 8 + 2
+    sub = {k: (a[v:v + 1] if k.endswith('beta') else a) for k, a in tabs.items()}
+    sc = oracle.Scan(ph.M.cpu().numpy(), (ph.dx, ph.dy, ph.dz), ct.SID, ct.SDD, sub)
+    L_ref, seg = sc.classic_lengths(S.K)
+    counts, _, L = pj.project(mu, W, view_begin=v, view_count=1, want_L=True)
+    assert scale_rel_err(L.cpu().numpy(), L_ref) < TOL[F32]
+    c_ref, _ = oracle.poly_detect(L_ref, mu, W, want_log=False)
+    assert scale_rel_err(counts.reshape(2, -1).cpu().numpy(), c_ref) < TOL[F32]
+    per_ray = seg / (ct.N_rows * ct.N_channels)
+    assert (500 < per_ray < 800) if name == 'C4' else (1000 < per_ray < 1600)
