@@ -36,10 +36,27 @@ def make_scan(n_views, n_ch, fan_angle_total, SID, SDD, n_rows=1, h_iso=1.0, rot
                      z0=-0.5 * (n_rows - 1) * dzdet, dzdet=dzdet)
 
 
+_small_tables = {}     # (content, shape, dtype, device) -> device tensor: attenuation / spectrum tables of a few KB
+
+
 def _as_device(a, dtype, device):
+    """Device tensor of ``dtype`` for a tensor or host array.  Small host tables (<= 64 KiB: mu, W, i0 -- read-only inputs
+    of the kernels) are uploaded once per content: a pageable upload is a synchronous copy, and an end-to-end step makes
+    five of them."""
     if isinstance(a, torch.Tensor):
         return a.to(device=device, dtype=dtype).contiguous()
-    return torch.as_tensor(np.ascontiguousarray(a), device=device).to(dtype).contiguous()
+    a = np.ascontiguousarray(a)
+    if a.nbytes > 65536:
+        return torch.as_tensor(a, device=device).to(dtype).contiguous()
+    import hashlib
+    key = (hashlib.blake2b(a.tobytes(), digest_size=16).digest(), a.shape, a.dtype.str, dtype, str(device))
+    t = _small_tables.get(key)
+    if t is None:
+        if len(_small_tables) >= 64:
+            _small_tables.clear()
+        t = torch.as_tensor(np.array(a), device=device).to(dtype).contiguous()
+        _small_tables[key] = t
+    return t
 
 
 class Projector:

@@ -11,6 +11,7 @@ import numpy as np
 import torch
 
 import xcompy as xc
+import xtomosim.xcompy as _xc_impl
 from dexct import config, dist
 from dexct.ops import dtype_code, gn_decompose
 
@@ -23,14 +24,28 @@ matcomp2 = 'H(3.4)C(15.5)N(4.2)O(43.5)Na(0.1)Mg(0.2)P(10.3)S(0.3)Ca(22.5)'
 density2 = 1.92  # [g/cm3]
 
 
+_tables_memo = {}      # content key -> (ee, i0, mus); a handful of entries (one per spectrum pair of a run)
+
+
+def _content_key(*arrays):
+    import zlib
+    return tuple((a.shape, zlib.crc32(np.ascontiguousarray(a, dtype=np.float64).tobytes())) for a in map(np.asarray, arrays))
+
+
 def spectral_tables(ct, spec1, spec2):
     """Host-side model tables of the decomposition (matdecomp.py:138-160).
 
     Union energy grid of the two spectra; first bin width runs from 0; detector efficiency interpolated onto the grid
     (times E for an energy-integrating detector); spectra interpolated with numpy's end-value clamping; basis rows are
     MASS attenuation (the reference leaves the density multiply commented out, so the outputs are g/cm^2).
-    Returns ee [nE], i0 [2, nE], mus [2, nE].
+    Returns ee [nE], i0 [2, nE], mus [2, nE] (read-only: memoised on the CONTENT of the inputs -- a few hundred numbers --
+    so that repeated decompositions of one acquisition do not rebuild them).
     """
+    key = (_content_key(spec1.E, spec1.I0, spec2.E, spec2.I0, ct.det_E, ct.det_eta_E), bool(ct.eid), matcomp1, matcomp2,
+           id(xc.mixatten), _xc_impl.generation)
+    hit = _tables_memo.get(key)
+    if hit is not None:
+        return hit
     ee = np.unique(np.concatenate([np.asarray(spec1.E), np.asarray(spec2.E)]))
     dE = np.diff(ee, prepend=0.0)
     resp = np.interp(ee, ct.det_E, ct.det_eta_E)
@@ -38,6 +53,11 @@ def spectral_tables(ct, spec1, spec2):
         resp = resp * ee
     i0 = np.stack([np.interp(ee, s.E, s.I0) * resp * dE for s in (spec1, spec2)])
     mus = np.stack([xc.mixatten(mc, ee) for mc in (matcomp1, matcomp2)])
+    for a in (ee, i0, mus):
+        a.setflags(write=False)
+    if len(_tables_memo) >= 16:
+        _tables_memo.clear()
+    _tables_memo[key] = (ee, i0, mus)
     return ee, i0, mus
 
 

@@ -34,6 +34,7 @@ _MEC2 = 510.99895             # keV
 
 _tables = {}                  # symbol -> (E [keV], mu/rho [cm2/g]) registered real data
 _provider = None
+generation = 0                # bumped whenever the data behind mixatten changes (memoising callers key on it)
 
 
 def klein_nishina(E_keV):
@@ -88,10 +89,13 @@ def mixatten(matcomp, E_keV):
 
 def register_element_table(sym, E_keV, mu_rho):
     """Use tabulated (e.g. XCOM) data for one element; log-log interpolated."""
+    global generation
     _tables[sym] = (np.asarray(E_keV, dtype=np.float64), np.asarray(mu_rho, dtype=np.float64))
+    generation += 1
 
 
 def set_provider(fn):
     """Replace ``mixatten`` wholesale (e.g. with the real xcompy): fn(matcomp, E_keV) -> mu/rho.  None restores the model."""
-    global _provider
+    global _provider, generation
     _provider = fn
+    generation += 1
