@@ -396,6 +396,12 @@ def run_b200(args):
         cfg.dtype = args.dtype
         k_e2e = max(3, min(args.steps, 10))
 
+        # N > 1: every rank keeps the host arrays of ITS OWN view range (config.gather_views off) -- the data-parallel form
+        # in which each rank writes its part of the output; with the default (every rank returns the whole arrays, like
+        # the single-process reference) each rank would move the whole scan over its PCIe link and the host side could
+        # not scale.  The air-mask maximum is still reduced over all ranks.
+        cfg.gather_views = ws == 1
+
         def e2e_step():
             FP.clear_cache()                                            # the phantom is uploaded and re-laid-out every step
             (raw_lo, log_lo), (raw_hi, log_hi) = FP.get_sinos(ct, ph, [lo, hi])
@@ -415,12 +421,14 @@ def run_b200(args):
         esz = 4 if args.dtype == 'f32' else 8
         # up: labels + tables + the two float64 count sinograms handed to get_basismat_sinos (they sit in page-locked
         # memory: get_sinos returned them); down: 2 x (raw, log) + 2 basis sinograms, float64 like the reference's arrays
-        h2d = ph.M.nbytes + 2 * n_views * N_CH * 8             # the KB-sized tables are uploaded once per content
+        # summed over ranks; the KB-sized tables are uploaded once per content
+        h2d = ws * ph.M.nbytes + 2 * n_views * N_CH * 8
         d2h = 6 * n_views * N_CH * 8
         e2e = {'value': n_views * N_CH / float(dt[0]), 'unit': UNIT, 'h2d_bytes_per_step': int(h2d), 'd2h_bytes_per_step': int(d2h),
                'ms_per_step': 1e3 * float(dt[0]), 'steps': k_e2e,
                'api': 'xtomosim.forward_project.get_sinos + matdecomp.get_basismat_sinos (float64 numpy in/out through page-locked '
-                      'buffers, phantom re-uploaded and re-laid-out every step)'}
+                      'buffers, phantom re-uploaded and re-laid-out every step'
+                      + (')' if ws == 1 else '; every rank keeps the host arrays of its own view range, bytes summed over ranks)')}
 
     if rank == 0:
         peaks = {}

@@ -12,6 +12,12 @@ cache_lengths = os.environ.get('DEXCT_CACHE_LENGTHS', '1') != '0'
 # Shard projection views (and decomposition pixels) over torch.distributed ranks when a process group is initialised.
 shard_views = os.environ.get('DEXCT_SHARD_VIEWS', '1') != '0'
 
+# With sharded views: True (default) = every rank returns the WHOLE arrays, like the single-process reference (all-gather +
+# a full device-to-host copy on every rank, so the host side does not scale); False = every rank returns, and accepts, only
+# ITS OWN contiguous view range [dexct.dist.shard_range(N_proj, rank, world)] -- the data-parallel form in which each rank
+# writes its part of the output files.  The air-mask maximum is still taken over all ranks.
+gather_views = os.environ.get('DEXCT_GATHER_VIEWS', '1') != '0'
+
 # Print progress the way the reference does (matdecomp.py:111-112)
 verbose = os.environ.get('DEXCT_VERBOSE', '0') != '0'
 

@@ -132,12 +132,18 @@ def do_matdecomp_gn(ct, sino1, sino2, spec1, spec2, n_iters, mask_thresh=0.0, to
     ee, i0, mus = spectral_tables(ct, spec1, spec2)
     rank, ws = dist.world() if config.shard_views else (0, 1)
     if ws > 1:
-        n_views = sino1.shape[0]
+        n_views = ct.N_proj
         v0, nv = dist.shard_range(n_views, rank, ws)
+        if sino1.shape[0] == n_views:
+            part = (sino1[v0:v0 + nv], sino2[v0:v0 + nv])
+        elif sino1.shape[0] == nv and not config.gather_views:
+            part = (sino1, sino2)                        # the caller holds only its own view range (config.gather_views off)
+        else:
+            raise ValueError(f'sinograms have {sino1.shape[0]} views: expected the whole scan ({n_views})'
+                             + ('' if config.gather_views else f' or this rank\'s range ({nv})'))
         # the air threshold needs the maximum over the whole sinogram: one integer MAX all-reduce between the shards
-        local = optimize_sino((sino1[v0:v0 + nv], sino2[v0:v0 + nv]), ee, i0, mus, n_iters, mask_thresh=mask_thresh,
-                              to_host=False, reduce_max_over_ranks=True)
-        full = dist.all_gather_views(local, n_views, dim=0)
+        local = optimize_sino(part, ee, i0, mus, n_iters, mask_thresh=mask_thresh, to_host=False, reduce_max_over_ranks=True)
+        full = dist.all_gather_views(local, n_views, dim=0) if config.gather_views else local
         return _host_f64(full) if to_host else full
     return optimize_sino((sino1, sino2), ee, i0, mus, n_iters, mask_thresh=mask_thresh, to_host=to_host)
 

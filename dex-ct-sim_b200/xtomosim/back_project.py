@@ -37,11 +37,12 @@ def recon_device(sino, ct, N_matrix, FOV, ramp, dtype=None):
         raise NotImplementedError('get_recon needs a full rotation (short-scan weighting is not implemented); '
                                   f'rotation_angle_total = {ct.rotation}')
     n_views = ct.N_proj
-    if sino.shape[0] != n_views or sino.shape[-1] != ct.N_channels:
-        raise ValueError(f'sinogram shape {tuple(sino.shape)} does not match the scanner ({n_views} views x {ct.N_channels} channels)')
     rank, ws = dist.world() if config.shard_views else (0, 1)
     v0, nv = dist.shard_range(n_views, rank, ws)
-    part = sino[v0:v0 + nv]
+    local_only = ws > 1 and not config.gather_views and sino.shape[0] == nv and nv != n_views
+    if (sino.shape[0] != n_views and not local_only) or sino.shape[-1] != ct.N_channels:
+        raise ValueError(f'sinogram shape {tuple(sino.shape)} does not match the scanner ({n_views} views x {ct.N_channels} channels)')
+    part = sino if local_only else sino[v0:v0 + nv]      # local_only: the caller holds just this rank's view range
     dev = torch.device('cuda', torch.cuda.current_device())
     if isinstance(part, torch.Tensor):
         local = part.to(device=dev, dtype=td)

@@ -146,7 +146,7 @@ def _to_host(tensors, ct):
     """
     hosts = []
     for t in tensors:
-        if config.shard_views:
+        if config.shard_views and config.gather_views:
             t = dist.all_gather_views(t, ct.N_proj, dim=t.dim() - 3)
         h = torch.empty(t.shape, dtype=torch.float64, pin_memory=True)
         h.copy_(t, non_blocking=True)
