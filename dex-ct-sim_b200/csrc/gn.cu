@@ -182,10 +182,14 @@ __global__ void __launch_bounds__(256, (PX == 4 && CTAB) ? 3 : 1) gn_kernel(cons
     // compiler may not use the uniform datapath, and the table reads fall back from LDCU to per-thread LDC (2x slower).
     const long long stride = blockDim.x;
     const long long n_groups = (P + stride * PX - 1) / (stride * PX);
-    if (rider.n && n_iters == 0) gn_rider_slice(rider, 0, 1);
+    // the rider's copy is cut into one slice per (group of this CTA, Newton iteration), so that it trickles out over the
+    // whole run of the kernel whatever the number of pixels; CTAs that own one group fewer send their last slices at the end
+    const int rider_per_grp = n_iters > 0 ? n_iters : 1;
+    const int rider_nk = rider_per_grp * (int)((n_groups + gridDim.x - 1) / gridDim.x);
+    int rider_k = 0;
+    const bool ride = rider.n != 0;                           // CTA-uniform
     for (long long grp = blockIdx.x; grp < n_groups; grp += gridDim.x) {
         const long long base = grp * stride * PX + threadIdx.x;
-        const bool ride = rider.n && grp == blockIdx.x;       // CTA-uniform: the slices go out during the first group
         R a1[PX], a2[PX], g1[PX], g2[PX];
         bool sane[PX];
 #pragma unroll
@@ -197,7 +201,7 @@ __global__ void __launch_bounds__(256, (PX == 4 && CTAB) ? 3 : 1) gn_kernel(cons
             g2[k] = p < P ? g[P + p] : (R)1;
         }
         for (int it = 0; it < n_iters; ++it) {
-            if (ride) gn_rider_slice(rider, it, n_iters);
+            if (ride) gn_rider_slice(rider, rider_k++, rider_nk);
             R acc[PX][12];
             if constexpr (PACKED) {
                 // FFMA2 (sm_100a): accumulator pair q = (measurement 1, measurement 2) of moment q; att is broadcast
@@ -364,6 +368,8 @@ __global__ void __launch_bounds__(256, (PX == 4 && CTAB) ? 3 : 1) gn_kernel(cons
             }
         }
     }
+    if (ride)
+        for (; rider_k < rider_nk; ++rider_k) gn_rider_slice(rider, rider_k, rider_nk);
 }
 
 // Float64 pass over the pixels the single-precision kernel flagged (scratch: [2] = count, [4 ...] = pixel ids): the same

@@ -38,14 +38,14 @@ def spectral_tables(ct, spec1, spec2):
     Union energy grid of the two spectra; first bin width runs from 0; detector efficiency interpolated onto the grid
     (times E for an energy-integrating detector); spectra interpolated with numpy's end-value clamping; basis rows are
     MASS attenuation (the reference leaves the density multiply commented out, so the outputs are g/cm^2).
-    Returns ee [nE], i0 [2, nE], mus [2, nE] (read-only: memoised on the CONTENT of the inputs -- a few hundred numbers --
-    so that repeated decompositions of one acquisition do not rebuild them).
+    Returns ee [nE], i0 [2, nE], mus [2, nE] (memoised on the CONTENT of the inputs -- a few hundred numbers -- so that
+    repeated decompositions of one acquisition do not rebuild them; the caller gets its own copies).
     """
     key = (_content_key(spec1.E, spec1.I0, spec2.E, spec2.I0, ct.det_E, ct.det_eta_E), bool(ct.eid), matcomp1, matcomp2,
            id(xc.mixatten), _xc_impl.generation)
     hit = _tables_memo.get(key)
     if hit is not None:
-        return hit
+        return tuple(a.copy() for a in hit)
     ee = np.unique(np.concatenate([np.asarray(spec1.E), np.asarray(spec2.E)]))
     dE = np.diff(ee, prepend=0.0)
     resp = np.interp(ee, ct.det_E, ct.det_eta_E)
@@ -53,11 +53,9 @@ def spectral_tables(ct, spec1, spec2):
         resp = resp * ee
     i0 = np.stack([np.interp(ee, s.E, s.I0) * resp * dE for s in (spec1, spec2)])
     mus = np.stack([xc.mixatten(mc, ee) for mc in (matcomp1, matcomp2)])
-    for a in (ee, i0, mus):
-        a.setflags(write=False)
     if len(_tables_memo) >= 16:
         _tables_memo.clear()
-    _tables_memo[key] = (ee, i0, mus)
+    _tables_memo[key] = (ee.copy(), i0.copy(), mus.copy())
     return ee, i0, mus
 
 

@@ -48,6 +48,12 @@ def test_single_rank_group_and_mirrored_decomposition():
             assert torch.equal(d1, gd) and torch.equal(d2, gd) and torch.equal(m3, out)
             if iters == 15:
                 assert torch.equal(out, plain)
+    # more pixels than one resident wave covers (a CTA then owns two groups, some only one): every slice must still go out
+    gb, i0b, musb, _ = S.gn_problem(700, 700, 30)
+    gd = torch.as_tensor(gb, dtype=torch.float32, device='cuda')
+    d1 = torch.zeros_like(gd)
+    out = gn_decompose(gd, i0b, musb, 3, dtype=F32, push=(gd, (C.c_void_p * 1)(d1.data_ptr())))
+    assert torch.equal(d1, gd) and torch.equal(out, gn_decompose(gd, i0b, musb, 3, dtype=F32))
     assert pg.status() == 0
     pg.close()
 

@@ -10,7 +10,8 @@
     python -m torch.distributed.run --nproc-per-node N ... tools/bench_configs.py C4 C5    # views sharded over N GPUs
 
 Under torchrun the total work is fixed (strong scaling): rank r traces, decomposes and back-projects its own contiguous view
-range; sinograms are assembled with all-gathers and the partial images summed with one all-reduce per volume (SURVEY.md
+range; sinograms are assembled through peer memory (the GN kernel carries the count/log shard and mirrors its results, as in
+bench.py; DEXCT_COLLECTIVE=nccl: all-gathers) and the partial images summed with one all-reduce per volume (SURVEY.md
 section 8e).  Times are CUDA-event times on the launching stream, max over ranks; inputs are resident before the timed
 region; every working set is far larger than the 126 MB L2 (C3: 268 MB of counts in, C4/C5: GBs).  One JSON line per
 configuration, printed by rank 0.
@@ -134,14 +135,28 @@ def run_scan(name, dev, rank, ws, reps, with_fbp):
     i0 = torch.as_tensor(i0_h, dtype=td, device=dev)
     mus = torch.as_tensor(mus_h, dtype=td, device=dev)
     R, Cn = ct.N_rows, ct.N_channels
-    counts = torch.empty((2, nv, R, Cn), dtype=td, device=dev)
-    logs = torch.empty_like(counts)
-    basis = torch.empty((nv, R, Cn, 2), dtype=td, device=dev)
     even = n_views % ws == 0
-    if ws > 1 and even:
-        g_counts = torch.empty((ws, 2, nv, R, Cn), dtype=td, device=dev)
-        g_logs = torch.empty_like(g_counts)
-        g_basis = torch.empty((ws, nv, R, Cn, 2), dtype=td, device=dev)
+    pg = None
+    if ws > 1 and even and os.environ.get('DEXCT_COLLECTIVE', 'peer') == 'peer':
+        # sinograms assembled through peer memory: the GN kernel carries the count/log shard to the other ranks' copies
+        # and stores its own results into all of them (dexct/peer.py), as bench.py does
+        from dexct.peer import PeerGroup
+        pg = PeerGroup()
+        slot_s, slot_b = 4 * nv * R * Cn * 4, nv * R * Cn * 2 * 4
+        sbuf, bbuf = pg.alloc(ws * slot_s), pg.alloc(ws * slot_b)
+        g_sino = sbuf.view(td, (ws, 4, nv, R, Cn))
+        g_basis = bbuf.view(td, (ws, nv, R, Cn, 2))
+        counts, logs, basis = g_sino[rank, 0:2], g_sino[rank, 2:4], g_basis[rank]
+        mirrors = bbuf.table(rank * slot_b, exclude_self=True)
+        push_table = sbuf.table(rank * slot_s, exclude_self=True)
+    else:
+        counts = torch.empty((2, nv, R, Cn), dtype=td, device=dev)
+        logs = torch.empty_like(counts)
+        basis = torch.empty((nv, R, Cn, 2), dtype=td, device=dev)
+        if ws > 1 and even:
+            g_counts = torch.empty((ws, 2, nv, R, Cn), dtype=td, device=dev)
+            g_logs = torch.empty_like(g_counts)
+            g_basis = torch.empty((ws, nv, R, Cn, 2), dtype=td, device=dev)
     n_matrix, fov, ramp = ph.Nx, ph.Nx * ph.dx, 0.8
     images = [torch.empty((R, n_matrix, n_matrix), dtype=td, device=dev) for _ in range(4)] if with_fbp else []
 
@@ -152,17 +167,21 @@ def run_scan(name, dev, rank, ws, reps, with_fbp):
         pj.project(mu, W, view_begin=v0, view_count=nv, counts=counts, logs=logs)
         st.mark('siddon_poly')
         pending = []
-        if ws > 1 and even:
+        if pg is None and ws > 1 and even:
             pending.append(dist.all_gather_into_tensor(g_counts, counts, async_op=True))
             pending.append(dist.all_gather_into_tensor(g_logs, logs, async_op=True))
         if with_fbp:
             for s in range(2):
                 fbp_fan(scan, logs[s], n_matrix, fov, ramp, view_begin=v0, image=images[s])
             st.mark('fbp_2_log_sinograms')
-        gn_decompose(counts.view(2, -1), i0, mus, GN_ITERS, mask_thresh=MASK_THRESH, out=basis.view(-1, 2),
-                     reduce_max_over_ranks=ws > 1)
+        if pg is not None:
+            gn_decompose(counts.reshape(2, -1), i0, mus, GN_ITERS, mask_thresh=MASK_THRESH, out=basis.view(-1, 2),
+                         reduce_max_over_ranks=True, peers=pg, mirrors=mirrors, push=(g_sino[rank], push_table))
+        else:
+            gn_decompose(counts.view(2, -1), i0, mus, GN_ITERS, mask_thresh=MASK_THRESH, out=basis.view(-1, 2),
+                         reduce_max_over_ranks=ws > 1)
         st.mark('gn')
-        if ws > 1 and even:
+        if pg is None and ws > 1 and even:
             pending.append(dist.all_gather_into_tensor(g_basis, basis, async_op=True))
         if with_fbp:
             for m in range(2):
@@ -173,6 +192,8 @@ def run_scan(name, dev, rank, ws, reps, with_fbp):
                     dist.all_reduce(im)
         for w in pending:
             w.wait()
+        if pg is not None:
+            pg.barrier()
         st.mark('collectives_tail')
         st.end()
 
@@ -214,8 +235,13 @@ def run_scan(name, dev, rank, ws, reps, with_fbp):
             'roofline_gn': {'bound': 'fp32_fma', 'achieved': gn_ach, 'peak': fma_peak, 'unit': 'TFLOP/s', 'frac': gn_ach / fma_peak},
             'prepare_ms': t_prepare, 'phantom_rasterise_s': t_phantom, 'all_finite': finite,
             'device_mem_gb': torch.cuda.max_memory_allocated(dev) / 1e9,
-            'collective': ('all-gather counts/logs/basis' + (' + all-reduce of 4 partial volumes' if with_fbp else '')) if ws > 1 and even
+            'collective': (('peer memory (GN kernel with fused push and mirrored epilogue)' if pg is not None else 'all-gather counts/logs/basis')
+                           + (' + all-reduce of 4 partial volumes' if with_fbp else '')) if ws > 1 and even
                           else ('all-reduce of 4 partial volumes' if ws > 1 and with_fbp else 'none')}
+    if pg is not None:
+        assert pg.status() == 0
+        del counts, logs, basis, g_sino, g_basis
+        pg.close()
     if with_fbp:
         pv = 2.0 * R * n_matrix * n_matrix * n_views
         line['fbp_pixel_views_per_s'] = pv / (t['fbp_2_log_sinograms'] * 1e-3)
