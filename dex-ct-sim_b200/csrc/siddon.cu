@@ -531,8 +531,9 @@ __device__ __forceinline__ f32x2 ffma2(f32x2 a, f32x2 b, f32x2 c)
 //   mu2 [nE2][KT]  float2 = mu_m * log2(e) at energies 2 e2, 2 e2 + 1  (rows of materials -> LDS.128 of two materials)
 //   W2  [nE2][NSP] float2 = W_s at energies 2 e2, 2 e2 + 1
 // An odd nE is padded with a zero-weight bin.  Per energy pair: KT FFMA2 + 2 MUFU.EX2 + NSP FFMA2.
-template <int KT, int NSP>
-__device__ __forceinline__ void detect_packed(const float (&Lr)[KT], const f32x2 *mu2, const f32x2 *W2, int nE2, float *out)
+// PM: bit h set = material pair (2h, 2h+1) takes part; a cleared bit promises that both lengths are zero.
+template <int KT, int NSP, unsigned PM>
+__device__ __forceinline__ void detect_packed_pm(const float (&Lr)[KT], const f32x2 *mu2, const f32x2 *W2, int nE2, float *out)
 {
     f32x2 L2[KT], acc[NSP];
 #pragma unroll
@@ -545,6 +546,7 @@ __device__ __forceinline__ void detect_packed(const float (&Lr)[KT], const f32x2
         f32x2 t0 = 0ull, t1 = 0ull;
 #pragma unroll
         for (int h = 0; h < KT / 2; ++h) {
+            if (!((PM >> h) & 1u)) continue;                 // compile time: adding 0 * mu would not change t0, t1
             const ulonglong2 q = row[h];
             t0 = ffma2(L2[2 * h], q.x, t0);
             t1 = ffma2(L2[2 * h + 1], q.y, t1);
@@ -566,6 +568,34 @@ __device__ __forceinline__ void detect_packed(const float (&Lr)[KT], const f32x2
         float x = 0.f, y = 0.f;
         if (sp < NSP) unpack2(acc[sp], x, y);
         out[sp] = x + y;
+    }
+}
+
+// Material sparsity: the 32 rays of a warp are neighbouring channels of one view and cross the same few materials (C2
+// phantom: 3.8 of 8 labels, 2.45 of the 4 label pairs per warp on average; one warp in five sees air only).  A pair whose
+// two lengths are zero in EVERY lane adds exact zeros to the exponent, so the warp votes once per ray batch and runs the
+// instance of the loop that leaves those pairs out -- bit-identical results, ~40 % fewer table loads and FFMA2.
+template <int KT, int NSP>
+__device__ __forceinline__ void detect_packed(const float (&Lr)[KT], const f32x2 *mu2, const f32x2 *W2, int nE2, float *out)
+{
+    if constexpr (KT == 8) {
+        const unsigned lanes = __activemask();
+        unsigned pm = 0;
+#pragma unroll
+        for (int h = 1; h < 4; ++h)
+            if (__any_sync(lanes, Lr[2 * h] != 0.f || Lr[2 * h + 1] != 0.f)) pm |= 1u << (h - 1);
+        switch (pm) {
+        case 0: detect_packed_pm<KT, NSP, 0x1u>(Lr, mu2, W2, nE2, out); break;
+        case 1: detect_packed_pm<KT, NSP, 0x3u>(Lr, mu2, W2, nE2, out); break;
+        case 2: detect_packed_pm<KT, NSP, 0x5u>(Lr, mu2, W2, nE2, out); break;
+        case 3: detect_packed_pm<KT, NSP, 0x7u>(Lr, mu2, W2, nE2, out); break;
+        case 4: detect_packed_pm<KT, NSP, 0x9u>(Lr, mu2, W2, nE2, out); break;
+        case 5: detect_packed_pm<KT, NSP, 0xBu>(Lr, mu2, W2, nE2, out); break;
+        case 6: detect_packed_pm<KT, NSP, 0xDu>(Lr, mu2, W2, nE2, out); break;
+        default: detect_packed_pm<KT, NSP, 0xFu>(Lr, mu2, W2, nE2, out); break;
+        }
+    } else {
+        detect_packed_pm<KT, NSP, 0xFFFFFFFFu>(Lr, mu2, W2, nE2, out);
     }
 }
 
