@@ -539,7 +539,7 @@ def extra_measurements(dev, dtype):
     out['prepare_c2_ms'] = timed(pj.prepare, 10)
     del pj
     n_views = 48
-    ct, ph, lo, hi = S.make_config('C4')
+    ct, ph, lo, hi = S.make_config('C4', device=dev)            # labels rasterised on the device (12 s in numpy)
     scan = make_scan(ct.N_proj, ct.N_channels, ct.gamma_fan, ct.SID, ct.SDD, n_rows=ct.N_rows, h_iso=ct.h_iso, rotation=ct.rotation)
     pj = Projector(scan, ph.M, (ph.dx, ph.dy, ph.dz), device=dev)
     out['prepare_c4_ms'] = timed(pj.prepare, 3)

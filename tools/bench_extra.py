@@ -49,7 +49,7 @@ def main():
     if 'c4' in which:
         n_views = int(os.environ.get('C4_VIEWS', '48'))
         t0 = time.time()
-        ct, ph, lo, hi = S.make_config('C4')
+        ct, ph, lo, hi = S.make_config('C4', device=dev)
         print('C4 phantom built in %.1f s' % (time.time() - t0))
         scan = make_scan(ct.N_proj, ct.N_channels, ct.gamma_fan, ct.SID, ct.SDD, n_rows=ct.N_rows, h_iso=ct.h_iso, rotation=ct.rotation)
         pj = Projector(scan, ph.M, (ph.dx, ph.dy, ph.dz), device=dev)
