@@ -265,6 +265,70 @@ __global__ void __launch_bounds__(256) fbp_backproject_kernel(const R *__restric
     *out = accumulate ? *out + r : r;
 }
 
+// Full rotation, view count a multiple of 4, even image size: the pixel turned by a quarter turn sees at view v + N/4 exactly
+// what the pixel itself sees at view v (same A, B, hence the same channel coordinate and 1/L^2).  A thread therefore owns the
+// four quarter-turn images of one pixel of the first quadrant and computes each (pixel, view) geometry once for all four:
+// per step j it works out the geometry at the views j, j + N/4, j + N/2, j + 3N/4 and feeds the sixteen (pixel k, view)
+// combinations from them -- 12.5 instead of 22 instructions per pixel-view.  `turn` is +1 when N/4 views advance the source
+// by +90 degrees (dbeta > 0), -1 otherwise.
+template <typename R, bool FAST>
+__global__ void __launch_bounds__(256) fbp_backproject_sym4_kernel(const R *__restrict__ q, int q_pitch, const R *__restrict__ cs,
+                                                                   int n_views, int n_rows, int n_ch, R sid, R gamma0,
+                                                                   R inv_dgamma, int n, R px, R scale, int accumulate, int turn,
+                                                                   R *__restrict__ image)
+{
+    typedef FbpMath<R, FAST> M;
+    const int ix = blockIdx.x * blockDim.x + threadIdx.x;
+    const int iy = blockIdx.y * blockDim.y + threadIdx.y;
+    const int row = blockIdx.z;
+    const int nh = n >> 1;
+    if (ix >= nh || iy >= nh) return;
+    const R half = (R)0.5 * (R)(n - 1);
+    const R x = ((R)ix - half) * px, y = ((R)iy - half) * px;
+    const R umax = (R)n_ch, ubias = -gamma0 * inv_dgamma;
+    const int nq = n_views >> 2;
+    const long long view_stride = (long long)n_rows * q_pitch;
+    const R *line = q + (long long)row * q_pitch + 1;
+    R acc[4] = {(R)0, (R)0, (R)0, (R)0};
+    for (int j = 0; j < nq; ++j) {
+        int off[4];
+        R f[4], w[4];
+#pragma unroll
+        for (int m = 0; m < 4; ++m) {
+            const int v = j + m * nq;
+            const R cb = cs[2 * v], sb = cs[2 * v + 1];
+            const R A = sid - fma(y, sb, x * cb);
+            const R negB = fma(x, sb, -(y * cb));
+            const R gam = M::gamma(negB, A);
+            R u = fma(gam, inv_dgamma, ubias);
+            u = fmin(fmax(u, (R)-1), umax);
+            const R fl = fmin(floor(u), umax - (R)1);
+            f[m] = u - fl;
+            off[m] = (int)fl;
+            w[m] = M::inv(fma(A, A, negB * negB));
+        }
+        const R *pj = line + j * view_stride;
+#pragma unroll
+        for (int m = 0; m < 4; ++m)
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {                    // pixel k (k quarter turns) at view j + ((m + k) & 3) N/4
+                const R *p = pj + (long long)((m + k) & 3) * nq * view_stride + off[m];
+                const R q0 = p[0], q1 = p[1];
+                acc[k] = fma(fma(f[m], q1 - q0, q0), w[m], acc[k]);
+            }
+    }
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+        // k quarter turns of (ix, iy): +90 degrees maps (ix, iy) -> (n-1-iy, ix), -90 degrees -> (iy, n-1-ix)
+        const int kk = turn > 0 ? k : (4 - k) & 3;
+        const int jx = kk == 0 ? ix : kk == 1 ? n - 1 - iy : kk == 2 ? n - 1 - ix : iy;
+        const int jy = kk == 0 ? iy : kk == 1 ? ix : kk == 2 ? n - 1 - iy : n - 1 - ix;
+        R *out = image + ((long long)row * n + jy) * n + jx;
+        const R r = acc[k] * scale;
+        *out = accumulate ? *out + r : r;
+    }
+}
+
 // Multi-row scans: every detector row is its own fan-beam slice with the SAME in-plane geometry, so the channel coordinate,
 // the interpolation weight and 1/L^2 of a (pixel, view) pair are computed once and applied to RB rows.  The filtered data
 // are row-fastest (q[view][plane][row_pitch], plane = channel + 1 with a zero plane on either side), so the RB values of
@@ -508,6 +572,19 @@ static int fbp_run(const DexctScan &s, const void *sino, int view_begin, int vie
         else if (fast) kern = fbp_backproject_rows_kernel<R, sizeof(R) == 4, 8>;
         kern<<<grid, block, 0, st>>>(q, row_pitch, cs, view_count, s.n_rows, s.n_ch, (R)s.sid, (R)s.gamma0, (R)(1.0 / s.dgamma),
                                      n, (R)(fov / n), (R)s.dbeta, accumulate, (R *)image);
+        DEXCT_CUDA_OK(cudaGetLastError());
+        return DEXCT_OK;
+    }
+    // whole full-rotation scans with 4 | n_views and an even image: quarter-turn symmetry (fbp_backproject_sym4_kernel)
+    const double turn_angle = s.dbeta * (double)(s.n_views / 4);
+    const char *sym_env = getenv("DEXCT_FBP_SYM");            // tuning knob: 0 forces the general kernel
+    if (view_begin == 0 && view_count == s.n_views && s.n_views % 4 == 0 && n % 2 == 0 &&
+        fabs(fabs(turn_angle) - 1.5707963267948966) < 1e-9 && !(sym_env && atoi(sym_env) == 0)) {
+        const dim3 block(32, 8), grid((n / 2 + 31) / 32, (n / 2 + 7) / 8, s.n_rows);
+        auto kern = fbp_backproject_sym4_kernel<R, false>;
+        if (fast) kern = fbp_backproject_sym4_kernel<R, sizeof(R) == 4>;
+        kern<<<grid, block, 0, st>>>(q, L.q_pitch, cs, s.n_views, s.n_rows, s.n_ch, (R)s.sid, (R)s.gamma0, (R)(1.0 / s.dgamma),
+                                     n, (R)(fov / n), (R)s.dbeta, accumulate, turn_angle > 0 ? 1 : -1, (R *)image);
         DEXCT_CUDA_OK(cudaGetLastError());
         return DEXCT_OK;
     }

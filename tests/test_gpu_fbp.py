@@ -79,6 +79,34 @@ def test_many_rows_share_the_in_plane_geometry(dtype, n_rows):
     assert scale_rel_err(img.cpu().numpy(), got.cpu().numpy()) < (1e-6 if dtype == F32 else 1e-13)
 
 
+@pytest.mark.parametrize('dtype', [F32, F64])
+@pytest.mark.parametrize('rotation', [2.0 * np.pi, -2.0 * np.pi])
+@pytest.mark.parametrize('n_rows', [1, 3])
+def test_quarter_turn_symmetry_path(dtype, rotation, n_rows, monkeypatch):
+    """Whole full-rotation scans with 4 | n_views and an even image take the kernel that shares each (pixel, view) geometry
+    between the four quarter-turn images of the pixel: it must match the oracle and the general kernel, for either sense of
+    rotation and any start angle, also when accumulating."""
+    n_views, n_ch, n = 80, 151, 64
+    scan = make_scan(n_views, n_ch, FAN, SID, SDD, n_rows=n_rows, h_iso=0.3, rotation=rotation, beta0=0.37)
+    beta = scan.beta0 + np.arange(n_views) * scan.dbeta
+    gam = scan.gamma0 + np.arange(n_ch) * scan.dgamma
+    r = np.random.default_rng(4)
+    sino = np.stack([FO.disc_sinogram(beta, gam, SID, (4.0 - k, -3.0 + 2 * k), 6.0, 0.2) + 0.01 * r.standard_normal((n_views, n_ch))
+                     for k in range(n_rows)], axis=1)
+    ref = FO.fbp_fan(sino, beta, scan.gamma0, scan.dgamma, scan.dbeta, SID, n, 38.0, 0.8)
+    d = torch.as_tensor(sino, device='cuda')
+    got = fbp_fan(scan, d, n, 38.0, 0.8, dtype=dtype)
+    assert scale_rel_err(got.cpu().numpy(), ref) < TOL[dtype]
+    monkeypatch.setenv('DEXCT_FBP_SYM', '0')
+    plain = fbp_fan(scan, d, n, 38.0, 0.8, dtype=dtype)
+    monkeypatch.delenv('DEXCT_FBP_SYM')
+    assert not torch.equal(plain, got)                       # (two kernels: the sums run in different orders)
+    assert scale_rel_err(got.cpu().numpy(), plain.cpu().numpy()) < (2e-6 if dtype == F32 else 1e-13)
+    img = got.clone()
+    fbp_fan(scan, d, n, 38.0, 0.8, dtype=dtype, image=img, accumulate=True)
+    assert scale_rel_err(img.cpu().numpy(), 2.0 * got.cpu().numpy()) < 1e-6
+
+
 def test_view_chunks_accumulate_to_the_whole_scan():
     """What view-sharded ranks do: partial images of disjoint view ranges sum to the image of the whole scan."""
     scan, beta, sino = _case(n_views=90)
