@@ -140,3 +140,75 @@ def test_all_gather_views_gloo_world2(n_views):
     for p in procs:
         p.join(timeout=60)
     assert res == [(0, True), (1, True)]
+
+
+def test_spectral_tables_memo_follows_its_inputs():
+    """The decomposition tables are memoised on the CONTENT of their inputs: the same content returns equal (separate)
+    arrays, a changed spectrum or a changed attenuation provider returns new ones."""
+    import matdecomp
+    import xcompy
+    from dexct import synthetic as S
+    ct, ph, lo, hi = S.make_config('C2', n_views=4, n=32)
+    a = matdecomp.spectral_tables(ct, lo, hi)
+    b = matdecomp.spectral_tables(ct, lo, hi)
+    assert all(np.array_equal(x, y) and x is not y for x, y in zip(a, b))
+    b[1][...] = 0                                              # the caller's copy is its own
+    assert np.array_equal(matdecomp.spectral_tables(ct, lo, hi)[1], a[1])
+    lo.I0 = lo.I0 * 2.0
+    c = matdecomp.spectral_tables(ct, lo, hi)
+    assert np.allclose(c[1][0], 2.0 * a[1][0]) and np.array_equal(c[1][1], a[1][1])
+    try:
+        xcompy.register_element_table('Ca', [1.0, 1000.0], [1.0, 1.0])
+        d = matdecomp.spectral_tables(ct, lo, hi)
+        assert not np.array_equal(d[2], c[2])                  # bone contains calcium
+    finally:
+        import xtomosim.xcompy as impl
+        impl._tables.pop('Ca', None)
+        impl.generation += 1
+    assert np.array_equal(matdecomp.spectral_tables(ct, lo, hi)[2], c[2])
+
+
+def test_cone_recurrence_equals_runs_then_diagonal_minimum():
+    """The skip layouts' run length is defined by the cone recurrence S(i,j) = 1 + min(S'(i+1,j), S'(i+1,j+1)); the device
+    builds it as R = run of homogeneous words of one label along the columns, then S(i,j) = min(R(i,j), 1 + S'(i+1,j+1))
+    along diagonals (csrc/siddon.cu, skip_runs_kernel / skip_cone_kernel).  Same numbers, on random and on blobby images."""
+    rng = np.random.default_rng(1)
+
+    def cone(lo, hi):
+        npc, ne = lo.shape
+        S = np.zeros((npc, ne), int)
+        pS, pL = np.zeros(ne + 1, int), np.full(ne + 1, 255)
+        for i in range(npc - 1, -1, -1):
+            cS, cL = np.zeros(ne + 1, int), np.full(ne + 1, 255)
+            for j in range(ne):
+                if lo[i, j] == hi[i, j]:
+                    sa = pS[j] if pL[j] == lo[i, j] else 0
+                    sb = pS[j + 1] if pL[j + 1] == lo[i, j] else 0
+                    S[i, j] = cS[j] = min(1 + min(sa, sb), 127)
+                    cL[j] = lo[i, j]
+            pS, pL = cS, cL
+        return S
+
+    def two_pass(lo, hi):
+        npc, ne = lo.shape
+        hom = lo == hi
+        R = np.zeros((npc + 1, ne + 1), int)
+        S = np.zeros((npc + 1, ne + 1), int)
+        for i in range(npc - 1, -1, -1):
+            for j in range(ne):
+                if hom[i, j]:
+                    ok = i + 1 < npc and hom[i + 1, j] and lo[i + 1, j] == lo[i, j]
+                    R[i, j] = min(1 + (R[i + 1, j] if ok else 0), 127)
+        for i in range(npc - 1, -1, -1):
+            for j in range(ne):
+                if hom[i, j]:
+                    ok = i + 1 < npc and j + 1 < ne and hom[i + 1, j + 1] and lo[i + 1, j + 1] == lo[i, j]
+                    S[i, j] = min(R[i, j], 1 + (S[i + 1, j + 1] if ok else 0))
+        return S[:npc, :ne]
+
+    for trial in range(12):
+        npc, ne = int(rng.integers(3, 36)), int(rng.integers(3, 36))
+        img = rng.integers(0, 3, (npc, ne + 1))
+        if trial % 2:
+            img = np.repeat(np.repeat(rng.integers(0, 3, (npc // 4 + 1, ne // 4 + 2)), 4, 0), 4, 1)[:npc, :ne + 1]
+        assert np.array_equal(cone(img[:, :-1], img[:, 1:]), two_pass(img[:, :-1], img[:, 1:]))
