@@ -76,6 +76,11 @@ class FanBeamGeometry:
         self.h_iso = float(h_iso)
         self.eid = bool(eid)
         self.rotation = float(rotation)
+        # "rotation_angle_total": 6.283185 (input/params.txt:27) is 2 pi written with seven digits: a total within 1e-5 of
+        # a full turn IS a full turn (project-defined), which keeps view v + N/4 exactly a quarter turn
+        # from view v -- the symmetry the back-projection uses
+        if abs(abs(self.rotation) - 2.0 * np.pi) < 1e-5:
+            self.rotation = float(np.copysign(2.0 * np.pi, self.rotation))
         self.beta0 = float(beta0)
         self.dgamma = self.gamma_fan / self.N_channels
         self.dbeta = self.rotation / self.N_proj
