@@ -168,3 +168,29 @@ def test_starved_pixels_stay_finite_in_single_precision():
     st = np.flatnonzero(fin[:60])
     rel = np.abs(out32[st] - out64[st]).max(axis=1) / np.maximum(np.abs(out64[st]).max(axis=1), 1.0)
     assert np.median(rel) < 1e-4
+
+
+@pytest.mark.parametrize('nE', [2, 3, 509, 510, 511, 640])
+def test_bin_counts_around_the_constant_bank_limit(nE):
+    """The single-precision kernel keeps its tables in the constant bank up to 510 bins (two padding rows of the 512) and in
+    shared memory beyond; odd bin counts run the two-bin pipelined loop into a zero row.  Every size must give the
+    reference's numbers (oracle/gn_oracle.py) -- synthetic spectra, counts from the forward model of matdecomp.py:116-118."""
+    rng = np.random.default_rng(nE)
+    E = np.linspace(40.0, 140.0, nE)
+    mus = np.stack([0.2 + 0.6 * (E / 20.0) ** -3 + 0.1 * (E / 60.0) ** -0.3,
+                    0.15 + 6.0 * (E / 20.0) ** -3 + 0.12 * (E / 60.0) ** -0.3])
+    i0 = (np.stack([np.exp(-0.5 * ((E - 55) / 18) ** 2), np.exp(-0.5 * ((E - 95) / 25) ** 2)]) + 1e-3) * 3e6 / nE
+    a_true = np.stack([rng.uniform(0, 12, (3, 41)), rng.uniform(0, 3, (3, 41))], -1)
+    att = np.exp(-(a_true[..., None, :] * mus.T[None, None]).sum(-1))             # [3, 41, nE]
+    g = np.stack([(att * i0[m]).sum(-1) for m in range(2)])
+    want = _oracle(g, i0, mus, 20)
+    assert scale_rel_err(want, a_true) < 1e-8                                      # the oracle recovers the truth
+    out64 = gn_decompose(g, i0, mus, 20, dtype=F64).cpu().numpy()
+    assert scale_rel_err(out64, want) < 1e-10
+    g32 = g.astype(np.float32).astype(np.float64)
+    i032 = i0.astype(np.float32).astype(np.float64)
+    mus32 = mus.astype(np.float32).astype(np.float64)
+    want32 = _oracle(g32, i032, mus32, 20)
+    out32 = gn_decompose(g, i0, mus, 20, dtype=F32).cpu().numpy()
+    assert np.isfinite(out32).all()
+    assert scale_rel_err(out32, want32) < 1e-5
