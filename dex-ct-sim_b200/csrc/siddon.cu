@@ -1033,15 +1033,24 @@ static int make_params(const DexctScan *scan, const DexctVolume *vol, const void
     return DEXCT_OK;
 }
 
+// Threads per CTA: 128, halved (down to one warp) while the per-thread material accumulators (acc_bytes each) plus the tables
+// do not fit into 200 KiB of shared memory -- float64 scans with more than ~180 materials.
+static int cta_threads(size_t acc_bytes, size_t tab_bytes)
+{
+    int block = 128;
+    while (block > 32 && acc_bytes * block + tab_bytes > 200 * 1024) block >>= 1;
+    return block;
+}
+
 template <typename R, bool IS3D, int KT, int NSP>
 static int launch_skip(const SiddonParams &P, int view_begin, long long n_rays, const DetectArgs &d, cudaStream_t st)
 {
-    const int block = 128;
     const int KP = KT > 0 ? KT : d.K;
     const bool packed = sizeof(R) == 4 && KT > 0;
     const int nE2 = (d.nE + 1) / 2;
     const size_t tab = packed ? 8 * (size_t)nE2 * (KT + NSP) + sizeof(R) * MAX_SPEC
                               : sizeof(R) * ((size_t)KP * d.nE + (size_t)d.nSpec * d.nE + MAX_SPEC);
+    const int block = cta_threads(sizeof(R) * (size_t)KP, tab);
     const size_t smem = sizeof(R) * (size_t)KP * block + tab;
     if (smem > 200 * 1024) {
         set_error("material/energy tables need %zu bytes of shared memory (limit 200 KiB): K=%d nE=%d", smem, d.K, d.nE);
@@ -1067,9 +1076,10 @@ static int launch_poly(const SiddonParams &P, int view_begin, long long n_rays, 
     if (P.skip[0] != nullptr && d.K <= 128)
         return d.nSpec <= 2 ? launch_skip<R, IS3D, KT, 2>(P, view_begin, n_rays, d, st)
                             : launch_skip<R, IS3D, KT, 4>(P, view_begin, n_rays, d, st);
-    const int block = 128;
     const int KP = KT > 0 ? KT : d.K;
-    const size_t smem = sizeof(R) * ((size_t)KP * block + (size_t)KP * d.nE + (size_t)d.nSpec * d.nE + MAX_SPEC);
+    const size_t tab = sizeof(R) * ((size_t)KP * d.nE + (size_t)d.nSpec * d.nE + MAX_SPEC);
+    const int block = cta_threads(sizeof(R) * (size_t)KP, tab);
+    const size_t smem = sizeof(R) * (size_t)KP * block + tab;
     if (smem > 200 * 1024) {
         set_error("material/energy tables need %zu bytes of shared memory (limit 200 KiB): K=%d nE=%d", smem, d.K, d.nE);
         return DEXCT_ECAPACITY;
@@ -1217,9 +1227,10 @@ extern "C" int dexct_poly_detect(const void *L, int64_t n_rays, const void *mu, 
     DEXCT_REQUIRE(L && mu && W && counts, "L, mu, W and counts must be non-null");
     DetectArgs d{mu, W, K, nE, nSpec, counts, logs, nullptr};
     cudaStream_t st = (cudaStream_t)stream;
-    const int block = 128;
     const size_t esz = dtype == DEXCT_F32 ? 4 : 8;
-    const size_t smem = esz * ((size_t)K * block + (size_t)K * nE + (size_t)nSpec * nE + MAX_SPEC);
+    const size_t tab = esz * ((size_t)K * nE + (size_t)nSpec * nE + MAX_SPEC);
+    const int block = cta_threads(esz * (size_t)K, tab);
+    const size_t smem = esz * (size_t)K * block + tab;
     if (smem > 200 * 1024) {
         set_error("material/energy tables need %zu bytes of shared memory (limit 200 KiB): K=%d nE=%d", smem, K, nE);
         return DEXCT_ECAPACITY;

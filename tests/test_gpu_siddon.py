@@ -314,3 +314,26 @@ def test_c4_c5_full_size_properties(name):
     assert scale_rel_err(counts.reshape(2, -1).cpu().numpy(), c_ref) < TOL[F32]
     per_ray = seg / (ct.N_rows * ct.N_channels)
     assert (500 < per_ray < 800) if name == 'C4' else (1000 < per_ray < 1600)
+
+
+@pytest.mark.parametrize('dtype', [F32, F64])
+@pytest.mark.parametrize('nz,n_rows,K', [(1, 1, 128), (1, 1, 129), (10, 4, 129), (1, 1, 256), (10, 4, 256)])
+def test_up_to_256_materials(dtype, nz, n_rows, K):
+    """Label values up to 255 (the uint8 phantom format's maximum).  The skip layouts keep 7 bits per label, so K <= 128 walks
+    them and K > 128 falls back to the pair-layout kernel (one column per step); the lengths stay in shared memory instead of
+    registers for K > 16.  Same numbers as Siddon 1985 either way."""
+    pj, sc = _pair(nz=nz, n_rows=n_rows, K=K, n_views=12, seed=K)
+    r = np.random.default_rng(K)
+    E = np.linspace(30, 120, 24)
+    mu = (0.01 + r.uniform(0, 0.4, (K, 1))) * (0.6 + (60.0 / E) ** r.uniform(1.0, 2.5, (K, 1)))
+    mu[0] = 0.0002
+    W = r.uniform(0.2, 1.0, (2, 24)) * 1e4
+    counts, logs, L = pj.project(mu, W, dtype=dtype, want_log=True, want_L=True)
+    L_ref, seg = sc.classic_lengths(K)
+    assert seg > 0 and L_ref[..., K - 1].max() > 0                                 # the highest label is really met
+    assert scale_rel_err(L.cpu().numpy(), L_ref) < TOL[dtype]
+    c_ref, l_ref, _ = sc.project_poly(mu, W)
+    assert scale_rel_err(counts.cpu().numpy(), c_ref) < TOL[dtype]
+    assert scale_rel_err(logs.cpu().numpy(), l_ref) < (1e-9 if dtype == F64 else 3e-5)
+    c2, l2 = poly_detect(L, mu, W, dtype=dtype)
+    assert scale_rel_err(c2.cpu().numpy(), counts.cpu().numpy()) < (1e-14 if dtype == F64 else 1e-6)
