@@ -365,3 +365,22 @@ def test_rectangular_volumes_and_anisotropic_voxels(dtype, shape, voxel, n_rows)
     # a view range on its own equals the same views inside the whole scan
     c_part, _, _ = pj.project(mu, W, view_begin=7, view_count=9, dtype=dtype)
     assert torch.equal(c_part, counts[:, 7:16])
+
+
+@pytest.mark.parametrize('dtype', [F32, F64])
+@pytest.mark.parametrize('n,nz,n_ch,n_views,n_rows,h_iso', [(1, 1, 1, 1, 1, 0.4), (2, 1, 3, 5, 1, 0.4), (33, 1, 7, 3, 4, 0.5),
+                                                             (17, 3, 33, 2, 1, 0.4), (40, 5, 1, 9, 2, 0.3), (64, 2, 40, 6, 3, 0.2)])
+def test_tiny_and_lopsided_sizes(dtype, n, nz, n_ch, n_views, n_rows, h_iso):
+    """One voxel, one ray, one view; a single slice under a multi-row detector (rays leave the slab through its faces);
+    odd plane counts under a single row in the mid-plane; fewer channels than a warp."""
+    pj, sc = _pair(n=n, n_ch=n_ch, n_views=n_views, n_rows=n_rows, nz=nz, K=5, fov=25.6 if n > 2 else 4.0, h_iso=h_iso,
+                   beta0=0.3, seed=n)
+    mu, W = _tables(5)
+    counts, logs, L = pj.project(mu, W, dtype=dtype, want_log=True, want_L=True)
+    assert counts.shape == (2, n_views, n_rows, n_ch) and L.shape == (n_views, n_rows, n_ch, 5)
+    L_ref, seg = sc.classic_lengths(5)
+    assert scale_rel_err(L.cpu().numpy(), L_ref) < TOL[dtype]
+    c_ref, l_ref, _ = sc.project_poly(mu, W)
+    assert scale_rel_err(counts.cpu().numpy(), c_ref) < TOL[dtype]
+    # (case 33-1-7-3-4: the four rows pass above and below the 1 mm slab -- all air, log = 0 to float rounding)
+    assert np.max(np.abs(logs.cpu().numpy() - l_ref)) < (1e-9 if dtype == F64 else 3e-5) * max(1.0, np.abs(l_ref).max())
