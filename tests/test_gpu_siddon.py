@@ -368,7 +368,7 @@ def test_rectangular_volumes_and_anisotropic_voxels(dtype, shape, voxel, n_rows)
 
 
 @pytest.mark.parametrize('dtype', [F32, F64])
-@pytest.mark.parametrize('n,nz,n_ch,n_views,n_rows,h_iso', [(1, 1, 1, 1, 1, 0.4), (2, 1, 3, 5, 1, 0.4), (33, 1, 7, 3, 4, 0.5),
+@pytest.mark.parametrize('n,nz,n_ch,n_views,n_rows,h_iso', [(1, 1, 1, 1, 1, 0.4), (2, 1, 3, 5, 1, 0.4), (33, 1, 7, 3, 4, 0.09),
                                                              (17, 3, 33, 2, 1, 0.4), (40, 5, 1, 9, 2, 0.3), (64, 2, 40, 6, 3, 0.2)])
 def test_tiny_and_lopsided_sizes(dtype, n, nz, n_ch, n_views, n_rows, h_iso):
     """One voxel, one ray, one view; a single slice under a multi-row detector (rays leave the slab through its faces);
@@ -382,5 +382,5 @@ def test_tiny_and_lopsided_sizes(dtype, n, nz, n_ch, n_views, n_rows, h_iso):
     assert scale_rel_err(L.cpu().numpy(), L_ref) < TOL[dtype]
     c_ref, l_ref, _ = sc.project_poly(mu, W)
     assert scale_rel_err(counts.cpu().numpy(), c_ref) < TOL[dtype]
-    # (case 33-1-7-3-4: the four rows pass above and below the 1 mm slab -- all air, log = 0 to float rounding)
+    # (absolute where the log sinogram is ~0: the outer rows of case 33-1-7-3-4 miss the 1 mm slab, the inner ones leave it half way)
     assert np.max(np.abs(logs.cpu().numpy() - l_ref)) < (1e-9 if dtype == F64 else 3e-5) * max(1.0, np.abs(l_ref).max())
