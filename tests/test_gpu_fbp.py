@@ -184,3 +184,29 @@ def test_c2_pipeline_get_sino_then_get_recon_recovers_the_phantom():
         ref += (qp[v][i0 + 1] + (u - fl) * (qp[v][i0 + 2] - qp[v][i0 + 1])) / (A * A + B * B)
     ref *= scan.dbeta
     assert np.max(np.abs(rec[252:260] - ref)) / np.max(np.abs(rec)) < 5e-5
+
+
+@pytest.mark.parametrize('dtype', [F32, F64])
+@pytest.mark.parametrize('n_rows', [1, 3, 9, 17, 30])
+def test_wide_fan_and_forced_kernel_variants(dtype, n_rows, monkeypatch):
+    """A 1.6 rad fan lies outside the range of the single-precision kernels' arctangent polynomial (|tan gamma| <= 0.85), so
+    every back-projection kernel runs its general variant; the one-line filter kernel and the smaller row blocks (tuning
+    knobs DEXCT_FBP_FILTER / DEXCT_FBP_RB) must reproduce the same image."""
+    fan, n_ch, n_views = 1.6, 181, 64
+    scan = make_scan(n_views, n_ch, fan, SID, SDD, n_rows=n_rows, h_iso=0.3, beta0=0.1)
+    beta = scan.beta0 + np.arange(n_views) * scan.dbeta
+    gam = scan.gamma0 + np.arange(n_ch) * scan.dgamma
+    r = np.random.default_rng(n_rows)
+    sino = np.stack([FO.disc_sinogram(beta, gam, SID, (2.0 - 0.3 * (k % 4), 1.0), 9.0 - (k % 3), 0.2)
+                     + 0.01 * r.standard_normal((n_views, n_ch)) for k in range(n_rows)], axis=1)
+    ref = FO.fbp_fan(sino, beta, scan.gamma0, scan.dgamma, scan.dbeta, SID, 44, 36.0, 0.8)
+    d = torch.as_tensor(sino, device='cuda')
+    got = fbp_fan(scan, d, 44, 36.0, 0.8, dtype=dtype)
+    assert scale_rel_err(got.cpu().numpy(), ref) < TOL[dtype]
+    for knob, values in (('DEXCT_FBP_FILTER', ['1']), ('DEXCT_FBP_RB', ['0', '8', '16'])):
+        for v in values:
+            monkeypatch.setenv(knob, v)
+            alt = fbp_fan(scan, d, 44, 36.0, 0.8, dtype=dtype)
+            monkeypatch.delenv(knob)
+            assert scale_rel_err(alt.cpu().numpy(), ref) < TOL[dtype], (knob, v)
+            assert scale_rel_err(alt.cpu().numpy(), got.cpu().numpy()) < (2e-6 if dtype == F32 else 1e-13), (knob, v)
