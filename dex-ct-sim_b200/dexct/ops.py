@@ -62,7 +62,9 @@ def _as_device(a, dtype, device):
 class Projector:
     """Owns the device copy of the label volume and the prepared workspace for one (scan, volume) pair."""
 
-    def __init__(self, scan: DexctScan, labels, voxel, device=None):
+    def __init__(self, scan: DexctScan, labels, voxel, device=None, max_label=None):
+        """``max_label``: the largest label value, if the caller already knows it (saves one reduction + synchronisation at
+        the first projection, which checks it against the number of rows of the attenuation table)."""
         N.require_device()
         self.device = torch.device('cuda', torch.cuda.current_device()) if device is None else torch.device(device)
         lab = labels if isinstance(labels, torch.Tensor) else torch.as_tensor(np.ascontiguousarray(labels, dtype=np.uint8))
@@ -81,9 +83,11 @@ class Projector:
             raise N.DexctError('invalid scan/volume sizes')
         self.workspace = torch.empty(nbytes, dtype=torch.uint8, device=self.device)
         self.prepare()
+        self._max_label = None if max_label is None else int(max_label)
 
     def prepare(self):
         """Re-run after the label tensor was modified in place."""
+        self._max_label = None
         with torch.cuda.device(self.device):
             N.check(N.lib().dexct_siddon_prepare(C.byref(self.scan), C.byref(self.vol), N.ptr(self.labels),
                                                  N.ptr(self.workspace), N.stream_ptr()))
@@ -117,6 +121,12 @@ class Projector:
             raise ValueError('mu must be [K, nE] and W [nSpec, nE] on the same energy grid')
         K, nE = mu.shape
         nS = W.shape[0]
+        # the kernels index their per-material accumulators with the label itself (include/dexct.h: labels >= K are a
+        # caller error), so a phantom that holds a label without a row in ``mu`` is refused here
+        if self._max_label is None:
+            self._max_label = int(self.labels.max())
+        if self._max_label >= K:
+            raise ValueError(f'the phantom holds label {self._max_label} but the attenuation table has only {K} rows')
         shape = (nS, view_count, s.n_rows, s.n_ch)
         if counts is None:
             counts = torch.empty(shape, dtype=td, device=self.device)

@@ -29,7 +29,10 @@ class _ScanState:
         labels, voxel = _labels_for(ct, phantom)
         scan = make_scan(ct.N_proj, ct.N_channels, ct.gamma_fan, ct.SID, ct.SDD, n_rows=ct.N_rows, h_iso=ct.h_iso,
                          rotation=ct.rotation, beta0=ct.beta0)
-        self.projector = Projector(scan, labels, voxel)
+        # host label arrays of moderate size: their maximum costs microseconds here and saves the projector a device
+        # reduction + synchronisation at its first projection
+        hint = int(labels.max()) if isinstance(labels, np.ndarray) and 0 < labels.nbytes <= (64 << 20) else None
+        self.projector = Projector(scan, labels, voxel, max_label=hint)
         self.L = None            # [views_local, n_rows, n_ch, K] on the device
         self.L_dtype = None
 

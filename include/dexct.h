@@ -97,7 +97,8 @@ int dexct_siddon_tables_host(const DexctScan *scan, const void *workspace, doubl
  *   counts   [nSpec][view_count][n_rows][n_ch]   sum_e W exp(-sum_m L_m mu_m)            (sino_raw)
  *   logs     same shape or NULL                   -ln(counts / sum_e W)                   (sino_log)
  *   L_out    [view_count][n_rows][n_ch][K] or NULL  per-material path length [cm]
- * K <= 256 (uint8 labels); labels >= K are a caller error (checked only in debug builds).                   */
+ * K <= 256 (uint8 labels); labels >= K are a caller error: the kernels index their accumulators with the label and do
+ * not check it (the Python binding does, once per prepared phantom: dexct.ops.Projector.project).               */
 int dexct_siddon_poly(const DexctScan *scan, const DexctVolume *vol, const void *workspace,
                       int32_t view_begin, int32_t view_count,
                       const void *mu_KxE, int32_t K, int32_t nE, const void *W_SxE, int32_t nSpec,

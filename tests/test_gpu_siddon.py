@@ -175,6 +175,16 @@ def test_argument_errors_are_reported():
         pj.project(big, np.ones((1, 300)), dtype=F64)
     L = N.lib()
     assert L.dexct_siddon_poly(None, None, None, 0, 0, None, 1, 1, None, 1, None, None, None, 0, None) == -1
+    # a label without a row in the attenuation table is refused (the kernels index their accumulators with the label)
+    pj.labels[0, 5, 5] = 9
+    pj.prepare()
+    with pytest.raises(ValueError, match='label 9'):
+        pj.project(mu, W)
+    mu10 = np.concatenate([mu, np.tile(mu[-1:], (6, 1))])
+    assert pj.project(mu10, W)[0].shape == (2, 36, 1, 120)
+    pj.labels[0, 5, 5] = 1
+    pj.prepare()
+    assert torch.isfinite(pj.project(mu, W)[0]).all()
 
 
 # ---- full-size properties ---------------------------------------------------------------------------------------
