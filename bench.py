@@ -274,20 +274,26 @@ def run_b200(args):
     # step.  'nccl': the same with three all-gathers and one all-reduce.
     pg = None
     collective = 'none'
+    esz = 4 if args.dtype == 'f32' else 8
+    slot_s, slot_b = 4 * nv * N_CH * esz, nv * N_CH * 2 * esz
     if ws > 1 and args.collective == 'peer':
+        from dexct.dist import all_agree
         from dexct.peer import PeerGroup
-        try:
+        try:                                                              # (a failure on one rank raises on all: peer.py)
             pg = PeerGroup()
-            collective = 'peer'
+            sbuf, bbuf = pg.alloc(ws * slot_s), pg.alloc(ws * slot_b)
         except Exception as exc:                                          # noqa: BLE001
+            print(f'bench.py: rank {rank}: peer memory unavailable ({exc})', file=sys.stderr)
+            sbuf = None
+        if not all_agree(pg is not None and sbuf is not None):            # belt and braces: all ranks take the same path
+            pg = None             # (not closed: closing is collective, and the ranks may not agree on what exists)
             if rank == 0:
-                print(f'bench.py: peer memory unavailable ({exc}); using NCCL all-gathers', file=sys.stderr)
+                print('bench.py: using NCCL all-gathers on every rank', file=sys.stderr)
+        else:
+            collective = 'peer'
     if ws > 1 and pg is None:
         collective = 'nccl'
-    esz = 4 if args.dtype == 'f32' else 8
     if pg is not None:
-        slot_s, slot_b = 4 * nv * N_CH * esz, nv * N_CH * 2 * esz
-        sbuf, bbuf = pg.alloc(ws * slot_s), pg.alloc(ws * slot_b)
         g_sino = sbuf.view(td, (ws, 4, nv, 1, N_CH))                      # [rank][counts lo, hi, logs lo, hi]
         g_basis = bbuf.view(td, (ws, nv, 1, N_CH, 2))
         counts, logs, basis = g_sino[rank, 0:2], g_sino[rank, 2:4], g_basis[rank]

@@ -26,6 +26,19 @@ def shard_range(n, rank, world_size):
     return begin, base + (1 if rank < extra else 0)
 
 
+def all_agree(flag, group=None):
+    """True only if ``flag`` is true on EVERY rank (one MIN all-reduce of a byte; plain ``bool(flag)`` without a process
+    group).  For set-up steps that may fail on one rank only -- mapping peer memory, say -- after which all ranks must take
+    the same fallback or the next collective hangs."""
+    rank, ws = world()
+    if ws == 1:
+        return bool(flag)
+    dev = torch.device('cuda', torch.cuda.current_device()) if dist.get_backend(group) == 'nccl' else torch.device('cpu')
+    t = torch.tensor([1 if flag else 0], dtype=torch.int32, device=dev)
+    dist.all_reduce(t, op=dist.ReduceOp.MIN, group=group)
+    return bool(int(t.item()))
+
+
 def shard_sizes(n, world_size):
     return [shard_range(n, r, world_size)[1] for r in range(world_size)]
 

@@ -10,11 +10,13 @@ used once per buffer, to exchange the 64-byte handles.
 from __future__ import annotations
 
 import ctypes as C
+import os
 
 import torch
 import torch.distributed as dist
 
 from . import _native as N
+from . import dist as ddist
 
 
 class _RawCuda:
@@ -29,29 +31,66 @@ class SymBuffer:
     in THIS process (``ptrs[rank]`` is the local one)."""
 
     def __init__(self, group, nbytes):
+        """Collective over the group.  A failure on ANY rank -- allocation, export, or mapping a peer's handle -- raises
+        DexctError on EVERY rank, after everything that did succeed was undone: the callers fall back together (bench.py:
+        NCCL all-gathers) instead of one rank waiting for the others in the next collective."""
         self.group = group
         self.nbytes = int(nbytes)
-        p = C.c_void_p()
-        N.check(N.lib().dexct_peer_alloc(self.nbytes, C.byref(p)))
-        self._own = p.value
+        self._own = None
         self._opened = []
-        handle = (C.c_ubyte * 64)()
-        N.check(N.lib().dexct_peer_export(C.c_void_p(self._own), handle))
-        handles = [None] * group.world_size
-        if group.world_size > 1:
-            dist.all_gather_object(handles, bytes(handle), group=group.group)
+        self.local = None
+        ws = group.world_size
+        err, mine = None, None
+        try:
+            if os.environ.get('DEXCT_PEER_FAIL') == f'alloc:{group.rank}':         # fault injection (tests/peer_worker.py)
+                raise N.DexctError('injected allocation failure')
+            p = C.c_void_p()
+            N.check(N.lib().dexct_peer_alloc(self.nbytes, C.byref(p)))
+            self._own = p.value
+            handle = (C.c_ubyte * 64)()
+            N.check(N.lib().dexct_peer_export(C.c_void_p(self._own), handle))
+            mine = bytes(handle)
+        except N.DexctError as exc:
+            err = exc
+        handles = [mine]
+        if ws > 1:
+            handles = [None] * ws
+            dist.all_gather_object(handles, mine, group=group.group)
+        failed = [r for r, h in enumerate(handles) if h is None]
+        if failed:
+            self._undo(collective=False)                   # nobody has mapped anything yet
+            raise N.DexctError(f'peer allocation of {self.nbytes} bytes failed on rank(s) {failed}'
+                               + (f': {err}' if err is not None else ''))
         self.ptrs = []
-        for r in range(group.world_size):
-            if r == group.rank:
-                self.ptrs.append(self._own)
-            else:
+        try:
+            for r in range(ws):
+                if r == group.rank:
+                    self.ptrs.append(self._own)
+                    continue
+                if os.environ.get('DEXCT_PEER_FAIL') == f'open:{group.rank}':
+                    raise N.DexctError('injected mapping failure')
                 q = C.c_void_p()
                 buf = (C.c_ubyte * 64).from_buffer_copy(handles[r])
                 N.check(N.lib().dexct_peer_open(buf, C.byref(q)))
                 self._opened.append(q.value)
                 self.ptrs.append(q.value)
+        except N.DexctError as exc:
+            err = exc
+        if ws > 1 and not ddist.all_agree(err is None, group=group.group):
+            self._undo(collective=True)
+            raise N.DexctError('peer memory could not be mapped on every rank' + (f': {err}' if err is not None else ''))
         self._raw = _RawCuda(self._own, self.nbytes)
         self.local = torch.as_tensor(self._raw, device=group.device)
+
+    def _undo(self, collective):
+        for q in self._opened:
+            N.lib().dexct_peer_close(C.c_void_p(q))
+        self._opened = []
+        if collective:
+            dist.barrier(group=self.group.group)           # nobody frees memory a peer still has mapped
+        if self._own is not None:
+            N.lib().dexct_peer_free(C.c_void_p(self._own))
+            self._own = None
 
     def view(self, dtype, shape):
         """This rank's copy as a tensor of ``dtype`` and ``shape`` (must fill the buffer exactly or less)."""

@@ -23,6 +23,20 @@ def main():
     dev = torch.device('cuda', rank % torch.cuda.device_count())
     torch.cuda.set_device(dev)
     dist.init_process_group('gloo', rank=rank, world_size=ws)
+    # ---- a set-up failure on ONE rank (injected: allocation on rank 0, mapping on the last rank) raises on ALL ranks, and
+    # what had succeeded is undone: the next group works
+    from dexct._native import DexctError
+    for fault in ('alloc:0', f'open:{ws - 1}'):
+        os.environ['DEXCT_PEER_FAIL'] = fault
+        try:
+            PeerGroup(timeout_s=10.0)
+        except DexctError as exc:
+            assert 'rank' in str(exc) or 'mapped' in str(exc), str(exc)
+        else:
+            raise AssertionError(f'rank {rank}: PeerGroup came up despite the injected fault {fault}')
+        finally:
+            del os.environ['DEXCT_PEER_FAIL']
+    assert ddist.all_agree(True) and not ddist.all_agree(rank != 0)
     pg = PeerGroup(timeout_s=10.0)
     assert pg.rank == rank and pg.world_size == ws
 

@@ -122,6 +122,8 @@ def _gloo_worker(rank, ws, port, n_views, q):
         # gather along a non-leading axis too ([nSpec, views, ch] layout)
         full2 = full.permute(1, 0, 2).contiguous()
         got2 = ddist.all_gather_views(full2[:, v0:v0 + nv].clone(), n_views, dim=1)
+        # a set-up step that failed on one rank only is seen by all of them
+        ok = ok and ddist.all_agree(True) and not ddist.all_agree(rank != 1) and not ddist.all_agree(False)
         q.put((rank, ok and torch.equal(got2, full2)))
     finally:
         dist.destroy_process_group()
@@ -140,6 +142,10 @@ def test_all_gather_views_gloo_world2(n_views):
     for p in procs:
         p.join(timeout=60)
     assert res == [(0, True), (1, True)]
+
+
+def test_all_agree_without_a_process_group():
+    assert ddist.all_agree(True) and not ddist.all_agree(False) and not ddist.all_agree(0)
 
 
 def test_spectral_tables_memo_follows_its_inputs():
