@@ -268,10 +268,11 @@ def run_b200(args):
     mus = torch.as_tensor(mus_h, dtype=td, device=dev)
     rays_local = nv * N_CH
     # N > 1: every rank ends the step holding the whole view-major sinograms.  'peer': the buffers are symmetric
-    # allocations mapped into every rank (dexct/peer.py); the projection writes its shard in place, a store kernel on a
-    # side stream copies it into the 7 other copies while the decomposition runs, the decomposition's epilogue stores each
-    # basis pixel into all copies, and the air maximum is exchanged through flags in peer memory -- no NCCL call in the
-    # step.  'nccl': the same with three all-gathers and one all-reduce.
+    # allocations mapped into every rank (dexct/peer.py); the projection writes its shard in place, the decomposition
+    # kernel carries that shard into the other ranks' copies while it iterates (DEXCT_PUSH=sm / dma: a store kernel or the
+    # copy engines on a side stream instead), its epilogue stores each basis pixel into all copies, and the air maximum is
+    # exchanged through flags in peer memory -- no NCCL call in the step.  'nccl': the same with three all-gathers and
+    # one all-reduce.
     pg = None
     collective = 'none'
     esz = 4 if args.dtype == 'f32' else 8
