@@ -105,3 +105,28 @@ def test_segment_count_matches_survey_probe():
     sc = oracle.Scan(lab, VOX, 60.0, 100.0, t)
     _, seg = sc.classic_lengths(1)
     assert 600 < seg / (8 * 900) < 660
+
+
+@pytest.mark.parametrize('shape,voxel,n_rows,K', [((1, 70, 120), (0.40, 0.55, 0.1), 1, 6), ((9, 120, 70), (0.55, 0.30, 0.7), 5, 6),
+                                                 ((14, 50, 131), (0.25, 0.62, 0.4), 6, 256)])
+def test_two_traversals_agree_on_rectangular_anisotropic_volumes(shape, voxel, n_rows, K):
+    """The checker's own consistency on the shapes tests/test_gpu_siddon.py uses for the device: nx != ny, dx != dy != dz and the
+    full uint8 label range.  Siddon 1985 (A) and the slab traversal (B) give the same lengths, total = chord of the box."""
+    nz, ny, nx = shape
+    r = np.random.default_rng(nx * 1000 + ny)
+    lab = r.integers(0, K, shape).astype(np.uint8)
+    t = oracle.fan_tables(140, 30, 0.8230337, N_rows=n_rows, h_iso=0.35, SID=60.0, SDD=100.0)
+    sc = oracle.Scan(lab, voxel, 60.0, 100.0, t)
+    L, seg = sc.classic_lengths(K)
+    assert seg > 0 and L.shape[-1] == K
+    L64 = sc.slab_lengths(K, f64=True)
+    assert np.max(np.abs(L64 - L)) < 1e-10
+    assert np.max(np.abs(sc.slab_lengths(K, f64=False) - L)) < 2e-5 * L.sum(-1).max()
+    half = np.array([nx * voxel[0], ny * voxel[1], nz * voxel[2]]) / 2
+    for v, row, c in [(0, 0, 0), (7, n_rows - 1, 70), (29, n_rows // 2, 139), (13, 0, 33)]:
+        S_, T_ = sc.endpoints(v, row, c)
+        d = T_ - S_
+        with np.errstate(divide='ignore', invalid='ignore'):
+            t1, t2 = (-half - S_) / d, (half - S_) / d
+        lo, hi = np.nanmax(np.minimum(t1, t2)).clip(0, 1), np.nanmin(np.maximum(t1, t2)).clip(0, 1)
+        assert abs(L[v, row, c].sum() - max(hi - lo, 0.0) * np.linalg.norm(d)) < 1e-9
