@@ -1,24 +1,28 @@
 #!/usr/bin/env python3
 """Benchmark of the hot path: Siddon polyenergetic forward projection + Gauss-Newton two-basis decomposition.
 
-    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl b200|reference]
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl b200|reference] [--config C5|C4|C2]
     python -m torch.distributed.run --nnodes=1 --nproc-per-node N ... bench.py --gpus N ...
 
-Workload (BASELINE.json configs[1], "C2"): synthetic 512x512 single-slice phantom, 900 channels x 1000 views, 120 energy
-bins, dual-spectrum sinograms (both spectra in ONE traversal) followed by the GN decomposition of every sinogram pixel
-(10 iterations, the fixed count configs[2] names).  One step = one whole scan: 900 000 rays -> 2 count sinograms ->
-900 000 decomposed pixel pairs.  Unit = rays (= pixels) per second through the whole path.
+Headline workload (BASELINE.json configs[4], "C5" -- the largest configuration that fits one GPU): synthetic 1024^3
+phantom, 128 detector rows x 1800 channels x 2400 views, 150 energy bins, both spectra in ONE traversal, followed by the GN
+decomposition of every sinogram pixel (10 iterations, the fixed count configs[2] names).  One step = one whole scan:
+552 960 000 rays -> 2 count + 2 log sinograms -> 552 960 000 decomposed pixel pairs.  Unit = rays (= pixels) per second
+through projection + decomposition.  The FBP stage of configs[4] ("simulate -> decompose -> FBP") is timed beside it under
+`extra.c5_pipeline`, the full 1200-view C4 scan under `extra.c4`, and round 1's headline (C2, weak scaling) under `extra.c2`.
 
-N > 1 (weak scaling): the scan has N x 1000 views; rank r owns the contiguous view range [1000 r, 1000 (r+1)), traces and
-decomposes it without communication, and the view-major sinograms are assembled with one NCCL all-gather per array.
+N > 1 (STRONG scaling, as configs[4] says "at 1/2/4/8 GPUs"): the 2400 views are split over the ranks; rank r traces and
+decomposes its own contiguous view range without communication, and every rank ends the step holding the whole view-major
+sinograms (north_star: "assembled with all-gather"): through peer memory (CUDA IPC over NVLink) -- small shards ride inside
+the decomposition kernel (`fused`), large ones go out on the copy engines beside it (`dma`) -- or NCCL (`--collective nccl`).
 
 `value`   : device throughput, inputs resident in HBM, CUDA events around every step, max over ranks.
-`e2e`     : the same work through the reference-facing Python entry points (get_sino x2 / get_basismat_sinos) with host
+`e2e`     : the same work through the reference-facing Python entry points (get_sinos / get_basismat_sinos) with host
             numpy arrays in and out; every step uploads the phantom again and reads the results back.
-`roofline`: the Siddon kernel against the bytes-per-ray HBM roofline of SURVEY.md section 8(d); `roofline_gn`: the GN kernel
-            against the FP32 FMA pipe.
+`roofline`: the 3-D Siddon kernel against the bytes-per-ray HBM roofline of SURVEY.md section 8(d); `roofline_gn`: the GN
+            kernel against the FP32 FMA pipe.
 `cpu_baseline` / `--impl reference`: the CPU oracle (oracle/: C restatement of Siddon 1985 with OpenMP + the numpy
-            restatement of the reference's optimize_sino_cpu, one process per core) on a bounded sample of the same scan.
+            restatement of the reference's optimize_sino_cpu, one process per core) on a bounded view sample of the SAME scan.
 """
 import argparse
 import json
@@ -35,86 +39,144 @@ for _p in (ROOT, PKG):
 
 import numpy as np  # noqa: E402
 
-VIEWS_PER_GPU = 1000
-N_CH = 900
 GN_ITERS = 10
 MASK_THRESH = 0.95
 METRIC = 'siddon_poly_gn_rays_per_s'
 UNIT = 'rays/s'
-WORKLOAD = ('C2: 512x512x1 phantom (K=8 materials), 900 ch x 1000 views per GPU, 120 energy bins, 2 spectra fused, '
-            'GN 10 iters water/bone, air mask 0.95')
+HEADLINE = 'C5'
 
+WORKLOADS = {
+    'C5': 'C5: 1024x1024x1024 phantom (K=8 materials), 128 rows x 1800 ch x 2400 views, 150 energy bins, 2 spectra fused, '
+          'GN 10 iters tissue/bone, air mask 0.95',
+    'C4': 'C4: 512x512x512 phantom (K=8 materials), 64 rows x 900 ch x 1200 views, 120 energy bins, 2 spectra fused, '
+          'GN 10 iters tissue/bone, air mask 0.95',
+    'C2': 'C2: 512x512x1 phantom (K=8 materials), 900 ch x 1000 views per GPU, 120 energy bins, 2 spectra fused, '
+          'GN 10 iters tissue/bone, air mask 0.95',
+}
+SCALING = {'C5': 'strong', 'C4': 'strong', 'C2': 'weak'}
 
-# N > 1: how the finished count/log shard reaches the peers' copies.  'fused' (default): the decomposition kernel's own
-# threads copy it, a slice per Newton iteration (dexct_gn_decompose_fused_push) -- spread over all SMs and over the kernel's
-# run time.  'sm': a separate store kernel on DEXCT_PUSH_CTAS CTAs on a side stream; 'dma': seven copy-engine transfers.
-# Measured at N = 8 (profiles/r01h_scaling.txt): sm/16 CTAs 0.855 ms per step, 48 CTAs 0.876, 148 CTAs 0.920, dma 0.905,
-# NCCL all-gathers 1.195.
-PUSH_MODE = os.environ.get('DEXCT_PUSH', 'fused')
+# N > 1: how a finished shard reaches the peers' copies.  'fused': the decomposition kernel's own threads copy the count/log
+# shard, a slice per Newton iteration, and its epilogue stores every basis pixel into all copies -- no extra launch, the
+# choice for steps of ~1 ms (C2: profiles/r01h_scaling.txt).  'dma': the copy engines carry the count/log shard beside the
+# decomposition, which runs in view chunks whose basis pixels follow on the copy engines as they finish -- no SM time, the
+# choice for GB-sized shards (C5 at N = 8: the rider stretched the GN kernel from 52 to 72 ms, profiles/r01k_configs_n8.jsonl).
+# 'auto' picks by shard size.  'sm': a separate store kernel on a side stream (kept for comparison).
+PUSH_MODE = os.environ.get('DEXCT_PUSH', 'auto')
 PUSH_CTAS = int(os.environ.get('DEXCT_PUSH_CTAS', '16'))
+DMA_THRESHOLD = int(os.environ.get('DEXCT_DMA_THRESHOLD', str(64 << 20)))     # count/log shard bytes
+GN_CHUNKS = int(os.environ.get('DEXCT_GN_CHUNKS', '4'))
 
 
 def parse():
     ap = argparse.ArgumentParser()
     ap.add_argument('--gpus', type=int, default=1)
-    ap.add_argument('--steps', type=int, default=200)
-    ap.add_argument('--warmup', type=int, default=5)
+    ap.add_argument('--steps', type=int, default=5)
+    ap.add_argument('--warmup', type=int, default=3)
     ap.add_argument('--impl', default='b200', choices=['b200', 'reference'])
+    ap.add_argument('--config', default=HEADLINE, choices=sorted(WORKLOADS))
     ap.add_argument('--dtype', default='f32', choices=['f32', 'f64'])
     ap.add_argument('--cpu-views', type=int, default=0, help='views in the CPU sample (0 = auto)')
     ap.add_argument('--no-cpu-baseline', action='store_true')
     ap.add_argument('--no-e2e', action='store_true')
-    ap.add_argument('--no-extra', action='store_true', help='skip the secondary measurements (3-D projector, FBP)')
+    ap.add_argument('--no-extra', action='store_true', help='skip the secondary measurements (C5 pipeline with FBP, C4, C2)')
     ap.add_argument('--collective', default='peer', choices=['peer', 'nccl'],
                     help='N > 1: assemble the sinograms by stores into peer memory (default) or by NCCL all-gathers')
     return ap.parse_args()
 
 
+def config_dict(name, ws):
+    """`config` of the JSON line -- the same for both arms, so that the driver compares like with like."""
+    from dexct import synthetic as S
+    c = S.CONFIGS[name]
+    views = c['n_views'] * (ws if SCALING[name] == 'weak' else 1)
+    return {'workload': WORKLOADS[name], 'views_total': views, 'rays_per_step': views * c['n_rows'] * c['n_ch'],
+            'gn_iters': GN_ITERS, 'parallelism': f'view-sharded x{ws}',
+            'l2': 'flushed between timed steps (256 MiB write)' if name == 'C2'
+                  else 'inputs and outputs of a step (GBs) are far larger than the 126 MB L2'}
+
+
+def load_peaks():
+    try:
+        return json.load(open(os.path.join(ROOT, 'MEASURED_PEAKS.json')))
+    except Exception:                                                     # noqa: BLE001
+        return {}
+
+
 # ----------------------------------------------------------------------------------------------------------------
 # CPU arm (oracle).  Used for `cpu_baseline` and `--impl reference`.
 
-def _gn_view_job(args):
+def _gn_job(args):
     from oracle import gn_oracle
-    g, i0, mus, n_iters = args
+    g, i0, mus, n_iters = args                                            # g [2, 1, n_ch]: one detector line
     nB = g.shape[2]
     i0_t = np.tile(i0, (1, nB)).reshape(2, nB, i0.shape[1])
     return gn_oracle.optimize_sino_cpu(g, None, i0_t, mus, n_iters)
 
 
+def _worker_init():
+    os.environ['OMP_NUM_THREADS'] = '1'
+    try:                                                                   # numpy's BLAS/OpenMP pools, if already loaded
+        import threadpoolctl
+        threadpoolctl.threadpool_limits(1)
+    except Exception:                                                     # noqa: BLE001
+        pass
+
+
 class CpuArm:
     """The oracle's CPU implementation of one bounded sample of the workload: `n_views` views spread evenly over the
-    rotation; Siddon + detection in C with OpenMP over all host threads, GN in numpy with one worker process per core."""
+    rotation, all detector rows and channels; Siddon + detection in C with OpenMP over all host threads, GN in numpy with
+    one worker process per core (one detector line per job)."""
 
-    def __init__(self, n_views):
+    def __init__(self, name, n_views):
         import multiprocessing as mp
+        self.cores = os.cpu_count() or 1
+        # a launcher may have exported OMP_NUM_THREADS=1 (torchrun does): the C oracle would then trace on ONE thread and
+        # every ratio against it would be inflated (round 1, SCALE N >= 2).  Ask for all cores, and check below.
+        os.environ['OMP_NUM_THREADS'] = str(self.cores)
         import oracle
         from oracle import gn_oracle
         from dexct import synthetic as S
         from xtomosim.forward_project import spectral_weights
         oracle.build()
-        self.oracle = oracle
-        ct, ph, lo, hi = S.make_config('C2', n_views=VIEWS_PER_GPU)
+        oracle.set_num_threads(self.cores)
+        self.threads = oracle.num_threads()
+        if self.threads < self.cores:
+            print(f'bench.py: WARNING: the C oracle runs on {self.threads} of {self.cores} cores', file=sys.stderr)
+        self.name = name
+        c = S.CONFIGS[name]
+        self.full_views = c['n_views']
+        dev = None
+        try:                                     # input generation only: the 1024^3 labels take minutes in numpy
+            import torch
+            dev = 'cuda' if torch.cuda.is_available() else ('cpu' if c['nz'] > 1 else None)
+        except Exception:                                                 # noqa: BLE001
+            pass
+        ct, ph, lo, hi = S.make_config(name, device=dev)
+        labels = ph.M.cpu().numpy() if dev is not None else ph.M
         tabs = oracle.fan_tables(ct.N_channels, ct.N_proj, ct.gamma_fan, ct.rotation, ct.beta0, ct.N_rows, ct.h_iso, ct.SID, ct.SDD)
         pick = np.linspace(0, ct.N_proj, n_views, endpoint=False).astype(int)
         tabs = {k: (v[pick] if k.endswith('beta') else v) for k, v in tabs.items()}
-        self.scan = oracle.Scan(ph.M, (ph.dx, ph.dy, ph.dz), ct.SID, ct.SDD, tabs)
+        self.scan = oracle.Scan(labels, (ph.dx, ph.dy, ph.dz), ct.SID, ct.SDD, tabs)
         self.mu = ph.mu_table(lo.E)
         self.W = np.stack([spectral_weights(ct, lo), spectral_weights(ct, hi)])
         import matdecomp
         _, self.i0, self.mus = gn_oracle.gn_model_tables(ct, lo, hi, matdecomp.xc.mixatten)
         self.n_views = n_views
-        self.cores = os.cpu_count() or 1
-        self.threads = oracle.num_threads()
+        self.n_rows, self.n_ch = ct.N_rows, ct.N_channels
+        self.rays = n_views * ct.N_rows * ct.N_channels
         self.pool = mp.get_context('spawn').Pool(self.cores, initializer=_worker_init) if self.cores > 1 else None
+        if self.pool:                                                      # workers imported and warm before the clock starts
+            self.pool.map(_gn_job, [(np.ones((2, 1, 4)), self.i0, self.mus, 1)] * self.cores, chunksize=1)
         self.seg_per_ray = None
 
     def step(self):
-        counts, _, seg = self.scan.project_poly(self.mu, self.W, want_log=True)
-        self.seg_per_ray = seg / (self.n_views * N_CH)
-        g = counts[:, :, 0, :]                                            # [2, views, ch]
+        counts, _, seg = self.scan.project_poly(self.mu, self.W, want_log=True)     # [2, views, rows, ch]
+        self.seg_per_ray = seg / self.rays
+        g = counts.reshape(2, -1, self.n_ch)                                          # [2, views * rows, ch]
         mask = g[0] >= MASK_THRESH * g[0].max()
-        jobs = [(g[:, v:v + 1], self.i0, self.mus, GN_ITERS) for v in range(self.n_views)]
-        outs = self.pool.map(_gn_view_job, jobs, chunksize=1) if self.pool else [_gn_view_job(j) for j in jobs]
+        jobs = [(g[:, ln:ln + 1], self.i0, self.mus, GN_ITERS) for ln in range(g.shape[1])]
+        outs = self.pool.map(_gn_job, jobs, chunksize=max(1, len(jobs) // (8 * self.cores))) if self.pool \
+            else [_gn_job(j) for j in jobs]
         a = np.concatenate(outs, axis=0)
         a[mask] = 0
         return a
@@ -125,42 +187,46 @@ class CpuArm:
             self.pool.join()
 
     def describe(self, value):
-        return {'value': value, 'unit': UNIT, 'cores': self.cores, 'kind': 'port',
-                'sample': f'{self.n_views} of {VIEWS_PER_GPU} views of the C2 scan, evenly spaced ({self.n_views * N_CH} rays): '
-                          f'oracle/siddon_oracle.c float64 Siddon 1985 + Beer-Lambert (OpenMP, {self.threads} threads) then '
-                          f'oracle/gn_oracle.py optimize_sino_cpu float64 numpy ({GN_ITERS} iters, {self.cores} worker processes)'}
+        return {'value': value, 'unit': UNIT, 'cores': self.cores, 'threads_used': self.threads, 'kind': 'port',
+                'sample': f'{self.n_views} of {self.full_views} views of the {self.name} scan, evenly spaced, all rows and channels '
+                          f'({self.rays} rays): oracle/siddon_oracle.c float64 Siddon 1985 + Beer-Lambert (OpenMP, {self.threads} '
+                          f'threads) then oracle/gn_oracle.py optimize_sino_cpu float64 numpy ({GN_ITERS} iters, {self.cores} worker '
+                          f'processes, one detector line per job)'}
 
 
-def auto_cpu_views():
-    # ~80 ms per view and core for the numpy Newton loop at 900 x 120 x 10: 24 views per core
-    # make a step of about 2-3 s
-    return int(min(VIEWS_PER_GPU, 24 * (os.cpu_count() or 1)))
-
-
-def _worker_init():
-    os.environ['OMP_NUM_THREADS'] = '1'
+def auto_cpu_views(name):
+    """A sample that keeps the host cores busy for roughly 10-20 s: the numpy Newton loop costs ~80 ms per 900 pixels x 120
+    bins x 10 iterations and core, the C tracer a third of that."""
+    from dexct import synthetic as S
+    c = S.CONFIGS[name]
+    cores = os.cpu_count() or 1
+    per_view_core_s = 0.080 * (c['n_rows'] * c['n_ch'] / 900.0) * (c['n_bins'] / 120.0)
+    return int(min(c['n_views'], max(1, round(10.0 * cores / per_view_core_s))))
 
 
 def run_reference(args):
     rank = int(os.environ.get('RANK', '0'))
     if rank != 0:
         return
-    arm = CpuArm(args.cpu_views or auto_cpu_views())
-    for _ in range(min(args.warmup, 1)):
+    ws = int(os.environ.get('WORLD_SIZE', '1'))
+    arm = CpuArm(args.config, args.cpu_views or auto_cpu_views(args.config))
+    n_warm = min(args.warmup, 1)
+    for _ in range(n_warm):
         arm.step()
     t = []
-    for _ in range(max(1, min(args.steps, 5))):
+    for _ in range(max(1, min(args.steps, 3))):
         t0 = time.perf_counter()
         arm.step()
         t.append(time.perf_counter() - t0)
     arm.close()
     steps = len(t)
     ms = 1e3 * sum(t) / steps
-    value = arm.n_views * N_CH / (ms * 1e-3)
+    value = arm.rays / (ms * 1e-3)
     line = {'impl': 'reference', 'metric': METRIC, 'value': value, 'unit': UNIT, 'n_gpus': args.gpus, 'steps': steps,
-            'warmup': min(args.warmup, 1), 'ms_per_step': ms, 'higher_is_better': True, 'scaling': 'weak',
+            'warmup': n_warm, 'ms_per_step': ms, 'higher_is_better': True, 'scaling': SCALING[args.config],
             'vs_baseline': None, 'dtype': 'f64', 'data': 'synthetic',
-            'config': {'workload': WORKLOAD, 'step': 'bounded sample: see cpu_baseline.sample'},
+            'config': config_dict(args.config, ws),
+            'step': 'bounded sample of the config: see cpu_baseline.sample',
             'cpu_baseline': arm.describe(value),
             'e2e': {'value': value, 'unit': UNIT, 'h2d_bytes_per_step': 0, 'd2h_bytes_per_step': 0},
             'gpu_launches': 0}
@@ -230,16 +296,433 @@ class ClockSampler(threading.Thread):
 # ----------------------------------------------------------------------------------------------------------------
 # B200 arm
 
+class ScanBench:
+    """One configuration on this rank's view range: resident inputs, output buffers (symmetric peer allocations at N > 1),
+    and `step()` = projection of both spectra + decomposition + assembly of the sinograms on every rank."""
+
+    def __init__(self, name, dev, rank, ws, dtype='f32', collective='peer', with_fbp=False, assemble=True):
+        import torch
+        import torch.distributed as dist
+        from dexct import dist as ddist
+        from dexct import synthetic as S
+        from dexct.ops import Projector, dtype_code, make_scan
+        from xtomosim import forward_project as FP
+        import matdecomp
+        self.torch, self.dist = torch, dist
+        self.name, self.dev, self.rank, self.ws = name, dev, rank, ws
+        self.scaling = SCALING[name]
+        self.code = dtype_code(dtype)
+        self.td = td = torch.float32 if dtype == 'f32' else torch.float64
+        self.esz = esz = 4 if dtype == 'f32' else 8
+        c = S.CONFIGS[name]
+        self.n_views = c['n_views'] * (ws if self.scaling == 'weak' else 1)
+        on_dev = c['nz'] > 1                                     # large volumes are rasterised on the device
+        ct, ph, lo, hi = S.make_config(name, n_views=self.n_views, device=dev if on_dev else None)
+        self.ct, self.ph, self.lo, self.hi = ct, ph, lo, hi
+        self.v0, self.nv = ddist.shard_range(self.n_views, rank, ws)
+        self.R, self.C = ct.N_rows, ct.N_channels
+        self.scan = make_scan(ct.N_proj, ct.N_channels, ct.gamma_fan, ct.SID, ct.SDD, n_rows=ct.N_rows, h_iso=ct.h_iso,
+                              rotation=ct.rotation)
+        self.pj = Projector(self.scan, ph.M, (ph.dx, ph.dy, ph.dz), device=dev)
+        self.mu = torch.as_tensor(ph.mu_table(lo.E), dtype=td, device=dev)
+        self.W = torch.as_tensor(np.stack([FP.spectral_weights(ct, lo), FP.spectral_weights(ct, hi)]), dtype=td, device=dev)
+        _, i0_h, mus_h = matdecomp.spectral_tables(ct, lo, hi)
+        self.i0 = torch.as_tensor(i0_h, dtype=td, device=dev)
+        self.mus = torch.as_tensor(mus_h, dtype=td, device=dev)
+        self.nE = int(self.i0.shape[1])
+        self.rays_local = self.nv * self.R * self.C
+        self.rays_total = self.n_views * self.R * self.C
+        nv, R, Cn = self.nv, self.R, self.C
+        even = self.n_views % ws == 0
+        self.pg = None
+        self.collective = 'none'
+        self.push_mode = None
+        self.launches = 0
+        slot_s, slot_b = 4 * nv * R * Cn * esz, nv * R * Cn * 2 * esz
+        self.slot_s, self.slot_b = slot_s, slot_b
+        if ws > 1 and collective == 'peer' and even:
+            from dexct.dist import all_agree
+            from dexct.peer import PeerGroup
+            sbuf = None
+            try:                                                          # (a failure on one rank raises on all: peer.py)
+                self.pg = PeerGroup()
+                sbuf, bbuf = self.pg.alloc(ws * slot_s), self.pg.alloc(ws * slot_b)
+            except Exception as exc:                                      # noqa: BLE001
+                print(f'bench.py: rank {rank}: peer memory unavailable ({exc})', file=sys.stderr)
+                sbuf = None
+            if not all_agree(self.pg is not None and sbuf is not None):   # belt and braces: all ranks take the same path
+                self.pg = None        # (not closed: closing is collective, and the ranks may not agree on what exists)
+                if rank == 0:
+                    print('bench.py: using NCCL all-gathers on every rank', file=sys.stderr)
+            else:
+                self.collective = 'peer'
+                self.sbuf, self.bbuf = sbuf, bbuf
+        if ws > 1 and self.pg is None:
+            self.collective = 'nccl'
+        if self.pg is not None:
+            self.g_sino = self.sbuf.view(td, (ws, 4, nv, R, Cn))             # [rank][counts lo, hi, logs lo, hi]
+            self.g_basis = self.bbuf.view(td, (ws, nv, R, Cn, 2))
+            self.counts, self.logs, self.basis = self.g_sino[rank, 0:2], self.g_sino[rank, 2:4], self.g_basis[rank]
+            self.mirrors = self.bbuf.table(rank * slot_b, exclude_self=True)
+            self.push_table = self.sbuf.table(rank * slot_s, exclude_self=True)
+            mode = PUSH_MODE
+            if mode == 'auto':
+                mode = 'dma' if slot_s > DMA_THRESHOLD else 'fused'
+            self.push_mode = mode
+            self.side = [torch.cuda.Stream(device=dev) for _ in range(4)]
+        else:
+            self.counts = torch.empty((2, nv, R, Cn), dtype=td, device=dev)
+            self.logs = torch.empty_like(self.counts)
+            self.basis = torch.empty((nv, R, Cn, 2), dtype=td, device=dev)
+            if ws > 1 and even and assemble:
+                self.g_counts = torch.empty((ws, 2, nv, R, Cn), dtype=td, device=dev)
+                self.g_logs = torch.empty_like(self.g_counts)
+                self.g_basis = torch.empty((ws, nv, R, Cn, 2), dtype=td, device=dev)
+            self.even = even and assemble
+        self.flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev) if name == 'C2' else None
+        self.with_fbp = with_fbp
+        if with_fbp:
+            self.n_matrix, self.fov, self.ramp = ph.Nx, ph.Nx * ph.dx, 0.8
+            self.images = [torch.empty((R, self.n_matrix, self.n_matrix), dtype=td, device=dev) for _ in range(4)]
+            if ws > 1 and R % ws == 0:
+                self.slabs = [torch.empty((R // ws, self.n_matrix, self.n_matrix), dtype=td, device=dev) for _ in range(4)]
+
+    # ---- peer-memory pushes on the copy engines: one DMA per destination, destinations taken in ring order from this
+    # rank's neighbour (so that the ranks do not all write to rank 0 first), spread over four side streams
+    def _dma_push(self, buf, offset_bytes, src):
+        torch = self.torch
+        main = torch.cuda.current_stream()
+        nb = src.numel() * src.element_size()
+        import ctypes as C
+        from dexct import _native as N
+        for k in range(1, self.ws):
+            r = (self.rank + k) % self.ws
+            st = self.side[(k - 1) % len(self.side)]
+            st.wait_stream(main)
+            with torch.cuda.stream(st):
+                tab = (C.c_void_p * 1)(buf.ptrs[r] + int(offset_bytes))
+                N.check(N.lib().dexct_peer_push_dma(N.ptr(src), nb, tab, 1, -1, N.stream_ptr()))
+
+    def _join_sides(self):
+        main = self.torch.cuda.current_stream()
+        for st in self.side:
+            main.wait_stream(st)
+
+    def step(self, t=None):
+        """t: four CUDA events (start, after projection, after decomposition, end) or None."""
+        torch, dist = self.torch, self.dist
+        from dexct.ops import gn_air_key, gn_decompose
+        rank, ws, pg, code = self.rank, self.ws, self.pg, self.code
+        counts, logs, basis = self.counts, self.logs, self.basis
+        if t is not None:
+            t[0].record()
+        self.pj.project(self.mu, self.W, view_begin=self.v0, view_count=self.nv, dtype=code, want_log=True, counts=counts, logs=logs)
+        n = 1                                                             # siddon kernel
+        if t is not None:
+            t[1].record()
+        if pg is not None and self.push_mode == 'dma':
+            # count/log shard: seven DMAs beside the decomposition.  Decomposition: GN_CHUNKS view ranges against the air
+            # threshold of the whole sinogram; each finished range of basis pixels follows on the copy engines.
+            self._dma_push(self.sbuf, rank * self.slot_s, self.g_sino[rank])
+            key = gn_air_key(counts[0], dtype=code, reduce_max_over_ranks=True, peers=pg)
+            n += 2                                                        # gn_max + peer_max
+            nch = max(1, min(GN_CHUNKS, self.nv))
+            bounds = [self.nv * k // nch for k in range(nch + 1)]
+            per_view = self.R * self.C * 2 * self.esz
+            for a, b in zip(bounds[:-1], bounds[1:]):
+                gn_decompose(counts[:, a:b].reshape(2, -1), self.i0, self.mus, GN_ITERS, mask_thresh=MASK_THRESH, dtype=code,
+                             out=basis[a:b].view(-1, 2), air_key=key)
+                n += 4                                                    # strided gather copy, gn_table, gn_kernel, gn_fixup
+                self._dma_push(self.bbuf, rank * self.slot_b + a * per_view, basis[a:b])
+            if t is not None:
+                t[2].record()
+            self._join_sides()
+            pg.barrier()                                                  # every rank's stores have landed in every copy
+            n += 1
+        elif pg is not None and self.push_mode == 'fused':
+            # one kernel: Newton iterations + the copy of the count/log shard into the peers, a slice per Newton iteration
+            gn_decompose(counts.reshape(2, -1), self.i0, self.mus, GN_ITERS, mask_thresh=MASK_THRESH, dtype=code, out=basis.view(-1, 2),
+                         reduce_max_over_ranks=True, peers=pg, mirrors=self.mirrors, push=(self.g_sino[rank], self.push_table))
+            if t is not None:
+                t[2].record()
+            pg.barrier()
+            n += 6                                                        # gn_max, peer_max, gn_table, gn_kernel, gn_fixup, barrier
+        elif pg is not None:                                              # 'sm': store kernel on a side stream
+            main = torch.cuda.current_stream()
+            self.side[0].wait_stream(main)
+            with torch.cuda.stream(self.side[0]):
+                pg.push(self.g_sino[rank], self.sbuf, rank * self.slot_s, dma=False, max_ctas=PUSH_CTAS)
+            gn_decompose(counts.reshape(2, -1), self.i0, self.mus, GN_ITERS, mask_thresh=MASK_THRESH, dtype=code, out=basis.view(-1, 2),
+                         reduce_max_over_ranks=True, peers=pg, mirrors=self.mirrors)
+            if t is not None:
+                t[2].record()
+            main.wait_stream(self.side[0])
+            pg.barrier()
+            n += 7
+        else:
+            pending = []
+            if ws > 1 and self.even:
+                # the sinogram gathers ride NCCL's stream behind the projection and overlap the decomposition, which only
+                # needs the local view shard
+                pending.append(dist.all_gather_into_tensor(self.g_counts, counts, async_op=True))
+                pending.append(dist.all_gather_into_tensor(self.g_logs, logs, async_op=True))
+            gn_decompose(counts.view(2, -1), self.i0, self.mus, GN_ITERS, mask_thresh=MASK_THRESH, dtype=code, out=basis.view(-1, 2),
+                         reduce_max_over_ranks=ws > 1)
+            n += 4                                                        # gn_max, gn_table, gn_kernel, gn_fixup
+            if t is not None:
+                t[2].record()
+            if ws > 1 and self.even:
+                pending.append(dist.all_gather_into_tensor(self.g_basis, basis, async_op=True))
+                for w in pending:
+                    w.wait()
+        if t is not None:
+            t[3].record()
+        self.launches += n
+
+    def pipeline_step(self, marks):
+        """configs[4]'s whole pipeline (/root/reference/main.py:109-168) on this rank's view range: projection, FBP of both
+        log sinograms, decomposition, FBP of both basis sinograms.  View-sharded FBP needs no assembled sinogram, so nothing
+        is replicated; the partial volumes are summed into row slabs (one reduce-scatter per volume, each rank ends with
+        R / N detector rows of every image).  Slice-by-slice fan-beam FBP: a throughput figure for multi-row scans, not a
+        cone-beam (FDK) reconstruction off the mid-plane."""
+        torch, dist = self.torch, self.dist
+        from dexct.ops import fbp_fan, gn_decompose
+        ev = lambda: torch.cuda.Event(enable_timing=True)                 # noqa: E731
+        m = [ev() for _ in range(6)]
+        m[0].record()
+        self.pj.project(self.mu, self.W, view_begin=self.v0, view_count=self.nv, dtype=self.code, counts=self.counts, logs=self.logs)
+        m[1].record()
+        for s in range(2):
+            fbp_fan(self.scan, self.logs[s], self.n_matrix, self.fov, self.ramp, view_begin=self.v0, dtype=self.code, image=self.images[s])
+        m[2].record()
+        gn_decompose(self.counts.reshape(2, -1), self.i0, self.mus, GN_ITERS, mask_thresh=MASK_THRESH, dtype=self.code,
+                     out=self.basis.view(-1, 2), reduce_max_over_ranks=self.ws > 1, peers=self.pg)
+        m[3].record()
+        for q in range(2):
+            fbp_fan(self.scan, self.basis[..., q].contiguous(), self.n_matrix, self.fov, self.ramp, view_begin=self.v0, dtype=self.code,
+                    image=self.images[2 + q])
+        m[4].record()
+        if self.ws > 1:
+            for k, im in enumerate(self.images):
+                if hasattr(self, 'slabs'):
+                    dist.reduce_scatter_tensor(self.slabs[k], im)
+                else:
+                    dist.all_reduce(im)
+        m[5].record()
+        marks.append(m)
+
+    def barrier(self):
+        if self.ws > 1:
+            self.dist.barrier()
+        self.torch.cuda.synchronize()
+
+    def run(self, steps, warmup):
+        """Timed steps; returns {'total', 'siddon', 'gn'} in ms per step, max over ranks."""
+        torch, dist = self.torch, self.dist
+        for _ in range(warmup):
+            if self.flush is not None:
+                self.flush.zero_()
+            self.step()
+        self.barrier()
+        self.launches = 0
+        marks = []
+        self.barrier()
+        for _ in range(steps):
+            if self.flush is not None:
+                self.flush.zero_()
+            t = [torch.cuda.Event(enable_timing=True) for _ in range(4)]
+            self.step(t)
+            marks.append(t)
+        self.barrier()
+        tot = sum(t[0].elapsed_time(t[3]) for t in marks) / steps
+        t_sid = sum(t[0].elapsed_time(t[1]) for t in marks) / steps
+        t_gn = sum(t[1].elapsed_time(t[2]) for t in marks) / steps
+        tt = torch.tensor([tot, t_sid, t_gn], dtype=torch.float64, device=self.dev)
+        if self.ws > 1:
+            dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+        tot, t_sid, t_gn = [float(x) for x in tt.cpu()]
+        return {'total': tot, 'siddon': t_sid, 'gn': t_gn}
+
+    def run_pipeline(self, reps):
+        torch, dist = self.torch, self.dist
+        marks = []
+        self.pipeline_step(marks)
+        marks.clear()
+        self.barrier()
+        for _ in range(reps):
+            self.pipeline_step(marks)
+        self.barrier()
+        names = ['siddon_poly', 'fbp_2_log_sinograms', 'gn', 'fbp_2_basis_sinograms', 'sum_partial_volumes']
+        vals = [sum(m[k].elapsed_time(m[k + 1]) for m in marks) / reps for k in range(5)]
+        vals.append(sum(m[0].elapsed_time(m[5]) for m in marks) / reps)
+        tt = torch.tensor(vals, dtype=torch.float64, device=self.dev)
+        if self.ws > 1:
+            dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+        out = dict(zip(names + ['total'], [float(x) for x in tt.cpu()]))
+        return out
+
+    def verify_peer(self):
+        """The peer-assembled buffers against NCCL's all-gather of the same shards (outside the timed region)."""
+        if self.pg is None:
+            return None
+        torch, dist = self.torch, self.dist
+        ok = True
+        for whole, mine in ((self.g_sino, self.g_sino[self.rank]), (self.g_basis, self.g_basis[self.rank])):
+            chk = torch.empty_like(whole)
+            dist.all_gather_into_tensor(chk, mine.contiguous())
+            ok = ok and bool(torch.equal(chk, whole))
+            del chk
+        flag = torch.tensor([int(ok)], device=self.dev)
+        dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+        return bool(int(flag[0]))
+
+    def segments_per_ray(self, n_sample=4):
+        """Mean voxel segments per ray on a sample of this rank's views, averaged over ranks (the unit of the roofline)."""
+        from dexct.ops import count_segments
+        torch, dist = self.torch, self.dist
+        sample = list(range(self.v0, self.v0 + self.nv, max(1, self.nv // n_sample)))[:n_sample]
+        seg = sum(count_segments(self.pj, v, 1) for v in sample) / (len(sample) * self.R * self.C)
+        st = torch.tensor([seg], dtype=torch.float64, device=self.dev)
+        if self.ws > 1:
+            dist.all_reduce(st)
+            st /= self.ws
+        return float(st[0])
+
+    def rooflines(self, t, clocks, peaks):
+        """Bytes-per-ray roofline of the projection kernel and FMA-pipe roofline of the decomposition kernel (whole job:
+        peaks x N)."""
+        ws = self.ws
+        hbm = float(peaks.get('hbm_gbs', 6650.0))
+        seg = self.segments_per_ray()
+        bytes_per_ray = seg * 1 + 2 * self.esz
+        ach = self.rays_total * bytes_per_ray / (t['siddon'] * 1e-3) / 1e9
+        kern = 'siddon_skip3_kernel' if self.name != 'C2' else 'siddon_skip_kernel'
+        traffic, traffic_src = None, None
+        try:                                                              # measured under ncu, committed with its source
+            tr = json.load(open(os.path.join(ROOT, 'profiles', 'ncu_traffic.json')))[f'{kern}:{self.name}']
+            traffic, traffic_src = tr['dram_bytes_read'] + tr['dram_bytes_write'], tr['source']
+        except Exception:                                                 # noqa: BLE001
+            pass
+        sm_mhz = (clocks or {}).get('sm_mhz') or peaks.get('sm_max_mhz', 1965.0)
+        fma_peak = 148 * 128 * 2 * sm_mhz * 1e6 / 1e12 * ws               # TFLOP/s fp32 at the clock seen during the run
+        gn_flops = 28.0 * self.nE * GN_ITERS * self.rays_total
+        gn_ach = gn_flops / (t['gn'] * 1e-3) / 1e12
+        roof = {'bound': 'hbm', 'achieved': ach, 'peak': hbm * ws, 'unit': 'GB/s', 'frac': ach / (hbm * ws), 'traffic': traffic,
+                'traffic_source': traffic_src, 'algorithmic_bytes_per_launch': self.rays_local * bytes_per_ray,
+                'kernel': kern, 'bytes_per_ray': bytes_per_ray, 'segments_per_ray': seg, 'launch_ms': t['siddon'],
+                'peak_source': ('MEASURED_PEAKS.json hbm_gbs' if peaks else 'fallback') + (f' x {ws} GPUs' if ws > 1 else '')}
+        roof_gn = {'bound': 'fp32_fma', 'achieved': gn_ach, 'peak': fma_peak, 'unit': 'TFLOP/s', 'frac': gn_ach / fma_peak,
+                   'kernel': 'gn_kernel', 'flop_per_pixel': 28.0 * self.nE * GN_ITERS, 'launch_ms': t['gn'], 'sm_mhz': sm_mhz}
+        return roof, roof_gn
+
+    def collective_text(self):
+        if self.collective == 'none':
+            return 'none'
+        if self.collective == 'nccl':
+            return 'NCCL: all-gather of counts/logs (overlapping the decomposition) and of the basis sinograms + 8-byte MAX all-reduce'
+        common = '; air maximum and end-of-step barrier through flags in peer memory (CUDA IPC over NVLink); no library collective in the step'
+        if self.push_mode == 'dma':
+            return (f'peer memory, copy engines: count/log shard ({self.slot_s >> 20} MiB per rank) sent by {self.ws - 1} DMAs beside the '
+                    f'decomposition, which runs in {GN_CHUNKS} view chunks whose basis pixels follow by DMA as they finish' + common)
+        if self.push_mode == 'fused':
+            return ('peer memory, fused: the decomposition kernel copies the count/log shard into the peers\' copies (a slice per '
+                    'Newton iteration) and its epilogue stores each basis pixel into all copies' + common)
+        return 'peer memory, store kernel on a side stream + mirrored GN epilogue' + common
+
+    def close(self):
+        torch = self.torch
+        status = 0
+        if self.pg is not None:
+            status = self.pg.status()
+            for k in ('counts', 'logs', 'basis', 'g_sino', 'g_basis'):
+                if hasattr(self, k):
+                    delattr(self, k)
+            self.pg.close()
+            self.pg = None
+        for k in list(self.__dict__):
+            if k not in ('torch', 'dist', 'rank', 'ws', 'dev', 'name'):
+                delattr(self, k)
+        torch.cuda.empty_cache()
+        if status:
+            raise SystemExit(f'bench.py: rank {self.rank} waited in vain for rank {status - 1} (peer flags)')
+
+
+def e2e_leg(name, dev, rank, ws, dtype, steps):
+    """The same scan through the reference-facing entry points, host numpy arrays in and out (float64, like the
+    reference's).  Returns the `e2e` object, or a note when the host cannot hold the arrays."""
+    import torch
+    import torch.distributed as dist
+    from dexct import config as cfg
+    from dexct import synthetic as S
+    from xtomosim import forward_project as FP
+    import matdecomp
+    c = S.CONFIGS[name]
+    n_views = c['n_views'] * (ws if SCALING[name] == 'weak' else 1)
+    rays = n_views * c['n_rows'] * c['n_ch']
+    # float64 host arrays alive at once on this node: 4 sinograms + 2 basis sinograms (+ the same again while the next step
+    # runs before the old arrays are dropped), phantom
+    need = 2 * 6 * rays * 8 + c['n'] * c['n'] * c['nz'] * ws
+    try:
+        import psutil
+        avail = psutil.virtual_memory().available
+    except Exception:                                                     # noqa: BLE001
+        avail = None
+    if avail is not None and need > 0.8 * avail:
+        return None, f'host has {avail / 1e9:.0f} GB available, the float64 arrays of {name} need {need / 1e9:.0f} GB'
+    cfg.dtype = dtype
+    # N > 1: every rank keeps the host arrays of ITS OWN view range (config.gather_views off) -- the data-parallel form in
+    # which each rank writes its part of the output; with the default (every rank returns the whole arrays, like the
+    # single-process reference) each rank would move the whole scan over its PCIe link and the host side could not scale.
+    # The air-mask maximum is still reduced over all ranks.
+    cfg.gather_views = ws == 1
+    on_dev = c['nz'] > 1
+    ct, ph, lo, hi = S.make_config(name, n_views=n_views, device=dev if on_dev else None)
+    if on_dev:                                   # the numpy-facing entry points take the phantom as a HOST array (page-locked)
+        host = torch.empty(ph.M.shape, dtype=torch.uint8, pin_memory=True)
+        host.copy_(ph.M)
+        torch.cuda.synchronize()
+        ph.M = host.numpy()
+    label_bytes = int(np.prod(ph.M.shape))
+
+    def step():
+        FP.clear_cache()                                                  # the phantom is uploaded and re-laid-out every step
+        (raw_lo, log_lo), (raw_hi, log_hi) = FP.get_sinos(ct, ph, [lo, hi])
+        m1, m2 = matdecomp.get_basismat_sinos(ct, raw_lo, raw_hi, lo, hi, n_iters=GN_ITERS, mask_thresh=MASK_THRESH)
+        return raw_lo, m1
+
+    def barrier():
+        if ws > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    for _ in range(2):
+        step()
+    barrier()
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        step()
+    barrier()
+    dt = torch.tensor([(time.perf_counter() - t0) / steps], dtype=torch.float64, device=dev)
+    if ws > 1:
+        dist.all_reduce(dt, op=dist.ReduceOp.MAX)
+    FP.clear_cache()
+    # up: labels + the two float64 count sinograms handed to get_basismat_sinos (they sit in page-locked memory: get_sinos
+    # returned them); down: 2 x (raw, log) + 2 basis sinograms, float64 like the reference's arrays; summed over ranks; the
+    # KB-sized tables are uploaded once per content
+    h2d = ws * label_bytes + 2 * rays * 8
+    d2h = 6 * rays * 8
+    return {'value': rays / float(dt[0]), 'unit': UNIT, 'h2d_bytes_per_step': int(h2d), 'd2h_bytes_per_step': int(d2h),
+            'ms_per_step': 1e3 * float(dt[0]), 'steps': steps, 'config': name,
+            'api': 'xtomosim.forward_project.get_sinos + matdecomp.get_basismat_sinos (float64 numpy in/out through page-locked '
+                   'buffers, phantom re-uploaded and re-laid-out every step'
+                   + (')' if ws == 1 else '; every rank keeps the host arrays of its own view range, bytes summed over ranks)')}, None
+
+
 def run_b200(args):
     import torch
     import torch.distributed as dist
 
     from dexct import _native as N
-    from dexct import synthetic as S
-    from dexct import dist as ddist
-    from dexct.ops import Projector, count_segments, dtype_code, gn_decompose, make_scan
-    from xtomosim import forward_project as FP
-    import matdecomp
 
     rank = int(os.environ.get('RANK', '0'))
     local_rank = int(os.environ.get('LOCAL_RANK', '0'))
@@ -252,271 +735,113 @@ def run_b200(args):
         os.environ.setdefault('MASTER_ADDR', '127.0.0.1')
         dist.init_process_group('nccl', device_id=dev)
     N.require_device()
-    code = dtype_code(args.dtype)
-    td = torch.float32 if args.dtype == 'f32' else torch.float64
+    peaks = load_peaks()
+    name = args.config
+    warmup = max(args.warmup, 3)
 
-    # ---- the scan: ws x 1000 views, this rank owns [v0, v0 + nv)
-    n_views = VIEWS_PER_GPU * ws
-    ct, ph, lo, hi = S.make_config('C2', n_views=n_views)
-    v0, nv = ddist.shard_range(n_views, rank, ws)
-    scan = make_scan(ct.N_proj, ct.N_channels, ct.gamma_fan, ct.SID, ct.SDD, rotation=ct.rotation)
-    pj = Projector(scan, ph.M, (ph.dx, ph.dy, ph.dz), device=dev)
-    mu = torch.as_tensor(ph.mu_table(lo.E), dtype=td, device=dev)
-    W = torch.as_tensor(np.stack([FP.spectral_weights(ct, lo), FP.spectral_weights(ct, hi)]), dtype=td, device=dev)
-    ee, i0_h, mus_h = matdecomp.spectral_tables(ct, lo, hi)
-    i0 = torch.as_tensor(i0_h, dtype=td, device=dev)
-    mus = torch.as_tensor(mus_h, dtype=td, device=dev)
-    rays_local = nv * N_CH
-    # N > 1: every rank ends the step holding the whole view-major sinograms.  'peer': the buffers are symmetric
-    # allocations mapped into every rank (dexct/peer.py); the projection writes its shard in place, the decomposition
-    # kernel carries that shard into the other ranks' copies while it iterates (DEXCT_PUSH=sm / dma: a store kernel or the
-    # copy engines on a side stream instead), its epilogue stores each basis pixel into all copies, and the air maximum is
-    # exchanged through flags in peer memory -- no NCCL call in the step.  'nccl': the same with three all-gathers and
-    # one all-reduce.
-    pg = None
-    collective = 'none'
-    esz = 4 if args.dtype == 'f32' else 8
-    slot_s, slot_b = 4 * nv * N_CH * esz, nv * N_CH * 2 * esz
-    if ws > 1 and args.collective == 'peer':
-        from dexct.dist import all_agree
-        from dexct.peer import PeerGroup
-        try:                                                              # (a failure on one rank raises on all: peer.py)
-            pg = PeerGroup()
-            sbuf, bbuf = pg.alloc(ws * slot_s), pg.alloc(ws * slot_b)
-        except Exception as exc:                                          # noqa: BLE001
-            print(f'bench.py: rank {rank}: peer memory unavailable ({exc})', file=sys.stderr)
-            sbuf = None
-        if not all_agree(pg is not None and sbuf is not None):            # belt and braces: all ranks take the same path
-            pg = None             # (not closed: closing is collective, and the ranks may not agree on what exists)
-            if rank == 0:
-                print('bench.py: using NCCL all-gathers on every rank', file=sys.stderr)
-        else:
-            collective = 'peer'
-    if ws > 1 and pg is None:
-        collective = 'nccl'
-    if pg is not None:
-        g_sino = sbuf.view(td, (ws, 4, nv, 1, N_CH))                      # [rank][counts lo, hi, logs lo, hi]
-        g_basis = bbuf.view(td, (ws, nv, 1, N_CH, 2))
-        counts, logs, basis = g_sino[rank, 0:2], g_sino[rank, 2:4], g_basis[rank]
-        mirrors = bbuf.table(rank * slot_b, exclude_self=True)
-        push_table = sbuf.table(rank * slot_s, exclude_self=True)
-        side = torch.cuda.Stream(device=dev)
-    else:
-        counts = torch.empty((2, nv, 1, N_CH), dtype=td, device=dev)
-        logs = torch.empty_like(counts)
-        basis = torch.empty((nv, 1, N_CH, 2), dtype=td, device=dev)
-        if ws > 1:
-            g_counts = torch.empty((ws, 2, nv, 1, N_CH), dtype=td, device=dev)
-            g_logs = torch.empty_like(g_counts)
-            g_basis = torch.empty((ws, nv, 1, N_CH, 2), dtype=td, device=dev)
-    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)      # > 126 MB L2
-
-    ev = lambda: torch.cuda.Event(enable_timing=True)                   # noqa: E731
-
-    def step(timers=None):
-        if timers is not None:
-            timers[0].record()
-        pj.project(mu, W, view_begin=v0, view_count=nv, dtype=code, want_log=True, counts=counts, logs=logs)
-        if timers is not None:
-            timers[1].record()
-        if pg is not None:
-            if PUSH_MODE == 'fused':
-                # one kernel: Newton iterations + the copy of the count/log shard into the peers, a slice per iteration
-                gn_decompose(counts.reshape(2, -1), i0, mus, GN_ITERS, mask_thresh=MASK_THRESH, dtype=code, out=basis.view(-1, 2),
-                             reduce_max_over_ranks=True, peers=pg, mirrors=mirrors, push=(g_sino[rank], push_table))
-                if timers is not None:
-                    timers[2].record()
-            else:
-                main = torch.cuda.current_stream()
-                side.wait_stream(main)
-                with torch.cuda.stream(side):
-                    pg.push(g_sino[rank], sbuf, rank * slot_s, dma=PUSH_MODE == 'dma', max_ctas=PUSH_CTAS)
-                gn_decompose(counts.reshape(2, -1), i0, mus, GN_ITERS, mask_thresh=MASK_THRESH, dtype=code, out=basis.view(-1, 2),
-                             reduce_max_over_ranks=True, peers=pg, mirrors=mirrors)
-                if timers is not None:
-                    timers[2].record()
-                main.wait_stream(side)
-            pg.barrier()                                    # every rank's stores have landed in every copy
-            return
-        pending = []
-        if ws > 1:
-            # the sinogram gathers ride NCCL's stream behind the projection and overlap the decomposition, which only
-            # needs the local view shard
-            pending.append(dist.all_gather_into_tensor(g_counts, counts, async_op=True))
-            pending.append(dist.all_gather_into_tensor(g_logs, logs, async_op=True))
-        gn_decompose(counts.view(2, -1), i0, mus, GN_ITERS, mask_thresh=MASK_THRESH, dtype=code, out=basis.view(-1, 2),
-                     reduce_max_over_ranks=ws > 1)
-        if timers is not None:
-            timers[2].record()
-        if ws > 1:
-            pending.append(dist.all_gather_into_tensor(g_basis, basis, async_op=True))
-            for w in pending:
-                w.wait()
-
-    def barrier():
-        if ws > 1:
-            dist.barrier()
-        torch.cuda.synchronize()
-
-    for _ in range(max(args.warmup, 3)):
-        flush.zero_()
-        step()
-    barrier()
-
+    # ---- headline: device-resident steps
+    sb = ScanBench(name, dev, rank, ws, dtype=args.dtype, collective=args.collective)
     sampler = ClockSampler(local_rank) if rank == 0 else None
+    for _ in range(warmup):                       # (warm-up outside the clock sampler's window)
+        sb.step()
+    sb.barrier()
     if sampler:
         sampler.start()
-    marks = []
-    barrier()
-    for _ in range(args.steps):
-        flush.zero_()
-        t = [ev() for _ in range(4)]
-        step(t)
-        t[3].record()
-        marks.append(t)
-    barrier()
+    t = sb.run(args.steps, 0)
     clocks = sampler.finish() if sampler else None
-    peer_ok = None
-    if pg is not None:
-        # the peer-assembled buffers against NCCL's all-gather of the same shards (outside the timed region)
-        chk_s, chk_b = torch.empty_like(g_sino), torch.empty_like(g_basis)
-        dist.all_gather_into_tensor(chk_s, g_sino[rank].contiguous())
-        dist.all_gather_into_tensor(chk_b, g_basis[rank].contiguous())
-        ok = torch.tensor([int(torch.equal(chk_s, g_sino) and torch.equal(chk_b, g_basis))], device=dev)
-        dist.all_reduce(ok, op=dist.ReduceOp.MIN)
-        peer_ok = bool(int(ok[0]))
-        del chk_s, chk_b
-    tot = sum(t[0].elapsed_time(t[3]) for t in marks)
-    t_sid = sum(t[0].elapsed_time(t[1]) for t in marks) / args.steps
-    t_gn = sum(t[1].elapsed_time(t[2]) for t in marks) / args.steps
-    tt = torch.tensor([tot, t_sid, t_gn], dtype=torch.float64, device=dev)
-    if ws > 1:
-        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
-    tot, t_sid, t_gn = [float(x) for x in tt.cpu()]
-    ms = tot / args.steps
-    value = rays_local * ws / (ms * 1e-3)
+    launches = sb.launches
+    peer_ok = sb.verify_peer()
+    roof, roof_gn = sb.rooflines(t, clocks, peaks)
+    value = sb.rays_total / (t['total'] * 1e-3)
+    line = None
+    if rank == 0:
+        line = {
+            'metric': METRIC, 'value': value, 'unit': UNIT, 'n_gpus': ws, 'steps': args.steps, 'warmup': warmup,
+            'ms_per_step': t['total'], 'higher_is_better': True, 'scaling': sb.scaling, 'vs_baseline': None, 'dtype': args.dtype,
+            'data': 'synthetic', 'config': config_dict(name, ws),
+            'assembly': sb.collective_text(),
+            'kernel_ms': {'siddon_poly': t['siddon'], 'gn': t['gn']},
+            **({'peer_buffers_equal_nccl_all_gather': peer_ok} if peer_ok is not None else {}),
+            'siddon_rays_per_s': sb.rays_total / (t['siddon'] * 1e-3), 'gn_pixels_per_s': sb.rays_total / (t['gn'] * 1e-3),
+            'roofline': roof, 'roofline_gn': roof_gn,
+            'gpu_launches': launches, 'gpu_launches_note': 'kernels and device copies enqueued by step() on this rank, counted where they are launched',
+            'clocks': clocks,
+        }
+
+    # ---- the whole pipeline of configs[4] (with FBP), on the same resident scan
+    extra = {}
+    if not args.no_extra and name == 'C5':
+        sb.close()
+        sb = ScanBench(name, dev, rank, ws, dtype=args.dtype, collective='nccl', with_fbp=True, assemble=False)
+        tp = sb.run_pipeline(2)
+        if rank == 0:
+            extra['c5_pipeline'] = {
+                'workload': WORKLOADS['C5'] + ', 4 x FBP -> 128 x 1024^2 (ramp 0.8)', 'ms': tp,
+                'rays_per_s_pipeline': sb.rays_total / (tp['total'] * 1e-3),
+                'fbp_pixel_views_per_s': 2.0 * sb.R * sb.n_matrix ** 2 * sb.n_views / (tp['fbp_2_log_sinograms'] * 1e-3),
+                'fbp_note': 'slice-by-slice fan-beam FBP of every detector row (no cone-angle / FDK weighting): a throughput figure, '
+                            'not a valid cone-beam reconstruction off the mid-plane',
+                'collective': 'none' if ws == 1 else 'no sinogram assembly (view-sharded FBP reads local views only); partial volumes '
+                              'summed by one NCCL reduce-scatter per volume into row slabs + 8-byte MAX all-reduce',
+                'device_mem_gb': torch.cuda.max_memory_allocated(dev) / 1e9}
+    sb.close()
+    del sb
 
     # ---- end to end through the reference-facing entry points, host buffers in and out
-    e2e = None
     if not args.no_e2e:
-        from dexct import config as cfg
-        cfg.dtype = args.dtype
-        k_e2e = max(3, min(args.steps, 10))
+        e2e, note = e2e_leg(name, dev, rank, ws, args.dtype, steps=max(2, min(args.steps, 3)) if name == 'C5' else max(3, min(args.steps, 10)))
+        if e2e is None and name != 'C4':
+            e2e, note2 = e2e_leg('C4', dev, rank, ws, args.dtype, steps=3)
+            if e2e is not None:
+                e2e['note'] = f'{note}; measured on C4 instead'
+        if rank == 0:
+            line['e2e'] = e2e if e2e is not None else {'value': None, 'unit': UNIT, 'note': note}
+        torch.cuda.empty_cache()
 
-        # N > 1: every rank keeps the host arrays of ITS OWN view range (config.gather_views off) -- the data-parallel form
-        # in which each rank writes its part of the output; with the default (every rank returns the whole arrays, like
-        # the single-process reference) each rank would move the whole scan over its PCIe link and the host side could
-        # not scale.  The air-mask maximum is still reduced over all ranks.
-        cfg.gather_views = ws == 1
-
-        def e2e_step():
-            FP.clear_cache()                                            # the phantom is uploaded and re-laid-out every step
-            (raw_lo, log_lo), (raw_hi, log_hi) = FP.get_sinos(ct, ph, [lo, hi])
-            m1, m2 = matdecomp.get_basismat_sinos(ct, raw_lo, raw_hi, lo, hi, n_iters=GN_ITERS, mask_thresh=MASK_THRESH)
-            return raw_lo, m1
-
-        for _ in range(2):
-            e2e_step()
-        barrier()
-        t0 = time.perf_counter()
-        for _ in range(k_e2e):
-            e2e_step()
-        barrier()
-        dt = torch.tensor([(time.perf_counter() - t0) / k_e2e], dtype=torch.float64, device=dev)
-        if ws > 1:
-            dist.all_reduce(dt, op=dist.ReduceOp.MAX)
-        esz = 4 if args.dtype == 'f32' else 8
-        # up: labels + tables + the two float64 count sinograms handed to get_basismat_sinos (they sit in page-locked
-        # memory: get_sinos returned them); down: 2 x (raw, log) + 2 basis sinograms, float64 like the reference's arrays
-        # summed over ranks; the KB-sized tables are uploaded once per content
-        h2d = ws * ph.M.nbytes + 2 * n_views * N_CH * 8
-        d2h = 6 * n_views * N_CH * 8
-        e2e = {'value': n_views * N_CH / float(dt[0]), 'unit': UNIT, 'h2d_bytes_per_step': int(h2d), 'd2h_bytes_per_step': int(d2h),
-               'ms_per_step': 1e3 * float(dt[0]), 'steps': k_e2e,
-               'api': 'xtomosim.forward_project.get_sinos + matdecomp.get_basismat_sinos (float64 numpy in/out through page-locked '
-                      'buffers, phantom re-uploaded and re-laid-out every step'
-                      + (')' if ws == 1 else '; every rank keeps the host arrays of its own view range, bytes summed over ranks)')}
+    # ---- secondary configurations (continuity with round 1)
+    if not args.no_extra:
+        for other, steps in (('C4', 3), ('C2', 20)):
+            if other == name:
+                continue
+            ob = ScanBench(other, dev, rank, ws, dtype=args.dtype, collective=args.collective)
+            to = ob.run(steps, 3)
+            ok = ob.verify_peer()
+            ro, rg = ob.rooflines(to, clocks, peaks)
+            if rank == 0:
+                extra[other.lower()] = {'workload': WORKLOADS[other], 'scaling': ob.scaling, 'steps': steps, 'ms_per_step': to['total'],
+                                        'kernel_ms': {'siddon_poly': to['siddon'], 'gn': to['gn']},
+                                        'value': ob.rays_total / (to['total'] * 1e-3), 'unit': UNIT, 'rays_per_step': ob.rays_total,
+                                        'assembly': ob.collective_text(), 'roofline': ro, 'roofline_gn': rg,
+                                        **({'peer_buffers_equal_nccl_all_gather': ok} if ok is not None else {})}
+            ob.close()
+            del ob
+        if ws == 1 and rank == 0:
+            extra.update(extra_single_gpu(dev, args.dtype, peaks))
 
     if rank == 0:
-        peaks = {}
-        try:
-            peaks = json.load(open(os.path.join(ROOT, 'MEASURED_PEAKS.json')))
-        except Exception:                                                 # noqa: BLE001
-            pass
-        hbm = float(peaks.get('hbm_gbs', 6650.0))
-        seg = count_segments(pj, v0, min(nv, 100)) / (min(nv, 100) * N_CH)
-        traffic, traffic_src = None, None
-        try:                                                              # measured under ncu, committed with its source
-            tr = json.load(open(os.path.join(ROOT, 'profiles', 'ncu_traffic.json')))['siddon_skip_kernel']
-            traffic, traffic_src = tr['dram_bytes_read'] + tr['dram_bytes_write'], tr['source']
-        except Exception:                                                 # noqa: BLE001
-            pass
-        bytes_per_ray = seg * 1 + 2 * (4 if args.dtype == 'f32' else 8)
-        ach = rays_local * bytes_per_ray / (t_sid * 1e-3) / 1e9
-        sm_mhz = (clocks or {}).get('sm_mhz') or peaks.get('sm_max_mhz', 1965.0)
-        fma_peak = 148 * 128 * 2 * sm_mhz * 1e6 / 1e12                    # TFLOP/s fp32 at the clock seen during the run
-        nE = int(i0.shape[1])
-        gn_flops = 28.0 * nE * GN_ITERS * rays_local
-        line = {
-            'metric': METRIC, 'value': value, 'unit': UNIT, 'n_gpus': ws, 'steps': args.steps, 'warmup': max(args.warmup, 3),
-            'ms_per_step': ms, 'higher_is_better': True, 'scaling': 'weak', 'vs_baseline': None, 'dtype': args.dtype,
-            'data': 'synthetic',
-            'config': {'workload': WORKLOAD, 'views_total': n_views, 'rays_per_step': rays_local * ws, 'gn_iters': GN_ITERS,
-                       'l2': 'flushed between timed steps (256 MiB write)', 'parallelism': f'view-sharded x{ws}',
-                       'collective': {'none': 'none',
-                                      'peer': 'none from a library: counts/logs pushed into the peers\' copies by a store kernel beside the '
-                                              'decomposition, basis sinograms stored to all copies by the GN epilogue, air maximum and end-of-step '
-                                              'barrier through flags in peer memory (CUDA IPC over NVLink)',
-                                      'nccl': 'all-gather of counts/logs (overlapping the decomposition) and basis sinograms + MAX all-reduce '
-                                              'inside the step'}[collective]},
-            'kernel_ms': {'siddon_poly': t_sid, 'gn': t_gn},
-            **({'peer_buffers_equal_nccl_all_gather': peer_ok} if peer_ok is not None else {}),
-            'siddon_rays_per_s': rays_local * ws / (t_sid * 1e-3), 'gn_pixels_per_s': rays_local * ws / (t_gn * 1e-3),
-            'roofline': {'bound': 'hbm', 'achieved': ach, 'peak': hbm, 'unit': 'GB/s', 'frac': ach / hbm, 'traffic': traffic,
-                         'traffic_source': traffic_src, 'algorithmic_bytes_per_launch': rays_local * bytes_per_ray,
-                         'kernel': 'siddon_skip_kernel', 'bytes_per_ray': bytes_per_ray, 'segments_per_ray': seg,
-                         'peak_source': 'MEASURED_PEAKS.json hbm_gbs' if peaks else 'fallback'},
-            'roofline_gn': {'bound': 'fp32_fma', 'achieved': gn_flops / (t_gn * 1e-3) / 1e12, 'peak': fma_peak, 'unit': 'TFLOP/s',
-                            'frac': gn_flops / (t_gn * 1e-3) / 1e12 / fma_peak, 'kernel': 'gn_kernel',
-                            'flop_per_pixel': 28.0 * nE * GN_ITERS},
-            # per step: siddon_skip, gn_max, gn_table, gn_kernel, gn_fixup (+ peer_push, peer_max, peer_barrier at N > 1)
-            'gpu_launches': ((7 if PUSH_MODE == 'fused' else 8) if pg is not None else 5) * args.steps, 'clocks': clocks,
-        }
-        if e2e:
-            line['e2e'] = e2e
         if ws == 1 and not args.no_cpu_baseline:
-            arm = CpuArm(args.cpu_views or auto_cpu_views())
-            arm.step()
+            arm = CpuArm(name, args.cpu_views or auto_cpu_views(name))
             t0 = time.perf_counter()
             arm.step()
             dtc = time.perf_counter() - t0
             arm.close()
-            line['cpu_baseline'] = arm.describe(arm.n_views * N_CH / dtc)
-        if ws == 1 and not args.no_extra:
-            line['extra'] = extra_measurements(dev, args.dtype)
+            line['cpu_baseline'] = arm.describe(arm.rays / dtc)
+            line['cpu_baseline']['segments_per_ray'] = arm.seg_per_ray
+        if extra:
+            line['extra'] = extra
         print(json.dumps(line), flush=True)
-    if pg is not None:
-        status = pg.status()
-        pg.close()
-        if status:
-            raise SystemExit(f'bench.py: rank {rank} waited in vain for rank {status - 1} (peer flags)')
     if ws > 1:
         dist.barrier()
         dist.destroy_process_group()
 
 
-def extra_measurements(dev, dtype):
-    """Secondary device timings, reported beside the headline (never part of `value`): the 3-D (cone-beam) projector on
-    two 48-view ranges of config C4 against the same bytes-per-ray roofline, and fan-beam FBP of one C2 sinogram."""
+def extra_single_gpu(dev, dtype, peaks):
+    """Secondary device timings at N = 1: the 3-D projector on two 48-view ranges of C4 (the slowest and a typical one),
+    workspace preparation, and fan-beam FBP of one C2 sinogram."""
     import torch
     from dexct import synthetic as S
     from dexct.ops import Projector, count_segments, fbp_fan, make_scan
     from xtomosim import forward_project as FP
-    peaks = {}
-    try:
-        peaks = json.load(open(os.path.join(ROOT, 'MEASURED_PEAKS.json')))
-    except Exception:                                                     # noqa: BLE001
-        pass
     hbm = float(peaks.get('hbm_gbs', 6650.0))
     td = torch.float32 if dtype == 'f32' else torch.float64
     esz = 4 if dtype == 'f32' else 8
@@ -546,7 +871,7 @@ def extra_measurements(dev, dtype):
     out['prepare_c2_ms'] = timed(pj.prepare, 10)
     del pj
     n_views = 48
-    ct, ph, lo, hi = S.make_config('C4', device=dev)            # labels rasterised on the device (12 s in numpy)
+    ct, ph, lo, hi = S.make_config('C4', device=dev)
     scan = make_scan(ct.N_proj, ct.N_channels, ct.gamma_fan, ct.SID, ct.SDD, n_rows=ct.N_rows, h_iso=ct.h_iso, rotation=ct.rotation)
     pj = Projector(scan, ph.M, (ph.dx, ph.dy, ph.dz), device=dev)
     out['prepare_c4_ms'] = timed(pj.prepare, 3)
@@ -556,13 +881,13 @@ def extra_measurements(dev, dtype):
     logs = torch.empty_like(counts)
     rays = n_views * ct.N_rows * ct.N_channels
     out['siddon_3d_c4'] = []
-    for v0 in (0, 150):
+    for v0 in (0, 150, 300, 450):
         t = timed(lambda: pj.project(mu, W, view_begin=v0, view_count=n_views, dtype=dtype, counts=counts, logs=logs), 5)
         seg = count_segments(pj, v0, 4) / (4 * ct.N_rows * ct.N_channels)
         ach = rays * (seg + 2 * esz) / (t * 1e-3) / 1e9
         out['siddon_3d_c4'].append({'views': [v0, v0 + n_views], 'ms': t, 'rays_per_s': rays / (t * 1e-3), 'segments_per_ray': seg,
                                     'roofline': {'bound': 'hbm', 'achieved': ach, 'peak': hbm, 'unit': 'GB/s', 'frac': ach / hbm}})
-    out['workload_c4'] = '512^3 phantom, 64 rows x 900 ch, 48 of 1200 views per range, 120 bins, 2 spectra fused'
+    out['workload_c4_ranges'] = '512^3 phantom, 64 rows x 900 ch, 48 of 1200 views per range, 120 bins, 2 spectra fused'
     return out
 
 

@@ -109,6 +109,11 @@ constexpr int GN_CTAB_ROWS = 512;                             // nE + 2 zero row
 constexpr int GN_CROW = 12;                                   // floats per moment row: 6 (measurement 1, measurement 2) pairs
 __constant__ ulonglong2 gn_ctab[GN_CTAB_ROWS * (GN_CROW / 4)];
 __constant__ f32x2 gn_cexp[GN_CTAB_ROWS];
+// Unified form (loop variants 1..3): one 64-byte row per bin = { exponent pair, six moment pairs, pad }, so that the loop
+// carries ONE uniform byte offset (add, compare, branch) instead of two scaled indices (eight uniform-ALU instructions per
+// trip in variant 0: profiles/r02a_gn_sass_loop.txt).  gn_crow overlays nothing: variant 0 keeps its own two tables.
+constexpr int GN_UROW = 16;                                   // floats per unified row
+__constant__ ulonglong2 gn_crow[(GN_CTAB_ROWS + 4) * (GN_UROW / 4)];
 
 // Staging image of both tables: [nE + 2][12] moment rows, then [nE + 2][2] exponent pairs; the two rows past nE are zero.
 __global__ void gn_table_kernel(const float *__restrict__ i0, const float *__restrict__ mus, int nE, float *__restrict__ tab)
@@ -130,6 +135,22 @@ __global__ void gn_table_kernel(const float *__restrict__ i0, const float *__res
     for (int q = 0; q < 6; ++q) { row[2 * q] = s1 * f[q]; row[2 * q + 1] = s2 * f[q]; }
 }
 
+// Unified rows: [nE + 4][16] = { -mu1 s, -mu2 s, six (measurement 1, measurement 2) moment pairs, 0, 0 }; four zero rows past nE.
+__global__ void gn_table_unified_kernel(const float *__restrict__ i0, const float *__restrict__ mus, int nE, float *__restrict__ tab)
+{
+    const int e = blockIdx.x * blockDim.x + threadIdx.x;
+    if (e >= nE + 4) return;
+    float *row = tab + e * GN_UROW;
+#pragma unroll
+    for (int q = 0; q < GN_UROW; ++q) row[q] = 0.f;
+    if (e >= nE) return;
+    const float m1 = mus[e], m2 = mus[nE + e], s1 = i0[e], s2 = i0[nE + e];
+    row[0] = -m1 * GnMath<float>::scale; row[1] = -m2 * GnMath<float>::scale;
+    const float f[6] = {1.f, m1, m2, m1 * m1, m1 * m2, m2 * m2};
+#pragma unroll
+    for (int q = 0; q < 6; ++q) { row[2 + 2 * q] = s1 * f[q]; row[3 + 2 * q] = s2 * f[q]; }
+}
+
 // Further copies of the result in peer memory (view-sharded scans, peer.cu): the epilogue stores every pixel to each of
 // them as well, so the basis sinograms are assembled on all ranks by the time the kernel ends -- no gather afterwards.
 struct GnMirrors { void *p[DEXCT_MAX_PEERS]; int n; };
@@ -147,7 +168,7 @@ __device__ __forceinline__ void gn_rider_slice(const GnRider &rd, int k, int nk)
     }
 }
 
-template <typename R, int PX, bool CTAB>
+template <typename R, int PX, bool CTAB, int VAR>
 __global__ void __launch_bounds__(256, (PX == 4 && CTAB) ? 3 : 1) gn_kernel(const R *__restrict__ g, const R *__restrict__ i0, const R *__restrict__ mus,
                                                  int nE, long long P, int n_iters, R mask_thresh, void *scratch,
                                                  R *__restrict__ a_out, const GnMirrors mir, const GnRider rider)
@@ -238,7 +259,54 @@ __global__ void __launch_bounds__(256, (PX == 4 && CTAB) ? 3 : 1) gn_kernel(cons
                         acc2[k][5] = ffma2(r[3].x, att2, acc2[k][5]);
                     }
                 };
-                if constexpr (CTAB) {
+                if constexpr (CTAB && VAR >= 1) {
+                    // unified 64-byte rows behind one uniform byte offset; pipelined like variant 0
+                    float att[PX], nxt[PX];
+                    auto exps_u = [&](f32x2 tt, float(&o)[PX]) {
+                        float t0, t1;
+                        unpack2(tt, t0, t1);
+#pragma unroll
+                        for (int k = 0; k < PX; ++k) o[k] = M::att(fmaf(a2[k], t1, a1[k] * t0));
+                    };
+                    auto accum_u = [&](const ulonglong2 *r, const float(&w)[PX]) {
+                        const f32x2 m0 = r[0].y, m5 = r[3].x;
+                        const ulonglong2 r1 = r[1], r2 = r[2];
+#pragma unroll
+                        for (int k = 0; k < PX; ++k) {
+                            const f32x2 att2 = pack2(w[k], w[k]);
+                            acc2[k][0] = ffma2(m0, att2, acc2[k][0]);
+                            acc2[k][1] = ffma2(r1.x, att2, acc2[k][1]);
+                            acc2[k][2] = ffma2(r1.y, att2, acc2[k][2]);
+                            acc2[k][3] = ffma2(r2.x, att2, acc2[k][3]);
+                            acc2[k][4] = ffma2(r2.y, att2, acc2[k][4]);
+                            acc2[k][5] = ffma2(m5, att2, acc2[k][5]);
+                        }
+                    };
+                    const ulonglong2 *r = gn_crow;
+                    const ulonglong2 *const rend = gn_crow + 4 * nE;
+                    exps_u(r[0].x, att);
+                    if constexpr (VAR == 1) {
+#pragma unroll 1
+                        for (; r < rend; r += 8) {
+                            exps_u(r[4].x, nxt);
+                            accum_u(r, att);
+                            exps_u(r[8].x, att);
+                            accum_u(r + 4, nxt);
+                        }
+                    } else {
+#pragma unroll 1
+                        for (; r < rend; r += 16) {
+                            exps_u(r[4].x, nxt);
+                            accum_u(r, att);
+                            exps_u(r[8].x, att);
+                            accum_u(r + 4, nxt);
+                            exps_u(r[12].x, nxt);
+                            accum_u(r + 8, att);
+                            exps_u(r[16].x, att);
+                            accum_u(r + 12, nxt);
+                        }
+                    }
+                } else if constexpr (CTAB) {
                     // pipelined over bins: exponentials of bin e + 1 first, then the FFMA2 of bin e on its moment row
                     float att[PX], nxt[PX];
                     {
@@ -451,20 +519,21 @@ static int launch_max(const void *g, long long P, void *scratch, cudaStream_t st
     return DEXCT_OK;
 }
 
-template <typename R, int PX>
+template <typename R, int PX, int VAR = 0>
 static int launch_gn(const void *g, const void *i0, const void *mus, int nE, long long P, int n_iters, double mask_thresh,
                      void *a_out, void *scratch, bool have_max, cudaStream_t st, const GnMirrors &mir, const GnRider &rider)
 {
     const char *bs = getenv("DEXCT_GN_BLOCK");         // tuning knob (threads per CTA: 128 or 256)
     const int block = (bs && atoi(bs) == 128) ? 128 : 256;
     const bool ctab = sizeof(R) == 4 && nE + 2 <= GN_CTAB_ROWS;
+    constexpr bool UNI = VAR >= 1;
     const size_t smem = ctab ? 0 : sizeof(R) * (size_t)(nE + 2) * GN_ROW;
     if (smem > 200 * 1024) {
         set_error("GN table needs %zu bytes of shared memory (limit 200 KiB): nE=%d", smem, nE);
         return DEXCT_ECAPACITY;
     }
-    void (*kern)(const R *, const R *, const R *, int, long long, int, R, void *, R *, const GnMirrors, const GnRider) = gn_kernel<R, PX, false>;
-    if (ctab) kern = gn_kernel<R, PX, sizeof(R) == 4>;
+    void (*kern)(const R *, const R *, const R *, int, long long, int, R, void *, R *, const GnMirrors, const GnRider) = gn_kernel<R, PX, false, 0>;
+    if (ctab) kern = gn_kernel<R, PX, sizeof(R) == 4, VAR>;
     if (smem > 48 * 1024) DEXCT_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     int per_sm = 0;
     DEXCT_CUDA_OK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, block, smem));
@@ -493,12 +562,19 @@ static int launch_gn(const void *g, const void *i0, const void *mus, int nE, lon
     if (ctab) {
         ConstSlot slot(SLOT_GN, st);                          // exclusive use of gn_ctab until the kernel below has run
         if (!slot.ok()) return DEXCT_ECUDA;
+        if (UNI) {
+            gn_table_unified_kernel<<<(nE + 4 + 127) / 128, 128, 0, st>>>((const float *)i0, (const float *)mus, nE, (float *)slot.staging());
+            DEXCT_CUDA_OK(cudaGetLastError());
+            DEXCT_CUDA_OK(cudaMemcpyToSymbolAsync(gn_crow, slot.staging(), sizeof(float) * (size_t)(nE + 4) * GN_UROW, 0,
+                                                  cudaMemcpyDeviceToDevice, st));
+        } else {
         gn_table_kernel<<<(nE + 2 + 127) / 128, 128, 0, st>>>((const float *)i0, (const float *)mus, nE, (float *)slot.staging());
         DEXCT_CUDA_OK(cudaGetLastError());
         DEXCT_CUDA_OK(cudaMemcpyToSymbolAsync(gn_ctab, slot.staging(), sizeof(float) * (size_t)(nE + 2) * GN_CROW, 0,
                                               cudaMemcpyDeviceToDevice, st));
         DEXCT_CUDA_OK(cudaMemcpyToSymbolAsync(gn_cexp, (const float *)slot.staging() + (size_t)(nE + 2) * GN_CROW,
                                               sizeof(float) * (size_t)(nE + 2) * 2, 0, cudaMemcpyDeviceToDevice, st));
+        }
         kern<<<(unsigned)grid, block, smem, st>>>((const R *)g, (const R *)i0, (const R *)mus, nE, P, n_iters, (R)mask_thresh,
                                                  scratch, (R *)a_out, mir, rider);
         DEXCT_CUDA_OK(cudaGetLastError());
@@ -549,6 +625,10 @@ static int gn_decompose_impl(const void *g, const void *i0, const void *mus, int
         if (npx == 1) return launch_gn<float, 1>(g, i0, mus, nE, P, n_iters, mask_thresh, a_out, scratch, have, st, mir, rider);
         if (npx == 3) return launch_gn<float, 3>(g, i0, mus, nE, P, n_iters, mask_thresh, a_out, scratch, have, st, mir, rider);
         if (npx == 2) return launch_gn<float, 2>(g, i0, mus, nE, P, n_iters, mask_thresh, a_out, scratch, have, st, mir, rider);
+        const char *vs = getenv("DEXCT_GN_VAR");         // tuning knob (loop variant)
+        const int var = vs ? atoi(vs) : 0;
+        if (var == 1) return launch_gn<float, 4, 1>(g, i0, mus, nE, P, n_iters, mask_thresh, a_out, scratch, have, st, mir, rider);
+        if (var == 2) return launch_gn<float, 4, 2>(g, i0, mus, nE, P, n_iters, mask_thresh, a_out, scratch, have, st, mir, rider);
         return launch_gn<float, 4>(g, i0, mus, nE, P, n_iters, mask_thresh, a_out, scratch, have, st, mir, rider);
     }
     return launch_gn<double, 1>(g, i0, mus, nE, P, n_iters, mask_thresh, a_out, scratch, have, st, mir, rider);

@@ -199,8 +199,31 @@ def poly_detect(L, mu, W, dtype=F32, want_log=True):
     return counts, logs
 
 
+def gn_air_key(g1, dtype=F32, reduce_max_over_ranks=False, peers=None):
+    """Monotone integer key of ``max(g1)`` -- the maximum of the first measurement, which sets the air threshold of
+    get_basismat_sinos (/root/reference/matdecomp.py:196) -- as an 8-byte device tensor for ``gn_decompose(air_key=...)``.
+    Lets a caller decompose a sinogram in several pieces (e.g. to start sending finished pieces to other ranks) against
+    the threshold of the WHOLE sinogram.  ``reduce_max_over_ranks``: MAX over all ranks (``peers``: through flags in peer
+    memory, else one NCCL all-reduce)."""
+    N.require_device()
+    code = dtype_code(dtype)
+    if not (isinstance(g1, torch.Tensor) and g1.is_cuda and g1.dtype == _TORCH_DTYPE[code] and g1.is_contiguous()):
+        raise ValueError('g1 must be a contiguous CUDA tensor of the compute dtype')
+    scratch = torch.empty(16, dtype=torch.uint8, device=g1.device)
+    with torch.cuda.device(g1.device):
+        N.check(N.lib().dexct_gn_air_max(N.ptr(g1), g1.numel(), N.ptr(scratch), code, N.stream_ptr()))
+        if reduce_max_over_ranks:
+            if peers is not None:
+                peers.max_key(scratch, code)
+            else:
+                import torch.distributed as dist
+                key = scratch[:8].view(torch.int64) if code == F64 else scratch[:4].view(torch.int32)
+                dist.all_reduce(key, op=dist.ReduceOp.MAX)
+    return scratch[:8]
+
+
 def gn_decompose(g, i0, mus, n_iters, mask_thresh=0.0, dtype=F32, out=None, reduce_max_over_ranks=False, peers=None,
-                 mirrors=None, push=None):
+                 mirrors=None, push=None, air_key=None):
     """g [2, ...] counts (device tensor or array), i0 [2, nE], mus [2, nE] -> a [..., 2] device tensor.
 
     ``reduce_max_over_ranks``: the pixels are one shard of a larger sinogram; the air threshold then uses the maximum of the
@@ -208,7 +231,8 @@ def gn_decompose(g, i0, mus, n_iters, mask_thresh=0.0, dtype=F32, out=None, redu
     (matdecomp.py:196) -- through ``peers`` (a dexct.peer.PeerGroup: flags in peer memory) when given, else NCCL.
     ``mirrors``: ctypes table of further device addresses (peer copies of the basis sinogram, SymBuffer.table) that the
     kernel's epilogue stores every pixel to as well.  ``push``: ``(src_tensor, table)`` -- a finished contiguous buffer
-    (the count/log shard) that the same kernel copies to the addresses in ``table`` while it computes."""
+    (the count/log shard) that the same kernel copies to the addresses in ``table`` while it computes.
+    ``air_key``: result of :func:`gn_air_key` -- the threshold then comes from that maximum instead of ``max(g[0])``."""
     N.require_device()
     code = dtype_code(dtype)
     td = _TORCH_DTYPE[code]
@@ -225,7 +249,10 @@ def gn_decompose(g, i0, mus, n_iters, mask_thresh=0.0, dtype=F32, out=None, redu
     scratch = torch.empty(N.lib().dexct_gn_scratch_bytes(P, code), dtype=torch.uint8, device=dev)
     have_max = 0
     with torch.cuda.device(dev):
-        if reduce_max_over_ranks and mask_thresh > 0:
+        if air_key is not None and mask_thresh > 0:
+            scratch[:8].copy_(air_key)
+            have_max = 1
+        elif reduce_max_over_ranks and mask_thresh > 0:
             import torch.distributed as dist
             N.check(N.lib().dexct_gn_air_max(N.ptr(g), P, N.ptr(scratch), code, N.stream_ptr()))
             if peers is not None:

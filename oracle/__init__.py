@@ -63,6 +63,7 @@ def lib():
         L.dexo_slab_trace.restype = C.c_int
         L.dexo_slab_lengths.argtypes = [C.POINTER(_Setup), P, C.c_int, C.c_int, C.c_int, C.c_int, P]
         L.dexo_num_threads.restype = C.c_int
+        L.dexo_set_num_threads.argtypes = [C.c_int]
         _lib = L
     return _lib
 
@@ -186,3 +187,9 @@ def poly_detect(L, mu, W, want_log=True):
 
 def num_threads():
     return int(lib().dexo_num_threads())
+
+
+def set_num_threads(n):
+    """OpenMP threads of the C oracle from here on (a launcher's OMP_NUM_THREADS=1 would otherwise throttle the timed CPU
+    baseline of bench.py)."""
+    lib().dexo_set_num_threads(int(n))

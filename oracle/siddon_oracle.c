@@ -497,6 +497,16 @@ void dexo_slab_lengths(const dexo_setup *g, const uint8_t *labels, int K, int v0
     }
 }
 
+/* A launcher may export OMP_NUM_THREADS=1 (torchrun does); the timed CPU baseline asks for its threads explicitly. */
+void dexo_set_num_threads(int n)
+{
+#ifdef _OPENMP
+    if (n > 0) omp_set_num_threads(n);
+#else
+    (void)n;
+#endif
+}
+
 int dexo_num_threads(void)
 {
 #ifdef _OPENMP
