@@ -168,6 +168,43 @@ __device__ __forceinline__ void gn_rider_slice(const GnRider &rd, int k, int nk)
     }
 }
 
+
+// One Newton step of a pixel from its twelve energy sums A[0..5] (measurement 1), A[6..11] (measurement 2):
+// {nu, sum i0 mu1 att, sum i0 mu2 att, sum i0 mu1^2 att, sum i0 mu1 mu2 att, sum i0 mu2^2 att}  (matdecomp.py:118-125).
+template <typename R>
+__device__ __forceinline__ void newton_update(const R *A, R g1, R g2, R &a1, R &a2, bool &sane)
+{
+    typedef GnMath<R> M;
+    const R nu1 = A[0], nu2 = A[6];
+    if (sizeof(R) == 4) {
+        // single precision cannot follow the reference where its exponent clip (matdecomp.py:116) is what keeps
+        // the sums finite: any sum beyond these bounds (inf and NaN included) sends the pixel to the float64 pass
+        R big = fmax(fabs(A[3]), fabs(A[9]));
+        big = fmax(big, fmax(fmax(fabs(A[4]), fabs(A[10])), fmax(fabs(A[5]), fabs(A[11]))));
+        sane = sane && (nu1 < (R)1e18) && (nu2 < (R)1e18) && (big < (R)1e30) && (nu1 > (R)0) && (nu2 > (R)0);
+    }
+    const R r1 = g1 / nu1 - (R)1, r2 = g2 / nu2 - (R)1;            // g/nu - 1
+    const R s1 = g1 / (nu1 * nu1), s2 = g2 / (nu2 * nu2);          // g/nu^2
+    // grad_mp = -A[1+p]; the two minus signs of dF cancel, grad grad^T is sign-free
+    const R d1 = r1 * A[1] + r2 * A[7];
+    const R d2 = r1 * A[2] + r2 * A[8];
+    const R h11 = -(r1 * A[3] + r2 * A[9]) + (s1 * A[1] * A[1] + s2 * A[7] * A[7]);
+    const R h12 = -(r1 * A[4] + r2 * A[10]) + (s1 * A[1] * A[2] + s2 * A[7] * A[8]);
+    const R h22 = -(r1 * A[5] + r2 * A[11]) + (s1 * A[2] * A[2] + s2 * A[8] * A[8]);
+    // 2x2 solve; the determinant is a difference of like-sized products -> compensate the first product
+    const R w = h12 * h12;
+    const R err = M::fma(-h12, h12, w);
+    const R det = M::fma(h11, h22, -w) + err;
+    const R inv = (R)1 / det;
+    a1 -= (h22 * d1 - h12 * d2) * inv;
+    a2 -= (h11 * d2 - h12 * d1) * inv;
+    // An indefinite Hessian means the iterate has left the basin of the minimum: from there the Newton map is chaotic and
+    // single precision cannot retrace the reference's float64 trajectory; neither can it where a basis thickness runs far
+    // below zero (photon-starved pixels: the exponent a.mu is then a difference of huge terms).  GN_A_FLOOR [g/cm2] is far
+    // outside anything physical.
+    if (sizeof(R) == 4) sane = sane && det > (R)0 && h11 > (R)0 && fmin(a1, a2) > (R)GN_A_FLOOR;
+}
+
 template <typename R, int PX, bool CTAB, int VAR>
 __global__ void __launch_bounds__(256, (PX == 4 && CTAB) ? 3 : 1) gn_kernel(const R *__restrict__ g, const R *__restrict__ i0, const R *__restrict__ mus,
                                                  int nE, long long P, int n_iters, R mask_thresh, void *scratch,
@@ -380,38 +417,7 @@ __global__ void __launch_bounds__(256, (PX == 4 && CTAB) ? 3 : 1) gn_kernel(cons
             }
             }
 #pragma unroll
-            for (int k = 0; k < PX; ++k) {
-                const R *A = acc[k];                                          // A[0..5] meas 1, A[6..11] meas 2
-                const R nu1 = A[0], nu2 = A[6];
-                if (sizeof(R) == 4) {
-                    // single precision cannot follow the reference where its exponent clip (matdecomp.py:116) is what keeps
-                    // the sums finite: any sum beyond these bounds (inf and NaN included) sends the pixel to the float64 pass
-                    R big = fmax(fabs(A[3]), fabs(A[9]));
-                    big = fmax(big, fmax(fmax(fabs(A[4]), fabs(A[10])), fmax(fabs(A[5]), fabs(A[11]))));
-                    sane[k] = sane[k] && (nu1 < (R)1e18) && (nu2 < (R)1e18) && (big < (R)1e30) && (nu1 > (R)0) && (nu2 > (R)0);
-                }
-                const R r1 = g1[k] / nu1 - (R)1, r2 = g2[k] / nu2 - (R)1;      // g/nu - 1
-                const R s1 = g1[k] / (nu1 * nu1), s2 = g2[k] / (nu2 * nu2);    // g/nu^2
-                // grad_mp = -A[1+p]; the two minus signs of dF cancel, grad grad^T is sign-free
-                const R d1 = r1 * A[1] + r2 * A[7];
-                const R d2 = r1 * A[2] + r2 * A[8];
-                const R h11 = -(r1 * A[3] + r2 * A[9]) + (s1 * A[1] * A[1] + s2 * A[7] * A[7]);
-                const R h12 = -(r1 * A[4] + r2 * A[10]) + (s1 * A[1] * A[2] + s2 * A[7] * A[8]);
-                const R h22 = -(r1 * A[5] + r2 * A[11]) + (s1 * A[2] * A[2] + s2 * A[8] * A[8]);
-                // 2x2 solve; the determinant is a difference of like-sized products -> compensate the first product
-                const R w = h12 * h12;
-                const R err = M::fma(-h12, h12, w);
-                const R det = M::fma(h11, h22, -w) + err;
-                const R inv = (R)1 / det;
-                // an indefinite Hessian means the iterate has left the basin of the minimum: from there the Newton map
-                // is chaotic and single precision cannot retrace the reference's float64 trajectory
-                a1[k] -= (h22 * d1 - h12 * d2) * inv;
-                a2[k] -= (h11 * d2 - h12 * d1) * inv;
-                // ... and neither can it where a basis thickness runs far below zero (photon-starved pixels: the exponent
-                // a.mu is then a difference of huge terms).  GN_A_FLOOR [g/cm2] is far outside anything physical.
-                if (sizeof(R) == 4)
-                    sane[k] = sane[k] && det > (R)0 && h11 > (R)0 && fmin(a1[k], a2[k]) > (R)GN_A_FLOOR;
-            }
+            for (int k = 0; k < PX; ++k) newton_update<R>(acc[k], g1[k], g2[k], a1[k], a2[k], sane[k]);
         }
 #pragma unroll
         for (int k = 0; k < PX; ++k) {
@@ -438,6 +444,279 @@ __global__ void __launch_bounds__(256, (PX == 4 && CTAB) ? 3 : 1) gn_kernel(cons
     }
     if (ride)
         for (; rider_k < rider_nk; ++rider_k) gn_rider_slice(rider, rider_k, rider_nk);
+}
+
+// ---------------------------------------------------------------------------------------------------------------------
+// Tensor-core form of the single-precision decomposition (sm_100a: tcgen05.mma + tensor memory).
+//
+// The twelve energy sums of a pixel are one row of the product  att[pixel][bin] x row[bin][moment]  -- a contraction over
+// the energy bins with N = 12 (padded to 16) columns -- and they are 24 of the 28 floating-point operations per (pixel,
+// bin).  Here they leave the FP32 pipe: a CTA owns a tile of 128 pixels (thread t <-> pixel t <-> lane t of tensor memory);
+// per chunk of bins each thread evaluates its exponentials, splits every value into a TF32 head and a tail
+// (att = hi + lo exactly: hi = att with the low 13 mantissa bits cleared) and stores both into tensor memory as the A operand
+// (tcgen05.st); one thread of a fifth warp then issues, per eight bins, three M128 x N16 x K8 TF32 MMAs
+//     D += hi x Bhi,  D += lo x Bhi,  D += hi x Blo            (Bhi + Blo = the moment rows, split once per call)
+// -- the "3xTF32" scheme: products of 11-bit significands are exact in the FP32 accumulator, and the one missing term
+// lo x Blo is below 2^-22 of the sum -- with B read from shared memory through a K-major no-swizzle matrix descriptor and D
+// (128 lanes x 16 columns of FP32) accumulating in tensor memory over all bins of a Newton iteration.  The threads read their
+// row of D back (tcgen05.ld), do the 2x2 Newton step in registers as before, and go round again.  A-operand chunks are double
+// buffered (mbarriers: full[b] by the compute warps, free[b] and done by tcgen05.commit), four CTAs share an SM (4 x 128
+// columns of tensor memory), so exponentials, MMAs and Newton updates of different tiles overlap.
+// What is left per (pixel, bin) on the ordinary pipes: FMUL2/FFMA2 halves for the exponent, one MUFU.EX2, one LOP3, half an
+// FADD2 -- the kernel is bound by the MUFU unit (16 ex2 per clock and SM) instead of the FMA pipe.
+constexpr int GT_KS = 8;                    // bins per MMA: 32 bytes of TF32 along K
+constexpr int GT_CHUNK_KS = 3;              // k-steps per A-operand chunk
+constexpr int GT_CH = GT_KS * GT_CHUNK_KS;  // bins per chunk
+constexpr int GT_NBUF = 2;
+constexpr int GT_COLS = 128;                // tensor-memory columns per CTA: 2 x (24 hi + 24 lo) + 16 accumulator + 16 spare
+constexpr int GT_DCOL = GT_NBUF * 2 * GT_CH;
+constexpr int GT_THREADS = 160;             // four compute warps (one per 32 lanes of tensor memory) + the MMA warp
+constexpr int GT_MAX_KS = 56;               // 56 KiB of B operand + 3.5 KiB of exponent pairs fit the 64 KiB staging slot
+constexpr uint32_t GT_IDESC = (1u << 4) | (2u << 7) | (2u << 10) | ((16u >> 3) << 17) | ((128u >> 4) << 24);   // F32 += TF32 x TF32, K-major A and B, N = 16, M = 128
+__constant__ ulonglong2 gn_tcx[GT_MAX_KS * 4];      // per k-step: -mu1 s of its 8 bins, then -mu2 s of its 8 bins (zero past nE)
+
+// B operand image: per k-step 512 B of TF32 heads then 512 B of tails, each the canonical K-major no-swizzle layout
+// [K half (4 bins)][moment group of 8][moment][4 bins]  -- core matrices of 8 rows x 16 bytes; LBO (next K half) = 256 B,
+// SBO (next moment group) = 128 B.  Followed by the exponent table [nks][16].
+__global__ void gn_tc_table_kernel(const float *__restrict__ i0, const float *__restrict__ mus, int nE, int nks, float *__restrict__ tab)
+{
+    const int e = blockIdx.x * blockDim.x + threadIdx.x;
+    if (e >= nks * GT_KS) return;
+    const int ks = e / GT_KS, kc = (e % GT_KS) / 4, kk = e % 4;
+    float row[16];
+#pragma unroll
+    for (int q = 0; q < 16; ++q) row[q] = 0.f;
+    float t0 = 0.f, t1 = 0.f;
+    if (e < nE) {
+        const float m1 = mus[e], m2 = mus[nE + e], s1 = i0[e], s2 = i0[nE + e];
+        t0 = -m1 * GnMath<float>::scale; t1 = -m2 * GnMath<float>::scale;
+        const float f[6] = {1.f, m1, m2, m1 * m1, m1 * m2, m2 * m2};
+#pragma unroll
+        for (int q = 0; q < 6; ++q) { row[q] = s1 * f[q]; row[6 + q] = s2 * f[q]; }
+    }
+    float *b = tab + (size_t)ks * 256;
+#pragma unroll
+    for (int n = 0; n < 16; ++n) {
+        const float hi = __uint_as_float((__float_as_uint(row[n]) + 0x1000u) & 0xffffe000u);      // nearest TF32 (11-bit significand)
+        const int at = ((kc * 2 + n / 8) * 8 + n % 8) * 4 + kk;
+        b[at] = hi;
+        b[128 + at] = row[n] - hi;                                                                  // exact
+    }
+    float *x = tab + (size_t)nks * 256 + ks * 16;
+    x[e % GT_KS] = t0;
+    x[8 + e % GT_KS] = t1;
+}
+
+__device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count)
+{
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(bar), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_arrive(uint32_t bar)
+{
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
+}
+// Wait for the phase of the given parity to complete.  A wait that lasts seconds can only mean a protocol error: trap
+// instead of hanging the device.
+__device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity)
+{
+    uint32_t ok = 0;
+    long long t0 = 0;
+    for (;;) {
+        asm volatile("{ .reg .pred p; mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2; selp.u32 %0, 1, 0, p; }"
+                     : "=r"(ok) : "r"(bar), "r"(parity) : "memory");
+        if (ok) return;
+        if (t0 == 0) t0 = clock64();
+        else if (clock64() - t0 > 8000000000ll) __trap();
+    }
+}
+__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tmem_st8(uint32_t taddr, const uint32_t (&v)[8])
+{
+    asm volatile("tcgen05.st.sync.aligned.32x32b.x8.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8};" ::"r"(taddr), "r"(v[0]), "r"(v[1]),
+                 "r"(v[2]), "r"(v[3]), "r"(v[4]), "r"(v[5]), "r"(v[6]), "r"(v[7]) : "memory");
+}
+__device__ __forceinline__ void tmem_ld16(uint32_t taddr, float (&v)[16])
+{
+    uint32_t r[16];
+    asm volatile("tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
+                 : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
+                   "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
+                 : "r"(taddr) : "memory");
+    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+#pragma unroll
+    for (int q = 0; q < 16; ++q) v[q] = __uint_as_float(r[q]);
+}
+// D[tmem] (+)= A[tmem] x B[smem descriptor], M128 N16 K8, TF32 in, FP32 accumulate
+__device__ __forceinline__ void tc_mma_tf32(uint32_t d_tmem, uint32_t a_tmem, uint64_t b_desc, uint32_t accumulate)
+{
+    asm volatile("{ .reg .pred p; setp.ne.b32 p, %4, 0; tcgen05.mma.cta_group::1.kind::tf32 [%0], [%1], %2, %3, p; }" ::"r"(d_tmem),
+                 "r"(a_tmem), "l"(b_desc), "r"(GT_IDESC), "r"(accumulate) : "memory");
+}
+__device__ __forceinline__ void tc_commit(uint32_t bar)
+{
+    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
+}
+__device__ __forceinline__ f32x2 fmul2(f32x2 a, f32x2 b)
+{
+    f32x2 r;
+    asm("mul.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
+    return r;
+}
+__device__ __forceinline__ f32x2 fsub2(f32x2 a, f32x2 b)
+{
+    f32x2 r;
+    asm("sub.rn.f32x2 %0, %1, %2;" : "=l"(r) : "l"(a), "l"(b));
+    return r;
+}
+
+__global__ void __launch_bounds__(GT_THREADS) gn_tc_kernel(const float *__restrict__ g, const float *__restrict__ btab, int nks, long long P,
+                                                           int n_iters, float mask_thresh, void *scratch, float *__restrict__ a_out,
+                                                           const GnMirrors mir, const GnRider rider, int lbo_sbo_swapped)
+{
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    float *bsm = (float *)smem_raw;                           // [nks][hi 128 floats, lo 128 floats]
+    __shared__ __align__(8) unsigned long long bars[2 * GT_NBUF + 1];
+    __shared__ uint32_t tmem_base_sm;
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const uint32_t bar_full = smem_u32(&bars[0]), bar_free = smem_u32(&bars[GT_NBUF]), bar_done = smem_u32(&bars[2 * GT_NBUF]);
+
+    for (int i = tid; i < nks * 64; i += GT_THREADS) ((float4 *)bsm)[i] = ((const float4 *)btab)[i];
+    if (tid == 0) {
+        for (int b = 0; b < GT_NBUF; ++b) { mbar_init(bar_full + 8 * b, 4); mbar_init(bar_free + 8 * b, 1); }
+        mbar_init(bar_done, 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (warp == 4) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&tmem_base_sm)), "r"(GT_COLS) : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");     // the B operand written above is read by the tensor core (async proxy)
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem = tmem_base_sm;
+
+    const long long n_tiles = (P + 127) / 128;
+    const int n_chunks = (nks + GT_CHUNK_KS - 1) / GT_CHUNK_KS;
+
+    if (warp == 4) {
+        // ---- MMA issuer: one thread mirrors the loop structure of the compute warps
+        if (lane == 0) {
+            const uint64_t lbo = lbo_sbo_swapped ? 128 : 256, sbo = lbo_sbo_swapped ? 256 : 128;
+            const uint64_t desc0 = ((lbo >> 4) << 16) | ((sbo >> 4) << 32) | (1ull << 46);
+            const uint32_t bsm_addr = smem_u32(bsm);
+            uint32_t cnt = 0;
+            for (long long tile = blockIdx.x; tile < n_tiles; tile += gridDim.x)
+                for (int it = 0; it < n_iters; ++it)
+                    for (int c = 0; c < n_chunks; ++c, ++cnt) {
+                        const uint32_t b = cnt % GT_NBUF;
+                        mbar_wait(bar_full + 8 * b, (cnt / GT_NBUF) & 1);
+                        tc_fence_after();
+                        const uint32_t a_hi = tmem + b * 2 * GT_CH, a_lo = a_hi + GT_CH;
+#pragma unroll
+                        for (int s = 0; s < GT_CHUNK_KS; ++s) {
+                            const int ks = c * GT_CHUNK_KS + s;
+                            if (ks < nks) {
+                                const uint64_t d_hi = desc0 | (uint64_t)(((bsm_addr + ks * 1024) & 0x3ffff) >> 4);
+                                const uint64_t d_lo = desc0 | (uint64_t)(((bsm_addr + ks * 1024 + 512) & 0x3ffff) >> 4);
+                                tc_mma_tf32(tmem + GT_DCOL, a_hi + s * GT_KS, d_hi, ks > 0);
+                                tc_mma_tf32(tmem + GT_DCOL, a_lo + s * GT_KS, d_hi, 1);
+                                tc_mma_tf32(tmem + GT_DCOL, a_hi + s * GT_KS, d_lo, 1);
+                            }
+                        }
+                        tc_commit(bar_free + 8 * b);                  // the chunk's A operand may be overwritten once these MMAs are done
+                        if (c == n_chunks - 1) tc_commit(bar_done);   // ... and the sums of this iteration are complete
+                    }
+        }
+        __syncwarp();
+    } else {
+        // ---- compute warps: thread t owns pixel tile * 128 + t and lane t of tensor memory
+        const float thr = mask_thresh > 0.f ? mask_thresh * decode_max<float>(scratch) : INFINITY;
+        const uint32_t lane_base = tmem + ((uint32_t)(warp * 32) << 16);
+        const int rider_per_tile = n_iters > 0 ? n_iters : 1;
+        const int rider_nk = rider_per_tile * (int)((n_tiles + gridDim.x - 1) / gridDim.x);
+        int rider_k = 0;
+        const bool ride = rider.n != 0;
+        auto rider_slice = [&](int k) {
+            const long long nthreads = (long long)gridDim.x * 128;
+            for (long long i = (long long)blockIdx.x * 128 + tid + nthreads * k; i < rider.n16; i += nthreads * rider_nk) {
+                const uint4 v = rider.src[i];
+                for (int d = 0; d < rider.n; ++d) ((uint4 *)rider.dst[d])[i] = v;
+            }
+        };
+        uint32_t cnt = 0, done_cnt = 0;
+        for (long long tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+            const long long p = tile * 128 + tid;
+            const float g1 = p < P ? g[p] : 1.f, g2 = p < P ? g[P + p] : 1.f;
+            float a1 = 1e-6f, a2 = 1e-6f;                                     // matdecomp.py:98
+            bool sane = true;
+            for (int it = 0; it < n_iters; ++it) {
+                if (ride) rider_slice(rider_k++);
+                const f32x2 a1p = pack2(a1, a1), a2p = pack2(a2, a2);
+#pragma unroll 1
+                for (int c = 0; c < n_chunks; ++c, ++cnt) {
+                    const uint32_t b = cnt % GT_NBUF;
+                    mbar_wait(bar_free + 8 * b, ((cnt / GT_NBUF) & 1) ^ 1);
+                    tc_fence_after();
+                    const uint32_t col = lane_base + b * 2 * GT_CH;
+#pragma unroll
+                    for (int s = 0; s < GT_CHUNK_KS; ++s) {
+                        const int ks = c * GT_CHUNK_KS + s;
+                        if (ks < nks) {
+                            const ulonglong2 *x = gn_tcx + ks * 4;
+                            const ulonglong2 t0a = x[0], t0b = x[1], t1a = x[2], t1b = x[3];
+                            const f32x2 t0[4] = {t0a.x, t0a.y, t0b.x, t0b.y}, t1[4] = {t1a.x, t1a.y, t1b.x, t1b.y};
+                            uint32_t hi[8], lo[8];
+#pragma unroll
+                            for (int j = 0; j < 4; ++j) {
+                                const f32x2 xx = ffma2(a2p, t1[j], fmul2(a1p, t0[j]));
+                                float x0, x1;
+                                unpack2(xx, x0, x1);
+                                const float e0 = GnMath<float>::att(x0), e1 = GnMath<float>::att(x1);
+                                hi[2 * j] = __float_as_uint(e0) & 0xffffe000u;
+                                hi[2 * j + 1] = __float_as_uint(e1) & 0xffffe000u;
+                                const f32x2 l2 = fsub2(pack2(e0, e1), pack2(__uint_as_float(hi[2 * j]), __uint_as_float(hi[2 * j + 1])));
+                                float l0, l1;
+                                unpack2(l2, l0, l1);
+                                lo[2 * j] = __float_as_uint(l0);
+                                lo[2 * j + 1] = __float_as_uint(l1);
+                            }
+                            tmem_st8(col + s * GT_KS, hi);
+                            tmem_st8(col + GT_CH + s * GT_KS, lo);
+                        }
+                    }
+                    asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
+                    tc_fence_before();
+                    __syncwarp();
+                    if (lane == 0) mbar_arrive(bar_full + 8 * b);
+                }
+                mbar_wait(bar_done, done_cnt++ & 1);
+                tc_fence_after();
+                float A[16];
+                tmem_ld16(lane_base + GT_DCOL, A);
+                tc_fence_before();
+                newton_update<float>(A, g1, g2, a1, a2, sane);
+            }
+            if (p < P) {
+                const bool masked = g1 >= thr;                                    // matdecomp.py:196,204-205
+                const float2 o = make_float2(masked ? 0.f : a1, masked ? 0.f : a2);
+                ((float2 *)a_out)[p] = o;
+                for (int d = 0; d < mir.n; ++d) ((float2 *)mir.p[d])[p] = o;
+                const bool finite = fabsf(a1) < INFINITY && fabsf(a2) < INFINITY;
+                if (!masked && !(sane && finite)) {                               // rare: hand the pixel to gn_fixup_kernel
+                    unsigned *fl = (unsigned *)scratch;
+                    fl[4 + atomicAdd(fl + 2, 1u)] = (unsigned)p;
+                }
+            }
+        }
+        if (ride)
+            for (; rider_k < rider_nk; ++rider_k) rider_slice(rider_k);
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 4) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"(GT_COLS) : "memory");
 }
 
 // Float64 pass over the pixels the single-precision kernel flagged (scratch: [2] = count, [4 ...] = pixel ids): the same
@@ -586,6 +865,44 @@ static int launch_gn(const void *g, const void *i0, const void *mus, int nE, lon
     return sizeof(R) == 4 ? fixup() : DEXCT_OK;
 }
 
+// Single precision through the tensor-core kernel (nE <= 8 GT_MAX_KS).  Same contract as launch_gn<float, .>.
+static int launch_gn_tc(const void *g, const void *i0, const void *mus, int nE, long long P, int n_iters, double mask_thresh,
+                        void *a_out, void *scratch, bool have_max, cudaStream_t st, const GnMirrors &mir, const GnRider &rider)
+{
+    const int nks = (nE + GT_KS - 1) / GT_KS;
+    const size_t smem = (size_t)nks * 1024;
+    DEXCT_CUDA_OK(cudaFuncSetAttribute(gn_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    int per_sm = 0;
+    DEXCT_CUDA_OK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, gn_tc_kernel, GT_THREADS, smem));
+    if (per_sm < 1) per_sm = 1;
+    if (per_sm > 512 / GT_COLS) per_sm = 512 / GT_COLS;         // tensor memory: 512 columns per SM
+    const long long n_tiles = (P + 127) / 128;
+    long long grid = (long long)sm_count() * per_sm;           // one resident wave; the tile-stride loop does the rest
+    if (grid > n_tiles) grid = n_tiles;
+    if (mask_thresh > 0 && !have_max) {
+        if (int e = launch_max<float>(g, P, scratch, st)) return e;
+    }
+    DEXCT_CUDA_OK(cudaMemsetAsync((char *)scratch + 8, 0, 8, st));                              // count of flagged pixels
+    const char *sw = getenv("DEXCT_GN_TC_SWAP");                // debugging knob: LBO/SBO of the B descriptor exchanged
+    {
+        ConstSlot slot(SLOT_GN, st);                          // exclusive use of gn_tcx and the staging image until the kernel has run
+        if (!slot.ok()) return DEXCT_ECUDA;
+        gn_tc_table_kernel<<<(nks * GT_KS + 127) / 128, 128, 0, st>>>((const float *)i0, (const float *)mus, nE, nks, (float *)slot.staging());
+        DEXCT_CUDA_OK(cudaGetLastError());
+        DEXCT_CUDA_OK(cudaMemcpyToSymbolAsync(gn_tcx, (const float *)slot.staging() + (size_t)nks * 256, sizeof(float) * 16 * (size_t)nks, 0,
+                                              cudaMemcpyDeviceToDevice, st));
+        gn_tc_kernel<<<(unsigned)grid, GT_THREADS, smem, st>>>((const float *)g, (const float *)slot.staging(), nks, P, n_iters,
+                                                              (float)mask_thresh, scratch, (float *)a_out, mir, rider, sw && atoi(sw));
+        DEXCT_CUDA_OK(cudaGetLastError());
+    }
+    const size_t fsm = sizeof(double) * 14 * (size_t)nE;
+    if (fsm > 48 * 1024) DEXCT_CUDA_OK(cudaFuncSetAttribute(gn_fixup_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)fsm));
+    gn_fixup_kernel<<<sm_count() * 4, 128, fsm, st>>>((const float *)g, (const float *)i0, (const float *)mus, nE, P, n_iters,
+                                                      (const unsigned *)scratch, (float *)a_out, mir);
+    DEXCT_CUDA_OK(cudaGetLastError());
+    return DEXCT_OK;
+}
+
 }  // namespace dexct
 
 using namespace dexct;
@@ -620,6 +937,9 @@ static int gn_decompose_impl(const void *g, const void *i0, const void *mus, int
     cudaStream_t st = (cudaStream_t)stream;
     const bool have = scratch_has_max != 0;
     if (dtype == DEXCT_F32) {
+        const char *tc = getenv("DEXCT_GN_TC");          // 1: tensor-core kernel (tcgen05), 0: FP32-pipe kernel
+        if (tc && atoi(tc) && (nE + GT_KS - 1) / GT_KS <= GT_MAX_KS)
+            return launch_gn_tc(g, i0, mus, nE, P, n_iters, mask_thresh, a_out, scratch, have, st, mir, rider);
         const char *px = getenv("DEXCT_GN_PX");          // tuning knob (pixels per thread)
         const int npx = px ? atoi(px) : 4;            // 4: the table row of a bin is fetched once for four pixels
         if (npx == 1) return launch_gn<float, 1>(g, i0, mus, nE, P, n_iters, mask_thresh, a_out, scratch, have, st, mir, rider);
