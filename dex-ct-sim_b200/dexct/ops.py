@@ -281,6 +281,14 @@ def gn_decompose(g, i0, mus, n_iters, mask_thresh=0.0, dtype=F32, out=None, redu
     return out
 
 
+def gn_fixup_count():
+    """Pixels the most recent single-precision ``gn_decompose`` call handed to its float64 pass (synchronises)."""
+    scratch = getattr(gn_decompose, 'last_scratch', None)
+    if scratch is None or scratch.numel() <= 16:
+        return 0
+    return int(scratch[8:12].view(torch.int32).item())
+
+
 def fbp_fan(scan, sino, n_matrix, fov, ramp, view_begin=0, dtype=F32, image=None, accumulate=False):
     """Fan-beam FBP of the views ``[view_begin, view_begin + sino.shape[0])`` of ``scan`` (replaces the numerics of
     get_recon, /root/reference/main.py:134,168).

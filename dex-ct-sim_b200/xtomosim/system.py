@@ -172,7 +172,10 @@ class VoxelPhantom:
         import torch
         mu = self.mu_table(np.array([float(E0)]))[:, 0]
         mu_w = xc.mixatten(WATER, np.array([float(E0)]))[0]
-        img = 1000.0 * (mu[self.M[self.z_index]] - mu_w) / mu_w
+        sl = self.M[self.z_index]
+        if isinstance(sl, torch.Tensor):                     # device-resident labels: one slice comes to the host
+            sl = sl.cpu().numpy()
+        img = 1000.0 * (mu[sl] - mu_w) / mu_w
         dev = 'cuda' if torch.cuda.is_available() else 'cpu'
         return _DeviceArray(torch.as_tensor(img.astype(np.float32), device=dev))
 

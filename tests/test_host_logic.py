@@ -218,3 +218,31 @@ def test_cone_recurrence_equals_runs_then_diagonal_minimum():
         if trial % 2:
             img = np.repeat(np.repeat(rng.integers(0, 3, (npc // 4 + 1, ne // 4 + 2)), 4, 0), 4, 1)[:npc, :ne + 1]
         assert np.array_equal(cone(img[:, :-1], img[:, 1:]), two_pass(img[:, :-1], img[:, 1:]))
+
+
+def test_phantom_digest_sees_every_voxel():
+    """The workspace cache of get_sino is keyed on the WHOLE label volume (host arrays of any size and device tensors):
+    a one-voxel in-place edit, or moving a block of voxels by a word, changes the key."""
+    import torch
+    from xtomosim.forward_project import _content_digest
+    rng = np.random.default_rng(3)
+    a = rng.integers(0, 8, size=(72, 1024, 1024), dtype=np.uint8)          # 72 MiB: the multi-piece path
+    d = _content_digest(a)
+    assert _content_digest(a.copy()) == d
+    b = a.copy()
+    b[40, 517, 4099 % 1024] ^= 1
+    assert _content_digest(b) != d
+    c = a.copy()
+    c[0, 0, :8], c[0, 0, 8:16] = a[0, 0, 8:16], a[0, 0, :8]
+    assert (c != a).any() and _content_digest(c) != d
+    small = a[:1, :64, :64]
+    assert _content_digest(small) == _content_digest(np.ascontiguousarray(small))
+    t = torch.from_numpy(a[:2].copy())
+    dt = _content_digest(t)
+    assert _content_digest(t.clone()) == dt
+    u = t.clone()
+    u[1, 1000, 1000] ^= 1
+    assert _content_digest(u) != dt
+    w = t.clone()
+    w[0, 0, :8], w[0, 0, 8:16] = t[0, 0, 8:16], t[0, 0, :8]
+    assert _content_digest(w) != dt
