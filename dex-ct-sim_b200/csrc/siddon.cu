@@ -656,9 +656,17 @@ __device__ __forceinline__ void stage_packed(const DetectArgs &d, f32x2 *mu2, f3
 // where q crosses j + 1.  W points at (column 0, mirrored row of j_c) of the layout for this ray's axis and slope sign.
 // No clamp on j: the ray is clipped to the volume, so j stays inside [-1, nq] -- the zero apron and the row padding of
 // the layout.
-template <typename R>
+// SINK: what else happens at every step.  Production passes NoStepSink (nothing, compiled out); the walk-trace kernel passes
+// a recorder, so that the sequence checked against the oracle is the sequence of THIS code, not of a look-alike.
+struct NoStepSink {
+    static constexpr bool active = false;
+    template <typename R>
+    __device__ __forceinline__ void operator()(int, int, int, const int *, const int *, const int *, const R *) const {}
+};
+
+template <typename R, typename SINK>
 __device__ __forceinline__ void walk_skip(const uint16_t *__restrict__ W, int pitch, int i0, int i1, int i_c, R am, R c0,
-                                          R ua, R ub, R inv_am, R *acc, int stride)
+                                          R ua, R ub, R inv_am, R *acc, int stride, SINK &sink)
 {
     typedef Rn<R> A;
     typedef FastInt<R> F;
@@ -686,6 +694,12 @@ __device__ __forceinline__ void walk_skip(const uint16_t *__restrict__ W, int pi
         const R v0 = *p0, v1 = *p1;
         *p1 = A::add(v1, whi);                                            // p1 == p0 only when whi == 0: order matters
         *p0 = A::add(v0, wlo);
+        if constexpr (SINK::active) {
+            const int jr = F::to_int(t);
+            const int js[3] = {jr, jr + 1, 0}, ks[3] = {0, 0, 0}, ls[3] = {f0, hom ? f0 : f1, 0};
+            const R ws[3] = {wlo, whi, (R)0};
+            sink(ofs / pitch, hom ? step : 0, 2, js, ks, ls, ws);
+        }
         ofs += step * pitch;
         fi = fnext;
     }
@@ -728,8 +742,9 @@ __global__ void __launch_bounds__(128) siddon_skip_kernel(SiddonParams P, int vi
             const int pitch = s.xmajor ? P.pitch_xm : P.pitch_ym;
             const uint16_t *W = P.skip[(s.xmajor ? 0 : 2) + (mpos ? 0 : 1)] + (mpos ? s.j_c : s.nq - 1 - s.j_c) + 1;
             const double c0 = mpos ? s.cq : 1.0 - s.cq;
+            NoStepSink none;
             walk_skip<R>(W, pitch, s.i0, s.i1, s.i_c, (R)fabs(s.m), (R)c0, (R)s.ua, (R)s.ub, (R)s.inv_am, acc_s + tid,
-                         (int)blockDim.x);
+                         (int)blockDim.x, none);
             seglen = (R)s.seglen;
         }
 
@@ -783,9 +798,9 @@ template <typename R> __device__ __forceinline__ void acc_add(R *acc, int stride
     *p = Rn<R>::add(*p, w);
 }
 
-template <typename R>
+template <typename R, typename SINK>
 __device__ __forceinline__ void walk_skip3(const uint16_t *__restrict__ W, int pitch, int plane, int i0, int i1, int i_c, R am,
-                                           R c0, R mz, R cw, R ua, R ub, R inv_am, R inv_amz, R *acc, int stride)
+                                           R c0, R mz, R cw, R ua, R ub, R inv_am, R inv_amz, R *acc, int stride, SINK &sink)
 {
     typedef Rn<R> A;
     typedef FastInt<R> F;
@@ -825,6 +840,14 @@ __device__ __forceinline__ void walk_skip3(const uint16_t *__restrict__ W, int p
         acc_add<R>(acc, stride, hom ? l00 : lA0, t1);
         acc_add<R>(acc, stride, hom ? l00 : (qfirst ? lA1 : lB0), A::sub(t2, t1));
         acc_add<R>(acc, stride, hom ? l00 : lB1, A::sub(wtot, t2));
+        if constexpr (SINK::active) {
+            const int jr = F::to_int(tj), kr = F::to_int(tk);
+            const int kA = mzpos ? kr : kr + 1, kB = mzpos ? kr + 1 : kr;
+            const int js[3] = {jr, qfirst ? jr + 1 : jr, jr + 1}, ks[3] = {kA, qfirst ? kA : kB, kB};
+            const int ls[3] = {hom ? l00 : lA0, hom ? l00 : (qfirst ? lA1 : lB0), hom ? l00 : lB1};
+            const R ws[3] = {t1, A::sub(t2, t1), A::sub(wtot, t2)};
+            sink(ofs / pitch, hom ? step : 0, 3, js, ks, ls, ws);
+        }
         ofs += step * pitch;
         fi = fnext;
     }
@@ -869,8 +892,9 @@ __global__ void __launch_bounds__(128) siddon_skip3_kernel(SiddonParams P, int v
             const uint16_t *W = P.skip[(s.xmajor ? 0 : 2) + (mpos ? 0 : 1)] + (long long)(s.k_c + 1) * plane +
                                 (mpos ? s.j_c : s.nq - 1 - s.j_c) + 1;
             const double c0 = mpos ? s.cq : 1.0 - s.cq;
+            NoStepSink none;
             walk_skip3<R>(W, pitch, plane, s.i0, s.i1, s.i_c, (R)fabs(s.m), (R)c0, (R)s.mz, (R)s.cw, (R)s.ua, (R)s.ub,
-                          (R)s.inv_am, (R)s.inv_amz, acc_s + tid, (int)blockDim.x);
+                          (R)s.inv_am, (R)s.inv_amz, acc_s + tid, (int)blockDim.x, none);
             seglen = (R)s.seglen;
         }
 
@@ -1002,6 +1026,81 @@ __global__ void siddon_trace_kernel(SiddonParams P, const int64_t *__restrict__ 
     n_seg[t] = n;
 }
 
+// Debug: the steps of the PRODUCTION walks (walk_skip / walk_skip3 over the skip layouts) of selected rays, recorded by a
+// sink inside the very same routine the production kernels inline.  Per step: first column, run length (0 = an ordinary
+// column split into pieces, S > 0 = a homogeneous stretch of S columns taken in one go), and up to three pieces (voxel,
+// label, length); a piece outside the volume (the zero apron) has voxel -1.
+template <typename R> struct WalkTraceSink {
+    static constexpr bool active = true;
+    int32_t *col, *run;
+    int64_t *vox;
+    uint8_t *lab;
+    R *len;
+    int n, max_steps;
+    bool xmajor, mpos;
+    int nx, ny, nq, nz, j_c, k_c;
+    R seglen;
+    __device__ __forceinline__ void operator()(int i, int run_len, int np, const int *js, const int *ks, const int *ls, const R *ws)
+    {
+        if (col && n < max_steps) {
+            col[n] = i;
+            run[n] = run_len;
+            for (int q = 0; q < 3; ++q) {
+                const int j = mpos ? j_c + js[q] : j_c - js[q], k = k_c + ks[q];
+                const bool inside = q < np && j >= 0 && j < nq && k >= 0 && k < nz;
+                vox[3 * n + q] = inside ? (xmajor ? ((int64_t)k * ny + j) * nx + i : ((int64_t)k * ny + i) * nx + j) : -1;
+                lab[3 * n + q] = q < np ? (uint8_t)ls[q] : 0;
+                len[3 * n + q] = q < np ? Rn<R>::mul(ws[q], seglen) : (R)0;
+            }
+        }
+        ++n;
+    }
+};
+
+template <typename R, bool IS3D>
+__global__ void siddon_walk_trace_kernel(SiddonParams P, const int64_t *__restrict__ ray_ids, int n_rays, int max_steps, int K,
+                                         int32_t *__restrict__ col, int32_t *__restrict__ run, int64_t *__restrict__ vox,
+                                         uint8_t *__restrict__ lab, R *__restrict__ len, int32_t *__restrict__ n_steps,
+                                         int32_t *__restrict__ meta, R *__restrict__ acc_scratch)
+{
+    const int t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= n_rays) return;
+    const int64_t ray = ray_ids[t];
+    const int c = (int)(ray % P.scan.n_ch);
+    const int64_t line = ray / P.scan.n_ch;
+    const int r = (int)(line % P.scan.n_rows);
+    const int v = (int)(line / P.scan.n_rows);
+    RaySetup s;
+    ray_setup<IS3D>(P, v, r, c, s);
+    R *acc = acc_scratch + (size_t)t * K;                      // per-material sums of the walk (stride 1), returned scaled
+    for (int m = 0; m < K; ++m) acc[m] = (R)0;
+    WalkTraceSink<R> sink;
+    sink.n = 0;
+    if (s.hit) {
+        const bool mpos = s.m >= 0.0;
+        const int pitch = s.xmajor ? P.pitch_xm : P.pitch_ym;
+        const size_t o = (size_t)t * max_steps;
+        sink.col = col ? col + o : nullptr; sink.run = run + o; sink.vox = vox + 3 * o; sink.lab = lab + 3 * o; sink.len = len + 3 * o;
+        sink.max_steps = max_steps; sink.xmajor = s.xmajor; sink.mpos = mpos;
+        sink.nx = P.vol.nx; sink.ny = P.vol.ny; sink.nq = s.nq; sink.nz = P.vol.nz; sink.j_c = s.j_c; sink.k_c = s.k_c;
+        sink.seglen = (R)s.seglen;
+        const double c0 = mpos ? s.cq : 1.0 - s.cq;
+        if (IS3D) {
+            const int plane = (int)(s.xmajor ? P.plane_xm : P.plane_ym);
+            const uint16_t *W = P.skip[(s.xmajor ? 0 : 2) + (mpos ? 0 : 1)] + (long long)(s.k_c + 1) * plane +
+                                (mpos ? s.j_c : s.nq - 1 - s.j_c) + 1;
+            walk_skip3<R>(W, pitch, plane, s.i0, s.i1, s.i_c, (R)fabs(s.m), (R)c0, (R)s.mz, (R)s.cw, (R)s.ua, (R)s.ub,
+                          (R)s.inv_am, (R)s.inv_amz, acc, 1, sink);
+        } else {
+            const uint16_t *W = P.skip[(s.xmajor ? 0 : 2) + (mpos ? 0 : 1)] + (mpos ? s.j_c : s.nq - 1 - s.j_c) + 1;
+            walk_skip<R>(W, pitch, s.i0, s.i1, s.i_c, (R)fabs(s.m), (R)c0, (R)s.ua, (R)s.ub, (R)s.inv_am, acc, 1, sink);
+        }
+        for (int m = 0; m < K; ++m) acc[m] = Rn<R>::mul(acc[m], (R)s.seglen);
+    }
+    n_steps[t] = sink.n;
+    meta[t] = (s.hit ? 8 : 0) | (s.hit && s.m >= 0.0 ? 4 : 0) | (s.fwd ? 2 : 0) | (s.xmajor ? 1 : 0);
+}
+
 // ---------------------------------------------------------------------------------------------------------
 // Host side
 
@@ -1026,6 +1125,12 @@ static int make_params(const DexctScan *scan, const DexctVolume *vol, const void
     // steepest z slope of any ray of the scan, in planes per column: |gz| / |gp| with |gp| >= SDD / sqrt(dx^2 + dy^2)
     const double zmax = fmax(fabs(scan->z0), fabs(scan->z0 + (scan->n_rows - 1) * scan->dzdet));
     const double muz = zmax / vol->dz * sqrt(vol->dx * vol->dx + vol->dy * vol->dy) / scan->sdd;
+    // the slab traversal (siddon_core.cuh) crosses at most ONE z plane per column: steeper scans -- thin slices under a tall
+    // detector or a short source-detector distance -- would silently drop voxels
+    DEXCT_REQUIRE(scan->n_rows == 1 || muz <= 1.0,
+                  "cone too steep for the slab traversal: a ray climbs up to %.3f slices per column (detector half-height %.4g cm "
+                  "at SDD %.4g cm, dz %.4g cm, dx %.4g cm, dy %.4g cm); at most 1 is supported -- use thicker slices or fewer rows",
+                  muz, zmax, scan->sdd, vol->dz, vol->dx, vol->dy);
     for (int l = 0; l < 4; ++l) {
         double cap = muz > 0 ? floor((l + 1) / muz) : 127.0;
         P.skip_cap[l] = (int)fmin(fmax(cap, 1.0), 127.0);
@@ -1268,6 +1373,36 @@ extern "C" int dexct_siddon_trace(const DexctScan *scan, const DexctVolume *vol,
     } else {
         if (is3d) siddon_trace_kernel<double, true><<<grid, block, 0, st>>>(P, ray_ids, n_rays, max_seg, vox, lab, (double *)len, n_seg);
         else siddon_trace_kernel<double, false><<<grid, block, 0, st>>>(P, ray_ids, n_rays, max_seg, vox, lab, (double *)len, n_seg);
+    }
+    DEXCT_CUDA_OK(cudaGetLastError());
+    return DEXCT_OK;
+}
+
+extern "C" int dexct_siddon_walk_trace(const DexctScan *scan, const DexctVolume *vol, const void *workspace,
+                                       const int64_t *ray_ids, int32_t n_rays, int32_t max_steps, int32_t K, int32_t *col,
+                                       int32_t *run, int64_t *vox, uint8_t *lab, void *len, int32_t *n_steps, int32_t *meta,
+                                       void *L_out, int32_t dtype, void *stream)
+{
+    if (int e = check_device()) return e;
+    SiddonParams P;
+    if (int e = make_params(scan, vol, workspace, P)) return e;
+    DEXCT_REQUIRE(ray_ids && n_steps && meta && L_out, "ray_ids, n_steps, meta and L_out must be non-null");
+    DEXCT_REQUIRE((col && run && vox && lab && len) || (!col && !run && !vox && !lab && !len),
+                  "col, run, vox, lab and len must be all given or all NULL");
+    DEXCT_REQUIRE(n_rays >= 0 && (max_steps > 0 || !col), "n_rays >= 0 and max_steps > 0 required");
+    DEXCT_REQUIRE(K >= 1 && K <= 128, "the skip layouts carry labels below 128: need 1 <= K <= 128 (K=%d)", K);
+    DEXCT_REQUIRE(P.skip[0] != nullptr, "this volume has no skip layouts (a side exceeds %d voxels)", SKIP_MAX_ENTRIES - 1);
+    DEXCT_REQUIRE(dtype == DEXCT_F32 || dtype == DEXCT_F64, "dtype must be DEXCT_F32 or DEXCT_F64");
+    if (n_rays == 0) return DEXCT_OK;
+    cudaStream_t st = (cudaStream_t)stream;
+    const bool is3d = scan_is_3d(*scan, *vol);
+    const int block = 64, grid = (n_rays + block - 1) / block;
+    if (dtype == DEXCT_F32) {
+        if (is3d) siddon_walk_trace_kernel<float, true><<<grid, block, 0, st>>>(P, ray_ids, n_rays, max_steps, K, col, run, vox, lab, (float *)len, n_steps, meta, (float *)L_out);
+        else siddon_walk_trace_kernel<float, false><<<grid, block, 0, st>>>(P, ray_ids, n_rays, max_steps, K, col, run, vox, lab, (float *)len, n_steps, meta, (float *)L_out);
+    } else {
+        if (is3d) siddon_walk_trace_kernel<double, true><<<grid, block, 0, st>>>(P, ray_ids, n_rays, max_steps, K, col, run, vox, lab, (double *)len, n_steps, meta, (double *)L_out);
+        else siddon_walk_trace_kernel<double, false><<<grid, block, 0, st>>>(P, ray_ids, n_rays, max_steps, K, col, run, vox, lab, (double *)len, n_steps, meta, (double *)L_out);
     }
     DEXCT_CUDA_OK(cudaGetLastError());
     return DEXCT_OK;

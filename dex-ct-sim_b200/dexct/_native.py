@@ -44,6 +44,8 @@ SIGNATURES = {
     'dexct_poly_detect': (C.c_int, [_P, C.c_int64, _P, C.c_int32, C.c_int32, _P, C.c_int32, _P, _P, C.c_int32, _P]),
     'dexct_siddon_trace': (C.c_int, [C.POINTER(DexctScan), C.POINTER(DexctVolume), _P, _P, C.c_int32, C.c_int32,
                                      _P, _P, _P, _P, C.c_int32, _P]),
+    'dexct_siddon_walk_trace': (C.c_int, [C.POINTER(DexctScan), C.POINTER(DexctVolume), _P, _P, C.c_int32, C.c_int32, C.c_int32,
+                                          _P, _P, _P, _P, _P, _P, _P, _P, C.c_int32, _P]),
     'dexct_gn_decompose': (C.c_int, [_P, _P, _P, C.c_int32, C.c_int64, C.c_int32, C.c_double, _P, _P, C.c_int32,
                                      C.c_int32, _P]),
     'dexct_gn_scratch_bytes': (C.c_size_t, [C.c_int64, C.c_int32]),

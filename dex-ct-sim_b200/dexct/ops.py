@@ -161,6 +161,46 @@ class Projector:
         return [(vox_h[t, :ns_h[t]], lab_h[t, :ns_h[t]], ln_h[t, :ns_h[t]]) for t in range(n)]
 
 
+    def walk_trace(self, ray_ids, K, max_steps=2048, dtype=F32, steps=True):
+        """Steps of the PRODUCTION walk over the skip layouts for the given rays (dexct_siddon_walk_trace).
+
+        Returns ``(rays, L)``: ``L`` [n, K] per-material lengths summed by the walk, and per ray a dict with ``meta``
+        (xmajor, fwd, mpos, hit) and -- with ``steps`` -- ``col`` int32[s], ``run`` int32[s], ``vox`` int64[s, 3],
+        ``lab`` uint8[s, 3], ``len`` float[s, 3]; without ``steps`` only ``n_steps``."""
+        code = dtype_code(dtype)
+        td = _TORCH_DTYPE[code]
+        ids = torch.as_tensor(np.asarray(ray_ids, dtype=np.int64), device=self.device)
+        n = ids.numel()
+        ns = torch.empty(n, dtype=torch.int32, device=self.device)
+        meta = torch.empty(n, dtype=torch.int32, device=self.device)
+        L = torch.empty((n, K), dtype=td, device=self.device)
+        col = run = vox = lab = ln = None
+        if steps:
+            col = torch.empty((n, max_steps), dtype=torch.int32, device=self.device)
+            run = torch.empty((n, max_steps), dtype=torch.int32, device=self.device)
+            vox = torch.empty((n, max_steps, 3), dtype=torch.int64, device=self.device)
+            lab = torch.empty((n, max_steps, 3), dtype=torch.uint8, device=self.device)
+            ln = torch.empty((n, max_steps, 3), dtype=td, device=self.device)
+        with torch.cuda.device(self.device):
+            N.check(N.lib().dexct_siddon_walk_trace(C.byref(self.scan), C.byref(self.vol), N.ptr(self.workspace), N.ptr(ids), n,
+                                                    max_steps if steps else 0, int(K), N.ptr(col), N.ptr(run), N.ptr(vox), N.ptr(lab),
+                                                    N.ptr(ln), N.ptr(ns), N.ptr(meta), N.ptr(L), code, N.stream_ptr()))
+        ns_h, meta_h = ns.cpu().numpy(), meta.cpu().numpy()
+        if steps and (ns_h > max_steps).any():
+            raise N.DexctError(f'walk trace overflow: a ray takes {ns_h.max()} steps, max_steps={max_steps}')
+        out = []
+        if steps:
+            col_h, run_h, vox_h, lab_h, ln_h = (x.cpu().numpy() for x in (col, run, vox, lab, ln))
+        for t in range(n):
+            m = int(meta_h[t])
+            rec = dict(xmajor=bool(m & 1), fwd=bool(m & 2), mpos=bool(m & 4), hit=bool(m & 8), n_steps=int(ns_h[t]))
+            if steps:
+                k = ns_h[t]
+                rec.update(col=col_h[t, :k], run=run_h[t, :k], vox=vox_h[t, :k], lab=lab_h[t, :k], len=ln_h[t, :k])
+            out.append(rec)
+        return out, L
+
+
 def count_segments(pj, view_begin=0, view_count=None, chunk=1 << 22):
     """Total number of voxel segments (pieces of positive length) of the rays of a view range -- the unit of the
     bytes-per-ray roofline."""

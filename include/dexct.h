@@ -118,6 +118,24 @@ int dexct_siddon_trace(const DexctScan *scan, const DexctVolume *vol, const void
                        const int64_t *ray_ids, int32_t n_rays, int32_t max_seg,
                        int64_t *vox, uint8_t *lab, void *len, int32_t *n_seg, int32_t dtype, void *stream);
 
+/* Debug: the steps of the PRODUCTION walk over the skip layouts (the routine dexct_siddon_poly inlines for phantoms
+ * with labels < 128), recorded by a sink inside that routine.  For ray t the first min(n_steps[t], max_steps) entries
+ * of rows t are valid, in order of increasing column index (the walk's order, whatever the ray's direction):
+ *   col  [n_rays][max_steps]      first column of the step (index along the ray's major axis)
+ *   run  [n_rays][max_steps]      0: one ordinary column, split into its pieces;  S > 0: a homogeneous stretch of S columns
+ *   vox / lab / len [n_rays][max_steps][3]   the pieces in order along the major axis: linear voxel index
+ *        (k*ny + j)*nx + i (-1: apron, outside the volume; for a run: the voxel it starts in), label, length [cm]
+ *   meta [n_rays]   bit 0: x is the major axis, bit 1: the ray travels towards +major, bit 2: non-negative minor slope,
+ *                   bit 3: the ray meets the volume
+ *   L_out [n_rays][K]   per-material lengths [cm] summed by the walk (what the production kernel feeds its epilogue)
+ * col .. len may all be NULL to obtain only n_steps, meta and L_out.  Needs 1 <= K <= 128.
+ * The oracle's voxel sequence of the same ray (north_star: "voxel-crossing index sequences and per-ray material IDs must
+ * match bit-exactly") is compared with these steps in tests/test_gpu_siddon.py.                                       */
+int dexct_siddon_walk_trace(const DexctScan *scan, const DexctVolume *vol, const void *workspace,
+                            const int64_t *ray_ids, int32_t n_rays, int32_t max_steps, int32_t K, int32_t *col, int32_t *run,
+                            int64_t *vox, uint8_t *lab, void *len, int32_t *n_steps, int32_t *meta, void *L_out,
+                            int32_t dtype, void *stream);
+
 /* ---- Gauss-Newton two-basis decomposition: replaces optimize_sino_cpu (matdecomp.py:87-127) --------------- */
 
 /* Per pixel p (P = views*channels, any order): n_iters full-Newton steps on the Poisson likelihood of the two

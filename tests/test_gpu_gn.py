@@ -17,7 +17,7 @@ import torch
 from conftest import scale_rel_err
 from dexct import _native as N
 from dexct import synthetic as S
-from dexct.ops import F32, F64, gn_decompose
+from dexct.ops import F32, F64, Projector, gn_decompose, make_scan
 from oracle import gn_oracle
 
 pytestmark = pytest.mark.gpu
@@ -194,3 +194,51 @@ def test_bin_counts_around_the_constant_bank_limit(nE):
     out32 = gn_decompose(g, i0, mus, 20, dtype=F32).cpu().numpy()
     assert np.isfinite(out32).all()
     assert scale_rel_err(out32, want32) < 1e-5
+
+
+def _sampled_f32_parity(g_dev, i0, mus, n_iters, lines, tol=1e-5):
+    """Single-precision decomposition of a FULL-size problem against the oracle on a sample of its detector lines: the oracle
+    gets exactly the float32 values the kernel read (counts, i0, mus)."""
+    a = gn_decompose(g_dev, i0, mus, n_iters, dtype=F32)
+    g32 = g_dev.float()[:, lines].double().cpu().numpy()                        # what the kernel read, as float64
+    r32 = lambda x: np.asarray(x).astype(np.float32).astype(np.float64)        # noqa: E731
+    with np.errstate(all='ignore'):
+        ref = _oracle(g32, r32(i0), r32(mus), n_iters)
+    got = a[lines].double().cpu().numpy()
+    assert got.shape == ref.shape
+    fin = np.isfinite(ref).all(-1)
+    assert np.isfinite(got[fin]).all()
+    return got, ref, g32
+
+
+def test_c3_full_size_f32_against_the_oracle_on_64_lines():
+    """Config C3 (2048 x 2048 pixel pairs, 120 bins, the fixed 10 iterations BASELINE.json names): the single-precision kernel
+    on the whole problem, compared with the reference restatement on 64 of its 2048 detector lines (131 072 pixels) at 1e-5."""
+    g, i0, mus, a_true = S.gn_problem(2048, 2048)
+    gd = torch.as_tensor(g).cuda()
+    lines = np.linspace(0, 2048, 64, endpoint=False).astype(int)
+    got, ref, _ = _sampled_f32_parity(gd, i0, mus, 10, lines)
+    err = scale_rel_err(got, ref)
+    assert err < 1e-5, f'C3 f32 vs oracle, 64 lines: {err:.3e}'
+
+
+def test_c2_full_size_f32_against_the_oracle_on_64_views():
+    """Config C2: sinograms of the whole 1000-view scan from the projector, decomposed in single precision (10 iterations, air
+    mask off so that every pixel is compared), against the oracle on 64 views.  Pixels with less than one detected photon in
+    either measurement (rays through the steel and titanium inserts) are photon-starved: their Newton iterates are still
+    travelling after 10 steps and the map is chaotic there, so they are held to finiteness only."""
+    from xtomosim.forward_project import spectral_weights
+    import matdecomp
+    ct, ph, lo, hi = S.make_config('C2')
+    scan = make_scan(ct.N_proj, ct.N_channels, ct.gamma_fan, ct.SID, ct.SDD, rotation=ct.rotation)
+    pj = Projector(scan, ph.M, (ph.dx, ph.dy, ph.dz))
+    W = np.stack([spectral_weights(ct, lo), spectral_weights(ct, hi)])
+    counts, _, _ = pj.project(ph.mu_table(lo.E), W, dtype=F32, want_log=False)
+    gd = counts[:, :, 0, :].contiguous()                                       # [2, 1000, 900]
+    _, i0, mus = matdecomp.spectral_tables(ct, lo, hi)
+    views = np.linspace(0, ct.N_proj, 64, endpoint=False).astype(int)
+    got, ref, g32 = _sampled_f32_parity(gd, i0, mus, 10, views)
+    lit = g32.min(axis=0) >= 1.0
+    assert lit.mean() > 0.9
+    err = float(np.max(np.abs(got[lit] - ref[lit])) / np.max(np.abs(ref[lit])))
+    assert err < 1e-5, f'C2 f32 vs oracle, 64 views, lit pixels: {err:.3e}'

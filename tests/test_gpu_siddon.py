@@ -13,7 +13,7 @@ import pytest
 import torch
 
 import oracle
-from conftest import scale_rel_err
+from conftest import elem_rel_err, per_ray_len_err, scale_rel_err
 from dexct import _native as N
 from dexct import synthetic as S
 from dexct.ops import F32, F64, Projector, make_scan, poly_detect
@@ -22,6 +22,12 @@ pytestmark = pytest.mark.gpu
 
 FAN = 0.8230337
 TOL = {F32: 1e-5, F64: 1e-10}
+# element-wise bounds (conftest.elem_rel_err / per_ray_len_err): counts on every pixel within six decades of the air count,
+# lengths of every ray against that ray's own chord.  A short chord is a sum of few voxel pieces, each placed with the
+# absolute accuracy of the column coordinate (2^-24 of the column count in single precision), so the per-chord bound of
+# short rays is looser than the scale-relative one by the ratio of the chords.
+TOL_ELEM = {F32: 1e-5, F64: 1e-10}
+TOL_RAY = {F32: 2e-5, F64: 1e-10}
 
 
 def _labels(n, nz, K, seed=3):
@@ -83,6 +89,128 @@ def test_voxel_sequences_bit_exact(dtype, nz, n_rows):
     assert n_seg > 50 * len(ids)
 
 
+def _check_production_walk(pj, sc, ids, dtype, K, shape):
+    """The steps the PRODUCTION walk (walk_skip / walk_skip3 over the skip layouts, recorded by a sink inside the routine the
+    production kernels inline) takes along each ray, against the oracle's voxel sequence of the same ray:
+    * the steps tile the ray's column range without gap or overlap;
+    * an ordinary column names exactly the oracle's voxels of that column, in order, with their labels (bit-exact indices
+      and material ids; lengths to rounding -- the walk computes them from differently grouped operations);
+    * a homogeneous stretch of S columns covers oracle voxels of ONE label only -- the one the walk books it to -- and its
+      length is the sum of theirs;
+    * hence the run-length-compressed material-id sequence of the ray is identical.
+    Returns (steps, voxels, homogeneous steps)."""
+    nz, ny, nx = shape
+    f64 = dtype == F64
+    recs, L = pj.walk_trace(ids, K, max_steps=4096, dtype=dtype)
+    L = L.cpu().numpy().astype(np.float64)
+    n_steps = n_vox = n_hom = 0
+    for t, (rid, rec) in enumerate(zip(ids, recs)):
+        c = int(rid % sc.n_ch)
+        row = int((rid // sc.n_ch) % sc.n_rows)
+        v = int(rid // (sc.n_ch * sc.n_rows))
+        w_vox, w_lab, w_len = sc.slab_trace(v, row, c, f64)
+        tag = (int(rid), v, row, c)
+        if not rec['hit']:
+            assert len(w_vox) == 0 and rec['n_steps'] == 0, tag
+            continue
+        if not rec['fwd']:                                    # the walk always runs towards +major
+            w_vox, w_lab, w_len = w_vox[::-1], w_lab[::-1], w_len[::-1]
+        o_col = (w_vox % nx) if rec['xmajor'] else ((w_vox // nx) % ny)
+        total = float(w_len.sum())
+        tiny = (2e-6 if not f64 else 1e-12) * max(total, 1e-3)
+        keep = w_len > tiny
+        o_vox, o_lab, o_len, o_col = w_vox[keep], w_lab[keep], w_len[keep], o_col[keep]
+        assert (np.diff(o_col) >= 0).all(), tag
+        pos = 0
+        nxt = int(rec['col'][0])
+        got_labels, want_labels = [], []
+        for s_col, s_run, s_vox, s_lab, s_len in zip(rec['col'], rec['run'], rec['vox'], rec['lab'], rec['len']):
+            assert int(s_col) == nxt, tag
+            s_len = s_len.astype(np.float64)
+            if s_run > 0:
+                n_hom += 1
+                end = pos
+                while end < len(o_col) and o_col[end] < s_col + s_run:
+                    end += 1
+                lab0 = int(s_lab[0])
+                assert (s_lab == lab0).all(), tag
+                assert (o_lab[pos:end] == lab0).all(), (tag, int(s_col), int(s_run))
+                assert abs(float(s_len.sum()) - float(o_len[pos:end].sum())) <= 4 * tiny + 1e-6 * (not f64) * float(s_len.sum()), tag
+                if s_len.sum() > tiny:
+                    got_labels.append(lab0)
+                want_labels.extend(int(x) for x in o_lab[pos:end])
+                pos = end
+                nxt = int(s_col) + int(s_run)
+            else:
+                end = pos
+                while end < len(o_col) and o_col[end] == s_col:
+                    end += 1
+                live = (s_len > tiny) & (s_vox >= 0)
+                assert np.array_equal(s_vox[live], o_vox[pos:end]), (tag, int(s_col), s_vox, s_len, o_vox[pos:end], o_len[pos:end])
+                assert np.array_equal(s_lab[live], o_lab[pos:end]), (tag, int(s_col))
+                assert np.max(np.abs(s_len[live] - o_len[pos:end]), initial=0.0) <= 4 * tiny, (tag, int(s_col))
+                got_labels.extend(int(x) for x in s_lab[live])
+                want_labels.extend(int(x) for x in o_lab[pos:end])
+                n_vox += end - pos
+                pos = end
+                nxt = int(s_col) + 1
+        assert pos == len(o_col), tag
+        rle = lambda a: [x for i, x in enumerate(a) if i == 0 or x != a[i - 1]]          # noqa: E731
+        assert rle(got_labels) == rle(want_labels), tag
+        # and the walk's per-material sums are the oracle's, label by label
+        want_L = np.bincount(w_lab, weights=w_len, minlength=K)[:K]
+        assert np.max(np.abs(L[t] - want_L)) <= (3e-6 if not f64 else 1e-11) * max(total, 1e-3) * 4, tag
+        n_steps += rec['n_steps']
+    return n_steps, n_vox, n_hom
+
+
+@pytest.mark.parametrize('dtype', [F32, F64])
+@pytest.mark.parametrize('nz,n_rows', [(1, 1), (16, 6)])
+def test_production_walk_sequences_random_labels(dtype, nz, n_rows):
+    """Same ray set as test_voxel_sequences_bit_exact, through the production walk (few homogeneous stretches: random labels)."""
+    pj, sc = _pair(nz=nz, n_rows=n_rows)
+    r = np.random.default_rng(11)
+    n_all = sc.n_views * sc.n_rows * sc.n_ch
+    ids = np.unique(np.concatenate([r.integers(0, n_all, 1500),
+                                    [((v * sc.n_rows + row) * sc.n_ch + c) for v in (0, 9, 18, 27, 4, 5)
+                                     for row in (0, sc.n_rows - 1) for c in (0, 59, 60, 119)]]))
+    n_steps, n_vox, n_hom = _check_production_walk(pj, sc, ids, dtype, 4, (nz, 96, 96))
+    assert n_vox > 40 * len(ids) and n_hom > 0
+
+
+@pytest.mark.parametrize('dtype', [F32, F64])
+@pytest.mark.parametrize('nz,n_rows,h_iso,voxz', [(1, 1, 0.4, 0.1), (48, 16, 1.2, 51.2 / 96), (48, 16, 0.5, 0.2)])
+def test_production_walk_sequences_anatomy_like(dtype, nz, n_rows, h_iso, voxz):
+    """Body ellipsoid + inserts: most of every ray is covered by homogeneous stretches, at all z-homogeneity levels."""
+    n, n_ch, n_views = 96, 110, 24
+    lab = S.phantom_labels(n, nz)
+    vox = 51.2 / n
+    voxel = (vox, vox, voxz)
+    scan = make_scan(n_views, n_ch, FAN, 60.0, 100.0, n_rows=n_rows, h_iso=h_iso, beta0=0.1)
+    pj = Projector(scan, lab, voxel)
+    sc = oracle.Scan(lab, voxel, 60.0, 100.0, pj.tables_host())
+    r = np.random.default_rng(5)
+    ids = np.unique(r.integers(0, n_views * n_rows * n_ch, 1200))
+    n_steps, n_vox, n_hom = _check_production_walk(pj, sc, ids, dtype, S.K, (nz, n, n))
+    assert n_hom > 2 * len(ids)
+    # the point of the layouts: far fewer steps than voxels crossed
+    segs = sum(len(sc.slab_trace(int(i // (n_ch * n_rows)), int((i // n_ch) % n_rows), int(i % n_ch), dtype == F64)[0]) for i in ids[:200])
+    steps = sum(rec['n_steps'] for rec in pj.walk_trace(ids[:200], S.K, dtype=dtype, steps=False)[0])
+    assert steps < 0.6 * segs
+
+
+def test_production_walk_degenerate_rays():
+    """Rays along grid planes, through voxel corners, axis-parallel (the set of test_degenerate_rays_bit_exact)."""
+    for n, n_ch, fov, beta0 in ((64, 9, 64.0, 0.0), (65, 9, 65.0, 0.0), (64, 8, 64.0, np.pi / 4), (64, 9, 200.0, 0.0)):
+        lab = _labels(n, 1, 4)
+        vox = fov / n
+        scan = make_scan(8, n_ch, 0.4, 60.0, 100.0, beta0=beta0)
+        pj = Projector(scan, lab, (vox, vox, 0.1))
+        sc = oracle.Scan(lab, (vox, vox, 0.1), 60.0, 100.0, pj.tables_host())
+        for dtype in (F32, F64):
+            _check_production_walk(pj, sc, np.arange(8 * n_ch), dtype, 4, (1, n, n))
+
+
 def test_degenerate_rays_bit_exact():
     """Rays along grid planes, through voxel corners, axis-parallel; even and odd grids; source inside the volume."""
     for n, n_ch, fov, beta0 in ((64, 9, 64.0, 0.0), (65, 9, 65.0, 0.0), (64, 8, 64.0, np.pi / 4), (64, 9, 200.0, 0.0)):
@@ -122,8 +250,12 @@ def test_lengths_counts_logs_vs_siddon1985(dtype, nz, n_rows, K):
     L_ref, seg = sc.classic_lengths(K)
     assert seg > 0
     assert scale_rel_err(L.cpu().numpy(), L_ref) < TOL[dtype]
+    e_ray = per_ray_len_err(L.cpu().numpy(), L_ref)
+    assert e_ray < TOL_RAY[dtype], f'per-ray length error {e_ray:.3e}'
     c_ref, l_ref, _ = sc.project_poly(mu, W)
     assert scale_rel_err(counts.cpu().numpy(), c_ref) < TOL[dtype]
+    e_cnt = elem_rel_err(counts.cpu().numpy(), c_ref)
+    assert e_cnt < TOL_ELEM[dtype], f'element-wise count error {e_cnt:.3e}'
     # the log sinogram is O(1..10): absolute error of tol x its scale
     assert scale_rel_err(logs.cpu().numpy(), l_ref) < (1e-9 if dtype == F64 else 3e-5)
     # detection from the stored lengths reproduces the fused epilogue
@@ -185,6 +317,14 @@ def test_argument_errors_are_reported():
     pj.labels[0, 5, 5] = 1
     pj.prepare()
     assert torch.isfinite(pj.project(mu, W)[0]).all()
+    # a cone so steep that a ray would cross more than one slice per column is refused, not traced wrongly (the slab
+    # traversal assumes at most one z crossing per column): 5 micrometre slices under an 8-row detector
+    scan = make_scan(12, 40, FAN, 60.0, 100.0, n_rows=8, h_iso=1.0)
+    with pytest.raises(N.DexctError, match='cone too steep'):
+        Projector(scan, _labels(32, 6, 4), (1.6, 1.6, 0.005)).project(mu, W)
+    # ... while the same thin slices under a single-row detector are an ordinary 2-D scan
+    scan1 = make_scan(12, 40, FAN, 60.0, 100.0, n_rows=1)
+    assert torch.isfinite(Projector(scan1, _labels(32, 1, 4), (1.6, 1.6, 0.005)).project(mu, W)[0]).all()
 
 
 # ---- full-size properties ---------------------------------------------------------------------------------------
@@ -225,6 +365,11 @@ def test_c2_full_size_chord_conservation_and_linearity(dtype):
     c_ref, l_ref, seg = sc.project_poly(mu, W)
     assert 500 < seg / (8 * 900) < 700
     assert scale_rel_err(counts[:, ::125].cpu().numpy(), c_ref) < TOL[dtype]
+    e_cnt = elem_rel_err(counts[:, ::125].cpu().numpy(), c_ref)
+    assert e_cnt < TOL_ELEM[dtype], f'element-wise count error {e_cnt:.3e}'
+    L_ref, _ = sc.classic_lengths(S.K)
+    e_ray = per_ray_len_err(L[::125].cpu().numpy(), L_ref)
+    assert e_ray < TOL_RAY[dtype], f'per-ray length error {e_ray:.3e}'
     # homogeneous phantom: closed form
     uni = np.ones_like(ph.M)
     pj1 = Projector(scan, uni, (ph.dx, ph.dy, ph.dz))
@@ -270,8 +415,12 @@ def test_steep_cone_on_anatomy_like_volume(dtype, h_iso, voxz):
     L_ref, seg = sc.classic_lengths(S.K)
     assert seg > 0
     assert scale_rel_err(L.cpu().numpy(), L_ref) < TOL[dtype]
+    e_ray = per_ray_len_err(L.cpu().numpy(), L_ref)
+    assert e_ray < TOL_RAY[dtype], f'per-ray length error {e_ray:.3e}'
     c_ref, l_ref, _ = sc.project_poly(mu, W)
     assert scale_rel_err(counts.cpu().numpy(), c_ref) < TOL[dtype]
+    e_cnt = elem_rel_err(counts.cpu().numpy(), c_ref)
+    assert e_cnt < TOL_ELEM[dtype], f'element-wise count error {e_cnt:.3e}'
 
 
 @pytest.mark.parametrize('name', ['C4', 'C5'])
@@ -342,8 +491,12 @@ def test_up_to_256_materials(dtype, nz, n_rows, K):
     L_ref, seg = sc.classic_lengths(K)
     assert seg > 0 and L_ref[..., K - 1].max() > 0                                 # the highest label is really met
     assert scale_rel_err(L.cpu().numpy(), L_ref) < TOL[dtype]
+    e_ray = per_ray_len_err(L.cpu().numpy(), L_ref)
+    assert e_ray < TOL_RAY[dtype], f'per-ray length error {e_ray:.3e}'
     c_ref, l_ref, _ = sc.project_poly(mu, W)
     assert scale_rel_err(counts.cpu().numpy(), c_ref) < TOL[dtype]
+    e_cnt = elem_rel_err(counts.cpu().numpy(), c_ref)
+    assert e_cnt < TOL_ELEM[dtype], f'element-wise count error {e_cnt:.3e}'
     assert scale_rel_err(logs.cpu().numpy(), l_ref) < (1e-9 if dtype == F64 else 3e-5)
     c2, l2 = poly_detect(L, mu, W, dtype=dtype)
     assert scale_rel_err(c2.cpu().numpy(), counts.cpu().numpy()) < (1e-14 if dtype == F64 else 1e-6)
@@ -369,8 +522,12 @@ def test_rectangular_volumes_and_anisotropic_voxels(dtype, shape, voxel, n_rows)
     L_ref, seg = sc.classic_lengths(6)
     assert seg > 0
     assert scale_rel_err(L.cpu().numpy(), L_ref) < TOL[dtype]
+    e_ray = per_ray_len_err(L.cpu().numpy(), L_ref)
+    assert e_ray < TOL_RAY[dtype], f'per-ray length error {e_ray:.3e}'
     c_ref, l_ref, _ = sc.project_poly(mu, W)
     assert scale_rel_err(counts.cpu().numpy(), c_ref) < TOL[dtype]
+    e_cnt = elem_rel_err(counts.cpu().numpy(), c_ref)
+    assert e_cnt < TOL_ELEM[dtype], f'element-wise count error {e_cnt:.3e}'
     assert scale_rel_err(logs.cpu().numpy(), l_ref) < (1e-9 if dtype == F64 else 3e-5)
     # a view range on its own equals the same views inside the whole scan
     c_part, _, _ = pj.project(mu, W, view_begin=7, view_count=9, dtype=dtype)
@@ -390,7 +547,11 @@ def test_tiny_and_lopsided_sizes(dtype, n, nz, n_ch, n_views, n_rows, h_iso):
     assert counts.shape == (2, n_views, n_rows, n_ch) and L.shape == (n_views, n_rows, n_ch, 5)
     L_ref, seg = sc.classic_lengths(5)
     assert scale_rel_err(L.cpu().numpy(), L_ref) < TOL[dtype]
+    e_ray = per_ray_len_err(L.cpu().numpy(), L_ref)
+    assert e_ray < TOL_RAY[dtype], f'per-ray length error {e_ray:.3e}'
     c_ref, l_ref, _ = sc.project_poly(mu, W)
     assert scale_rel_err(counts.cpu().numpy(), c_ref) < TOL[dtype]
+    e_cnt = elem_rel_err(counts.cpu().numpy(), c_ref)
+    assert e_cnt < TOL_ELEM[dtype], f'element-wise count error {e_cnt:.3e}'
     # (absolute where the log sinogram is ~0: the outer rows of case 33-1-7-3-4 miss the 1 mm slab, the inner ones leave it half way)
     assert np.max(np.abs(logs.cpu().numpy() - l_ref)) < (1e-9 if dtype == F64 else 3e-5) * max(1.0, np.abs(l_ref).max())

@@ -40,6 +40,11 @@ def main():
     ms = e0.elapsed_time(e1) / reps
     rays = nv * ct.N_rows * ct.N_channels
     seg = count_segments(pj, v0, min(nv, 4)) / (min(nv, 4) * ct.N_rows * ct.N_channels)
+    # steps of the production walk (homogeneous stretches and ordinary columns) on one view of the range
+    ids = np.arange(v0 * pj.rays_per_view, (v0 + 1) * pj.rays_per_view, 7, dtype=np.int64)
+    recs, _ = pj.walk_trace(ids, 8, dtype='f32', steps=False)
+    steps = float(np.mean([r['n_steps'] for r in recs]))
+    print(f'{name} view {v0}: {steps:.1f} walk steps per ray (sample of {len(ids)} rays)')
     print(f'{name} views [{v0}, {v0 + nv}): {ms:.4f} ms per launch, {rays / ms / 1e6:.3f} Grays/s, {seg:.1f} segments per ray, '
           f'{rays * (seg + 8) / ms / 1e6:.1f} GB/s algorithmic, checksum {float(counts.sum()):.6e}')
 
