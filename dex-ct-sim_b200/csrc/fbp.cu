@@ -68,13 +68,30 @@ __global__ void fbp_setup_kernel(DexctScan s, int view_begin, int view_count, do
     }
 }
 
+// Short scans (total rotation below a full turn): Parker's weights in the form that takes any range pi + 2 delta with
+// delta >= half the fan angle; conjugate of ray (b, gamma) is (b + pi + 2 gamma, -gamma) for a source moving towards +beta,
+// a scan towards -beta is the mirror image (gamma -> -gamma).  The full-turn formula carries 1/2 for the double coverage, so
+// the weights are applied twice over.  delta < 0: full turn, weight 1.  Same expressions as oracle/fbp_oracle.py parker().
+struct FbpParker { double delta, absdb; int view0, sign; };
+__device__ __forceinline__ double fbp_parker2(const FbpParker &p, long long view_rel, double gamma)
+{
+    if (p.delta < 0.0) return 1.0;
+    const double PI = 3.14159265358979323846;
+    const double g = p.sign >= 0 ? gamma : -gamma;
+    const double b = (double)(p.view0 + view_rel) * p.absdb;
+    double w = 1.0;
+    if (b < 2.0 * p.delta - 2.0 * g) { const double sn = sin(0.25 * PI * b / fmax(p.delta - g, 1e-300)); w = sn * sn; }
+    if (b > PI - 2.0 * g) { const double sn = sin(0.25 * PI * (PI + 2.0 * p.delta - b) / fmax(p.delta + g, 1e-300)); w = sn * sn; }
+    return 2.0 * w;
+}
+
 // One detector line (view, row) per CTA: pre-weight into shared memory, then the convolution with the taps.
 // Thread t produces channels t, t + blockDim, ...: the tap reads of a warp are consecutive words (conflict-free) and
 // the line element is a broadcast.
 template <typename R>
 __global__ void __launch_bounds__(256) fbp_filter_kernel(const R *__restrict__ sino, int n_ch, double gamma0, double dgamma,
                                                          double sid, const R *__restrict__ taps, R *__restrict__ q, int q_pitch,
-                                                         int n_rows, int row_pitch)
+                                                         int n_rows, int row_pitch, const FbpParker pk)
 {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     R *line = (R *)smem_raw;                 // [n_ch]
@@ -82,7 +99,7 @@ __global__ void __launch_bounds__(256) fbp_filter_kernel(const R *__restrict__ s
     const long long ln = blockIdx.x;
     const R *src = sino + ln * n_ch;
     for (int c = threadIdx.x; c < n_ch; c += blockDim.x)
-        line[c] = src[c] * (R)(sid * cos(gamma0 + (double)c * dgamma));
+        line[c] = src[c] * (R)(sid * cos(gamma0 + (double)c * dgamma) * fbp_parker2(pk, ln / n_rows, gamma0 + (double)c * dgamma));
     for (int t = threadIdx.x; t < 2 * n_ch - 1; t += blockDim.x) g[t] = taps[t];
     __syncthreads();
     // row_pitch == 0: line-major q[line][q_pitch]; else row-fastest q[view][plane][row_pitch] (plane = channel + 1)
@@ -126,7 +143,7 @@ constexpr int FBP_FL = 8;                                     // lines per CTA
 template <typename R>
 __global__ void __launch_bounds__(256) fbp_filter8_kernel(const R *__restrict__ sino, long long n_lines, int n_ch, double gamma0,
                                                           double dgamma, double sid, const R *__restrict__ taps,
-                                                          R *__restrict__ q, int q_pitch, int n_rows, int row_pitch)
+                                                          R *__restrict__ q, int q_pitch, int n_rows, int row_pitch, const FbpParker pk)
 {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     const int n_chp = (n_ch + 7) & ~7;
@@ -138,7 +155,9 @@ __global__ void __launch_bounds__(256) fbp_filter8_kernel(const R *__restrict__ 
     for (int i = threadIdx.x; i < FBP_FL * n_chp; i += blockDim.x) {
         const int r = i / n_chp, c = i - r * n_chp;
         R v = (R)0;
-        if (c < n_ch && ln0 + r < n_lines) v = sino[(ln0 + r) * n_ch + c] * (R)(sid * cos(gamma0 + (double)c * dgamma));
+        if (c < n_ch && ln0 + r < n_lines)
+            v = sino[(ln0 + r) * n_ch + c] *
+                (R)(sid * cos(gamma0 + (double)c * dgamma) * fbp_parker2(pk, (ln0 + r) / n_rows, gamma0 + (double)c * dgamma));
         line[r * lstride + c] = v;
     }
     for (int i = threadIdx.x; i < 2 * n_chp + 8; i += blockDim.x) {
@@ -513,6 +532,19 @@ static int fbp_run(const DexctScan &s, const void *sino, int view_begin, int vie
                    void *image, int accumulate, void *scratch, int dtype, cudaStream_t st)
 {
     const FbpLayout L = fbp_layout(s, view_count, dtype);
+    // total rotation of the scan: one full turn (no weighting), or a short scan of at least pi + fan (Parker weights)
+    const double PI = 3.14159265358979323846;
+    const double total = fabs(s.dbeta) * (double)s.n_views;
+    const double half_fan = fmax(fabs(s.gamma0), fabs(s.gamma0 + (s.n_ch - 1) * s.dgamma));
+    FbpParker pk{-1.0, fabs(s.dbeta), view_begin, s.dbeta >= 0 ? 1 : -1};
+    if (fabs(total - 2.0 * PI) > 1e-6) {
+        if (!(total < 2.0 * PI && 0.5 * (total - PI) >= half_fan - 1e-12)) {
+            set_error("total rotation %.6f rad: get_recon takes one full turn (2 pi) or a short scan of at least pi + fan angle = "
+                      "%.6f rad and less than 2 pi", total, PI + 2.0 * half_fan);
+            return DEXCT_EINVAL;
+        }
+        pk.delta = 0.5 * (total - PI);
+    }
     char *w = (char *)scratch;
     R *cs = (R *)(w + L.off_cs), *taps = (R *)(w + L.off_taps), *q = (R *)(w + L.off_q);
     const int nset = max(view_count, 2 * s.n_ch - 1);
@@ -543,10 +575,10 @@ static int fbp_run(const DexctScan &s, const void *sino, int view_begin, int vie
             if (smem8 > 48 * 1024)
                 DEXCT_CUDA_OK(cudaFuncSetAttribute(fbp_filter8_kernel<R>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem8));
             fbp_filter8_kernel<R><<<(unsigned)((n_lines + FBP_FL - 1) / FBP_FL), 256, smem8, st>>>(
-                (const R *)sino, n_lines, s.n_ch, s.gamma0, s.dgamma, s.sid, taps, q, L.q_pitch, s.n_rows, row_pitch);
+                (const R *)sino, n_lines, s.n_ch, s.gamma0, s.dgamma, s.sid, taps, q, L.q_pitch, s.n_rows, row_pitch, pk);
         } else {
             fbp_filter_kernel<R><<<(unsigned)n_lines, 256, smem, st>>>(
-                (const R *)sino, s.n_ch, s.gamma0, s.dgamma, s.sid, taps, q, L.q_pitch, s.n_rows, row_pitch);
+                (const R *)sino, s.n_ch, s.gamma0, s.dgamma, s.sid, taps, q, L.q_pitch, s.n_rows, row_pitch, pk);
         }
     }
     DEXCT_CUDA_OK(cudaGetLastError());
@@ -561,7 +593,7 @@ static int fbp_run(const DexctScan &s, const void *sino, int view_begin, int vie
         else if (rpl == 2) kern = fast ? fbp_backproject_warprows_kernel<R, sizeof(R) == 4, 2> : fbp_backproject_warprows_kernel<R, false, 2>;
         else if (fast) kern = fbp_backproject_warprows_kernel<R, sizeof(R) == 4, 1>;
         kern<<<grid, 256, 0, st>>>(q, row_pitch, cs, view_count, s.n_rows, s.n_ch, (R)s.sid, (R)s.gamma0, (R)(1.0 / s.dgamma),
-                                   n, (R)(fov / n), (R)s.dbeta, accumulate, (R *)image);
+                                   n, (R)(fov / n), (R)fabs(s.dbeta), accumulate, (R *)image);
         DEXCT_CUDA_OK(cudaGetLastError());
         return DEXCT_OK;
     }
@@ -571,7 +603,7 @@ static int fbp_run(const DexctScan &s, const void *sino, int view_begin, int vie
         if (rb == 16) kern = fast ? fbp_backproject_rows_kernel<R, sizeof(R) == 4, 16> : fbp_backproject_rows_kernel<R, false, 16>;
         else if (fast) kern = fbp_backproject_rows_kernel<R, sizeof(R) == 4, 8>;
         kern<<<grid, block, 0, st>>>(q, row_pitch, cs, view_count, s.n_rows, s.n_ch, (R)s.sid, (R)s.gamma0, (R)(1.0 / s.dgamma),
-                                     n, (R)(fov / n), (R)s.dbeta, accumulate, (R *)image);
+                                     n, (R)(fov / n), (R)fabs(s.dbeta), accumulate, (R *)image);
         DEXCT_CUDA_OK(cudaGetLastError());
         return DEXCT_OK;
     }
@@ -584,7 +616,7 @@ static int fbp_run(const DexctScan &s, const void *sino, int view_begin, int vie
         auto kern = fbp_backproject_sym4_kernel<R, false>;
         if (fast) kern = fbp_backproject_sym4_kernel<R, sizeof(R) == 4>;
         kern<<<grid, block, 0, st>>>(q, L.q_pitch, cs, s.n_views, s.n_rows, s.n_ch, (R)s.sid, (R)s.gamma0, (R)(1.0 / s.dgamma),
-                                     n, (R)(fov / n), (R)s.dbeta, accumulate, turn_angle > 0 ? 1 : -1, (R *)image);
+                                     n, (R)(fov / n), (R)fabs(s.dbeta), accumulate, turn_angle > 0 ? 1 : -1, (R *)image);
         DEXCT_CUDA_OK(cudaGetLastError());
         return DEXCT_OK;
     }
@@ -592,7 +624,7 @@ static int fbp_run(const DexctScan &s, const void *sino, int view_begin, int vie
     auto kern = fbp_backproject_kernel<R, false>;
     if (fast) kern = fbp_backproject_kernel<R, sizeof(R) == 4>;
     kern<<<grid, block, 0, st>>>(q, L.q_pitch, cs, view_count, s.n_rows, s.n_ch, (R)s.sid, (R)s.gamma0, (R)(1.0 / s.dgamma), n,
-                                 (R)(fov / n), (R)s.dbeta, accumulate, (R *)image);
+                                 (R)(fov / n), (R)fabs(s.dbeta), accumulate, (R *)image);
     DEXCT_CUDA_OK(cudaGetLastError());
     return DEXCT_OK;
 }

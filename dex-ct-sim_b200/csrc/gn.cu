@@ -719,6 +719,89 @@ __global__ void __launch_bounds__(GT_THREADS) gn_tc_kernel(const float *__restri
     if (warp == 4) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"(GT_COLS) : "memory");
 }
 
+// ---------------------------------------------------------------------------------------------------------------------
+// General form of optimize_sino_cpu (matdecomp.py:87-127 as written: any number of measurements and basis materials, and
+// a spectrum PER DETECTOR BIN, i0 [nMeas][nBins][nE] -- :101-105,118 broadcast a per-bin i0, :95,125 invert an
+// [nBins, nMats, nMats] stack).  get_basismat_sinos never needs it (two measurements, two materials, one spectrum tiled
+// over the bins, :151) and takes the specialised kernels above; this one keeps the drop-in's signature honest.  One thread
+// per pixel, arithmetic in float64 whatever the I/O type, the reference's exponent clip, Gaussian elimination with
+// partial pivoting for the nMats x nMats Newton system.
+constexpr int GG_MAX = 4;
+template <typename R>
+__global__ void __launch_bounds__(128) gn_general_kernel(const R *__restrict__ g, const R *__restrict__ i0, const R *__restrict__ mus,
+                                                         int nMeas, int nMats, int nE, long long n_bins, long long i0_bin_stride,
+                                                         long long P, int n_iters, R *__restrict__ a_out)
+{
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    double *mu_s = (double *)smem_raw;                        // [nMats][nE]
+    for (int t = threadIdx.x; t < nMats * nE; t += blockDim.x) mu_s[t] = (double)mus[t];
+    __syncthreads();
+    const long long p = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (p >= P) return;
+    const long long bin = p % n_bins;                          // sinogram pixels are [views][bins]
+    double a[GG_MAX], gm[GG_MAX];
+    for (int q = 0; q < GG_MAX; ++q) a[q] = 1e-6;              // matdecomp.py:98
+    for (int m = 0; m < nMeas; ++m) gm[m] = (double)g[(long long)m * P + p];
+    for (int it = 0; it < n_iters; ++it) {
+        double nu[GG_MAX], gr[GG_MAX][GG_MAX], hs[GG_MAX][GG_MAX][GG_MAX];
+        for (int m = 0; m < GG_MAX; ++m) {
+            nu[m] = 0.0;
+            for (int u = 0; u < GG_MAX; ++u) {
+                gr[m][u] = 0.0;
+                for (int w = 0; w < GG_MAX; ++w) hs[m][u][w] = 0.0;
+            }
+        }
+        for (int e = 0; e < nE; ++e) {
+            double x = 0.0;
+            for (int u = 0; u < nMats; ++u) x -= a[u] * mu_s[u * nE + e];
+            const double att = exp(fmin(fmax(x, -700.0), 700.0));                                   // :116
+            for (int m = 0; m < nMeas; ++m) {
+                const double w = (double)i0[((long long)m * n_bins + bin) * i0_bin_stride + e] * att;
+                nu[m] += w;                                                                         // :118
+                for (int u = 0; u < nMats; ++u) {
+                    const double wu = w * mu_s[u * nE + e];
+                    gr[m][u] += wu;                                                                 // -nu_grad, :119
+                    for (int v = u; v < nMats; ++v) hs[m][u][v] += wu * mu_s[v * nE + e];           // :120
+                }
+            }
+        }
+        // dF_u = -sum_m r_m nu_grad_mu = sum_m r_m gr_mu;   H_uv = -sum_m (r_m hs_muv - g_m/nu_m^2 gr_mu gr_mv)    (:122-123)
+        double H[GG_MAX][GG_MAX + 1];
+        for (int u = 0; u < nMats; ++u)
+            for (int v = 0; v <= nMats; ++v) H[u][v] = 0.0;
+        for (int m = 0; m < nMeas; ++m) {
+            const double r = gm[m] / nu[m] - 1.0, s2 = gm[m] / (nu[m] * nu[m]);
+            for (int u = 0; u < nMats; ++u) {
+                H[u][nMats] += r * gr[m][u];
+                for (int v = 0; v < nMats; ++v) {
+                    const double h = u <= v ? hs[m][u][v] : hs[m][v][u];
+                    H[u][v] += -(r * h) + s2 * gr[m][u] * gr[m][v];
+                }
+            }
+        }
+        // solve H d = dF (augmented column), partial pivoting; a -= d   (:125)
+        for (int c = 0; c < nMats; ++c) {
+            int piv = c;
+            for (int u = c + 1; u < nMats; ++u)
+                if (fabs(H[u][c]) > fabs(H[piv][c])) piv = u;
+            if (piv != c)
+                for (int v = 0; v <= nMats; ++v) { const double t = H[c][v]; H[c][v] = H[piv][v]; H[piv][v] = t; }
+            const double inv = 1.0 / H[c][c];
+            for (int u = c + 1; u < nMats; ++u) {
+                const double f = H[u][c] * inv;
+                for (int v = c; v <= nMats; ++v) H[u][v] -= f * H[c][v];
+            }
+        }
+        for (int c = nMats - 1; c >= 0; --c) {
+            double d = H[c][nMats];
+            for (int v = c + 1; v < nMats; ++v) d -= H[c][v] * H[v][nMats];
+            H[c][nMats] = d / H[c][c];
+        }
+        for (int u = 0; u < nMats; ++u) a[u] -= H[u][nMats];
+    }
+    for (int u = 0; u < nMats; ++u) a_out[p * nMats + u] = (R)a[u];
+}
+
 // Float64 pass over the pixels the single-precision kernel flagged (scratch: [2] = count, [4 ...] = pixel ids): the same
 // Newton iteration in double precision with the reference's exponent clip, on the same (float) inputs.  These are
 // photon-starved or metal-crossing pixels whose iterates leave the float range; the reference's float64 result for them is
@@ -1009,4 +1092,38 @@ extern "C" int dexct_gn_decompose_fused_push(const void *g, const void *i0, cons
         }
     }
     return gn_decompose_impl(g, i0, mus, nE, P, n_iters, mask_thresh, a_out, mir, rider, scratch, scratch_has_max, dtype, stream);
+}
+
+extern "C" int dexct_gn_decompose_general(const void *g, const void *i0, const void *mus, int32_t nMeas, int32_t nMats, int32_t nE,
+                                          int64_t n_bins, int32_t i0_per_bin, int64_t P, int32_t n_iters, void *a_out, int32_t dtype,
+                                          void *stream)
+{
+    if (int e = check_device()) return e;
+    DEXCT_REQUIRE(nMeas >= 1 && nMeas <= GG_MAX && nMats >= 1 && nMats <= GG_MAX,
+                  "1 to %d measurements and basis materials are supported (nMeas=%d nMats=%d)", GG_MAX, nMeas, nMats);
+    DEXCT_REQUIRE(nE >= 1 && P >= 0 && n_iters >= 0 && n_bins >= 1, "need nE >= 1, P >= 0, n_iters >= 0, n_bins >= 1");
+    DEXCT_REQUIRE(P % n_bins == 0, "P = %lld pixels is not a whole number of views of %lld bins", (long long)P, (long long)n_bins);
+    DEXCT_REQUIRE(dtype == DEXCT_F32 || dtype == DEXCT_F64, "dtype must be DEXCT_F32 or DEXCT_F64");
+    if (P == 0) return DEXCT_OK;
+    DEXCT_REQUIRE(g && i0 && mus && a_out, "g, i0, mus and a_out must be non-null");
+    const size_t smem = sizeof(double) * (size_t)nMats * nE;
+    if (smem > 200 * 1024) {
+        set_error("basis table needs %zu bytes of shared memory (limit 200 KiB): nMats=%d nE=%d", smem, nMats, nE);
+        return DEXCT_ECAPACITY;
+    }
+    cudaStream_t st = (cudaStream_t)stream;
+    // one spectrum for all bins: the bin index is folded away by a zero "bins" extent
+    const long long pix_bins = i0_per_bin ? n_bins : 1;
+    const unsigned grid = (unsigned)((P + 127) / 128);
+    if (dtype == DEXCT_F32) {
+        if (smem > 48 * 1024) DEXCT_CUDA_OK(cudaFuncSetAttribute(gn_general_kernel<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        gn_general_kernel<float><<<grid, 128, smem, st>>>((const float *)g, (const float *)i0, (const float *)mus, nMeas, nMats, nE,
+                                                        pix_bins, (long long)nE, P, n_iters, (float *)a_out);
+    } else {
+        if (smem > 48 * 1024) DEXCT_CUDA_OK(cudaFuncSetAttribute(gn_general_kernel<double>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        gn_general_kernel<double><<<grid, 128, smem, st>>>((const double *)g, (const double *)i0, (const double *)mus, nMeas, nMats, nE,
+                                                         pix_bins, (long long)nE, P, n_iters, (double *)a_out);
+    }
+    DEXCT_CUDA_OK(cudaGetLastError());
+    return DEXCT_OK;
 }

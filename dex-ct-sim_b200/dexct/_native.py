@@ -48,6 +48,8 @@ SIGNATURES = {
                                           _P, _P, _P, _P, _P, _P, _P, _P, C.c_int32, _P]),
     'dexct_gn_decompose': (C.c_int, [_P, _P, _P, C.c_int32, C.c_int64, C.c_int32, C.c_double, _P, _P, C.c_int32,
                                      C.c_int32, _P]),
+    'dexct_gn_decompose_general': (C.c_int, [_P, _P, _P, C.c_int32, C.c_int32, C.c_int32, C.c_int64, C.c_int32, C.c_int64,
+                                             C.c_int32, _P, C.c_int32, _P]),
     'dexct_gn_scratch_bytes': (C.c_size_t, [C.c_int64, C.c_int32]),
     'dexct_gn_air_max': (C.c_int, [_P, C.c_int64, _P, C.c_int32, _P]),
     'dexct_fbp_workspace_bytes': (C.c_size_t, [C.POINTER(DexctScan), C.c_int32, C.c_int32]),

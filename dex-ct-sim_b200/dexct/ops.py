@@ -321,6 +321,31 @@ def gn_decompose(g, i0, mus, n_iters, mask_thresh=0.0, dtype=F32, out=None, redu
     return out
 
 
+def gn_decompose_general(g, i0, mus, n_iters, dtype=F32):
+    """optimize_sino_cpu in its general form (/root/reference/matdecomp.py:87-127): g [nMeas, nViews, nBins] counts,
+    i0 [nMeas, nBins, nE] (a spectrum per detector bin) or [nMeas, nE], mus [nMats, nE], 1..4 measurements and materials
+    -> a [nViews, nBins, nMats] device tensor.  float64 arithmetic inside; no air mask."""
+    N.require_device()
+    code = dtype_code(dtype)
+    td = _TORCH_DTYPE[code]
+    dev = g.device if isinstance(g, torch.Tensor) and g.is_cuda else torch.device('cuda', torch.cuda.current_device())
+    g = _as_device(g, td, dev)
+    i0 = _as_device(i0, td, dev)
+    mus = _as_device(mus, td, dev)
+    if g.dim() != 3:
+        raise ValueError('g must be [nMeas, nViews, nBins]')
+    n_meas, n_views, n_bins = g.shape
+    n_mats, nE = mus.shape
+    per_bin = i0.dim() == 3
+    if i0.shape[0] != n_meas or i0.shape[-1] != nE or (per_bin and i0.shape[1] != n_bins):
+        raise ValueError(f'i0 must be [{n_meas}, {n_bins}, {nE}] or [{n_meas}, {nE}], got {tuple(i0.shape)}')
+    out = torch.empty((n_views, n_bins, n_mats), dtype=td, device=dev)
+    with torch.cuda.device(dev):
+        N.check(N.lib().dexct_gn_decompose_general(N.ptr(g), N.ptr(i0), N.ptr(mus), n_meas, n_mats, nE, n_bins, int(per_bin),
+                                                   n_views * n_bins, int(n_iters), N.ptr(out), code, N.stream_ptr()))
+    return out
+
+
 def gn_fixup_count():
     """Pixels the most recent single-precision ``gn_decompose`` call handed to its float64 pass (synchronises)."""
     scratch = getattr(gn_decompose, 'last_scratch', None)

@@ -90,9 +90,11 @@ def optimize_sino(Sino_gg, ee, i0, mus, n_iters, verbose=True, dtype=None, mask_
                   reduce_max_over_ranks=False):
     """GPU Newton iterations; signature of matdecomp.py:20 (``ee`` is unused there too).
 
-    Sino_gg [2, nViews, nBins] counts (array, device tensor, or a pair of them); i0 [2, nBins, nE] (all bins identical,
-    matdecomp.py:151) or [2, nE]; mus [2, nE].  Returns [nViews, nBins, 2] -- float64 numpy by default, the device
-    tensor with ``to_host=False``.
+    Sino_gg [nMeas, nViews, nBins] counts (array, device tensor, or a sequence of them); i0 [nMeas, nBins, nE] or
+    [nMeas, nE]; mus [nMats, nE].  Returns [nViews, nBins, nMats] -- float64 numpy by default, the device tensor with
+    ``to_host=False``.  Two measurements, two basis materials and one spectrum for all bins (what do_matdecomp_gn
+    builds, matdecomp.py:151) take the fast kernels; a spectrum per detector bin or other counts of measurements /
+    materials (1..4; matdecomp.py:95,101-105,118,125 allow them) take the general float64 kernel.
     """
     del ee, verbose
     from dexct import _native
@@ -100,14 +102,24 @@ def optimize_sino(Sino_gg, ee, i0, mus, n_iters, verbose=True, dtype=None, mask_
     code = dtype_code(config.dtype if dtype is None else dtype)
     td = torch.float32 if code == 0 else torch.float64
     i0 = np.asarray(i0, dtype=np.float64)
-    if i0.ndim == 3:
-        if i0.shape[1] > 1 and not np.array_equal(i0[:, :1, :].repeat(i0.shape[1], axis=1), i0):
-            raise NotImplementedError('per-channel spectra are not supported: the reference tiles one spectrum over '
-                                      'all channels (matdecomp.py:151) and the kernel relies on that')
-        i0 = i0[:, 0, :]
     mus = np.asarray(mus, dtype=np.float64)
-    if mus.shape[0] != 2:
-        raise NotImplementedError('two basis materials only (matdecomp.py:155)')
+    per_bin = i0.ndim == 3 and i0.shape[1] > 1 and not np.array_equal(i0[:, :1, :].repeat(i0.shape[1], axis=1), i0)
+    n_meas = Sino_gg.shape[0] if hasattr(Sino_gg, 'shape') else len(Sino_gg)
+    if per_bin or mus.shape[0] != 2 or n_meas != 2:
+        # the reference's general form (matdecomp.py:95,101-105,118,125): a spectrum per detector bin, any number of
+        # measurements / basis materials (1..4) -- the general kernel; get_basismat_sinos never comes here
+        from dexct.ops import gn_decompose_general
+        if mask_thresh > 0 or reduce_max_over_ranks:
+            raise ValueError('the air mask belongs to get_basismat_sinos (two materials, one spectrum for all bins)')
+        g = Sino_gg if isinstance(Sino_gg, torch.Tensor) else np.ascontiguousarray(np.stack([np.asarray(s) for s in Sino_gg]))
+        if g.ndim != 3:
+            raise ValueError('Sino_gg must be [nMeas, nViews, nBins]')
+        if not per_bin and i0.ndim == 3:
+            i0 = i0[:, 0, :]
+        out = gn_decompose_general(g, i0, mus, n_iters, dtype=code)
+        return _host_f64(out) if to_host else out
+    if i0.ndim == 3:
+        i0 = i0[:, 0, :]
     if isinstance(Sino_gg, torch.Tensor) and Sino_gg.is_cuda:
         g = Sino_gg
     else:

@@ -33,9 +33,8 @@ def recon_device(sino, ct, N_matrix, FOV, ramp, dtype=None):
     -> image tensor ``[N_rows, N, N]``, summed over ranks when views are sharded."""
     code = dtype_code(config.dtype if dtype is None else dtype)
     td = torch.float32 if code == 0 else torch.float64
-    if abs(abs(ct.rotation) - 2.0 * np.pi) > 1e-3:
-        raise NotImplementedError('get_recon needs a full rotation (short-scan weighting is not implemented); '
-                                  f'rotation_angle_total = {ct.rotation}')
+    # rotation_angle_total (input/params.txt:24): one full turn, or a short scan of at least pi + fan angle, which takes
+    # Parker's weights inside the filter kernel; anything else is refused by the library with the numbers in the message
     n_views = ct.N_proj
     rank, ws = dist.world() if config.shard_views else (0, 1)
     v0, nv = dist.shard_range(n_views, rank, ws)

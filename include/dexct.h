@@ -155,6 +155,16 @@ int dexct_gn_decompose(const void *g_2xP, const void *i0_2xE, const void *mus_2x
                        int32_t n_iters, double mask_thresh, void *a_out_Px2, void *scratch,
                        int32_t scratch_has_max, int32_t dtype, void *stream);
 
+/* optimize_sino_cpu as the reference wrote it (matdecomp.py:87-127), beyond what get_basismat_sinos feeds it: nMeas
+ * measurements g [nMeas][P], nMats basis materials mus [nMats][nE] (1..4 each; :95,125 invert an nMats x nMats system
+ * per pixel) and, with i0_per_bin != 0, a spectrum per detector bin i0 [nMeas][n_bins][nE] (:101-105,118) -- pixel p
+ * then belongs to bin p % n_bins (P a multiple of n_bins); with i0_per_bin == 0, i0 is [nMeas][nE].  a_out [P][nMats].
+ * Arithmetic in float64 with the reference's exponent clip whatever `dtype` (which names the type of g, i0, mus, a_out);
+ * no air mask (get_basismat_sinos applies it for two materials only).                                              */
+int dexct_gn_decompose_general(const void *g, const void *i0, const void *mus, int32_t nMeas, int32_t nMats, int32_t nE,
+                               int64_t n_bins, int32_t i0_per_bin, int64_t P, int32_t n_iters, void *a_out, int32_t dtype,
+                               void *stream);
+
 /* max_p g1[p] (the first measurement, matdecomp.py:196) into scratch[0..8) as an order-preserving integer key:
  * int32 (DEXCT_F32) or int64 (DEXCT_F64), so that ranks holding different pixels can combine their values with an
  * integer MAX all-reduce before calling dexct_gn_decompose(..., scratch_has_max = 1).                          */

@@ -52,7 +52,42 @@ def filter_lines(sino, gamma0, dgamma, SID, ramp):
     return (out * dgamma).reshape(sino.shape)
 
 
-def fbp_fan(sino, beta, gamma0, dgamma, dbeta, SID, n_matrix, fov, ramp):
+def parker_weights(n_views, dbeta, gamma):
+    """Short-scan weights [n_views, n_ch] for a scan of n_views views dbeta apart covering less than a full turn
+    (Parker 1982, in the form that takes any angular range pi + 2 delta with delta >= the half fan angle -- the "virtual fan"
+    of Silver 2000): every line through the object is measured once or twice over such a scan, the conjugate of ray
+    (beta, gamma) being (beta + pi + 2 gamma, -gamma) for a source moving towards +beta, and the weights of a conjugate
+    pair add up to 1, going smoothly to 0 at both ends of the scan:
+        w = sin^2(pi/4 * b / (delta - gamma))                   0 <= b <= 2 delta - 2 gamma
+        w = 1                                                   2 delta - 2 gamma <= b <= pi - 2 gamma
+        w = sin^2(pi/4 * (pi + 2 delta - b) / (delta + gamma))  pi - 2 gamma <= b <= pi + 2 delta
+    with b = v |dbeta| the angle from the start of the scan.  A scan towards -beta is the mirror image: gamma -> -gamma.
+    The full-turn formula carries a factor 1/2 (every line measured twice), so these weights are used TWICE over."""
+    gamma = np.asarray(gamma, dtype=np.float64)
+    total = n_views * abs(float(dbeta))
+    delta = 0.5 * (total - np.pi)
+    gmax = float(np.max(np.abs(gamma)))
+    if not (delta >= gmax - 1e-12 and total < 2.0 * np.pi):
+        raise ValueError(f'short-scan weights need pi + fan <= rotation < 2 pi (rotation {total}, fan {2 * gmax})')
+    g = (gamma if dbeta >= 0 else -gamma)[None, :]
+    b = (np.arange(n_views) * abs(float(dbeta)))[:, None]
+    return parker(b, g, delta)
+
+
+def parker(b, g, delta):
+    """The weight function itself: b angle from the start of the scan, g fan angle (scan towards +beta), range pi + 2 delta;
+    0 outside the scan."""
+    b, g = np.broadcast_arrays(np.asarray(b, dtype=np.float64), np.asarray(g, dtype=np.float64))
+    tiny = 1e-300
+    w = np.ones(b.shape)
+    w1 = np.sin(0.25 * np.pi * b / np.maximum(delta - g, tiny)) ** 2
+    w3 = np.sin(0.25 * np.pi * (np.pi + 2.0 * delta - b) / np.maximum(delta + g, tiny)) ** 2
+    w = np.where(b < 2.0 * delta - 2.0 * g, w1, w)
+    w = np.where(b > np.pi - 2.0 * g, w3, w)
+    return np.where((b < 0) | (b > np.pi + 2.0 * delta), 0.0, w)
+
+
+def fbp_fan(sino, beta, gamma0, dgamma, dbeta, SID, n_matrix, fov, ramp, short_scan=False):
     """sino [n_views, n_ch] (or [n_views, n_rows, n_ch]) -> image [n, n] (or [n_rows, n, n]), float64.
 
     Pixel (j, i) is centred at x = (i - (n-1)/2) fov/n, y = (j - (n-1)/2) fov/n.  For the source at
@@ -65,6 +100,8 @@ def fbp_fan(sino, beta, gamma0, dgamma, dbeta, SID, n_matrix, fov, ramp):
     if squeeze:
         sino = sino[:, None, :]
     n_views, n_rows, n_ch = sino.shape
+    if short_scan:
+        sino = sino * (2.0 * parker_weights(n_views, dbeta, gamma0 + np.arange(n_ch) * dgamma))[:, None, :]
     q = filter_lines(sino, gamma0, dgamma, SID, ramp)
     qp = np.zeros((n_views, n_rows, n_ch + 2))
     qp[..., 1:-1] = q
@@ -84,7 +121,7 @@ def fbp_fan(sino, beta, gamma0, dgamma, dbeta, SID, n_matrix, fov, ramp):
         for r in range(n_rows):
             line = qp[v, r]
             img[r] += (line[i0 + 1] + f * (line[i0 + 2] - line[i0 + 1])) * w
-    img *= dbeta
+    img *= abs(dbeta)                              # the sum over views is a quadrature in |d beta|, whichever way the source turns
     return img[0] if squeeze else img
 
 

@@ -242,3 +242,50 @@ def test_c2_full_size_f32_against_the_oracle_on_64_views():
     assert lit.mean() > 0.9
     err = float(np.max(np.abs(got[lit] - ref[lit])) / np.max(np.abs(ref[lit])))
     assert err < 1e-5, f'C2 f32 vs oracle, 64 views, lit pixels: {err:.3e}'
+
+
+@pytest.mark.parametrize('n_meas,n_mats', [(2, 2), (3, 3), (3, 2), (4, 3), (1, 1), (4, 4)])
+def test_general_form_per_bin_spectra_and_other_material_counts(n_meas, n_mats):
+    """optimize_sino_cpu in the generality the reference wrote it with (matdecomp.py:95,101-105,118,125): a spectrum per
+    detector bin, 1..4 measurements and basis materials -- through the drop-in entry point, against the oracle (which
+    tests/test_oracle_gn.py pins to the reference function on the same shapes)."""
+    import matdecomp
+    from dexct import config
+    rng = np.random.default_rng(100 * n_meas + n_mats)
+    nV, nB, nE = 3, 29, 64
+    E = 30.0 + 1.5 * np.arange(nE)
+    base = np.stack([0.2 + 5.0 / E, 0.15 + 60.0 / E ** 1.5, 0.1 + 900.0 / E ** 2.5, 0.05 + 2.0e4 / E ** 3.2])
+    mus = base[:n_mats]
+    shape = np.exp(-0.5 * ((E[None, :] - np.linspace(45, 110, n_meas)[:, None]) / 16.0) ** 2) + 0.02
+    i0 = shape[:, None, :] * rng.uniform(0.5, 1.5, (n_meas, nB, 1)) * rng.uniform(0.9, 1.1, (n_meas, nB, nE)) * 1e5
+    a = np.stack([rng.uniform(0, [12, 2.5, 0.3, 0.05][q], (nV, nB)) for q in range(n_mats)], axis=-1)
+    att = np.exp(-(a[..., None, :] * mus.T[None, None]).sum(-1))
+    g = np.stack([(att * i0[m][None]).sum(-1) for m in range(n_meas)])
+    n_iters = 12
+    want = gn_oracle.optimize_sino_cpu(g, E, i0, mus, n_iters)
+    old = config.dtype
+    try:
+        config.dtype = 'f64'
+        got = matdecomp.optimize_sino_cpu(g, E, i0, mus, n_iters, verbose=False)
+        assert got.shape == (nV, nB, n_mats) and got.dtype == np.float64
+        assert scale_rel_err(got, want) < 1e-10
+        if n_meas == n_mats:
+            assert scale_rel_err(got, a) < 1e-6                       # a square, consistent system: the truth comes back
+        # single-precision I/O: the oracle is fed the rounded inputs
+        config.dtype = 'f32'
+        r32 = lambda x: np.asarray(x).astype(np.float32).astype(np.float64)            # noqa: E731
+        want32 = gn_oracle.optimize_sino_cpu(r32(g), E, r32(i0), r32(mus), n_iters)
+        got32 = matdecomp.optimize_sino(g, E, i0, mus, n_iters)
+        assert scale_rel_err(got32, want32) < 1e-5
+        # one spectrum tiled over the bins with three materials takes the same kernel ([nMeas, nE] form inside)
+        if n_mats != 2 or n_meas != 2:
+            i0_t = np.tile(i0[:, :1, :], (1, nB, 1))
+            g_t = np.stack([(att * i0_t[m][None]).sum(-1) for m in range(n_meas)])
+            config.dtype = 'f64'
+            assert scale_rel_err(matdecomp.optimize_sino_cpu(g_t, E, i0_t, mus, n_iters),
+                                 gn_oracle.optimize_sino_cpu(g_t, E, i0_t, mus, n_iters)) < 1e-10
+    finally:
+        config.dtype = old
+    with pytest.raises(N.DexctError, match='1 to 4'):
+        from dexct.ops import gn_decompose_general
+        gn_decompose_general(np.ones((5, 1, 4)), np.ones((5, 8)), np.ones((2, 8)), 1, dtype=F64)

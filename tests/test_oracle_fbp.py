@@ -73,3 +73,42 @@ def test_multi_row_is_row_by_row_and_hu():
     one = F.fbp_fan(s, beta, gamma0, dg, 2 * np.pi / 90, SID, 32, 25.0, 0.8)
     assert np.allclose(both[0], one, rtol=0, atol=1e-15) and np.allclose(both[1], 2 * one, rtol=1e-13, atol=1e-15)
     assert np.allclose(F.hounsfield(np.array([0.0, 0.2, 0.4]), 0.2), [-1000.0, 0.0, 1000.0])
+
+
+def test_parker_weights_of_conjugate_rays_add_up_to_one():
+    n_ch = 121
+    dg = FAN / n_ch
+    gam = (np.arange(n_ch) - 0.5 * (n_ch - 1)) * dg
+    for total, sign in ((np.pi + FAN, 1), (np.pi + FAN + 0.7, 1), (4.5, -1), (5.9, 1)):
+        n_views = 3000
+        db = sign * total / n_views
+        w = F.parker_weights(n_views, db, gam)
+        assert w.min() >= 0.0 and w.max() <= 1.0 and np.all(w[0] < 1e-6)
+        delta = 0.5 * (total - np.pi)
+        g = (gam if sign > 0 else -gam)[None, :]
+        b = (np.arange(n_views) * abs(db))[:, None]
+        assert np.array_equal(w, F.parker(b, g, delta))
+        # the same line is also seen from (b + pi + 2 g, -g) and from (b - pi + 2 g, -g), whichever lie inside the scan:
+        # the weights of all sightings of a line add up to 1
+        total_w = w + F.parker(b + np.pi + 2.0 * g, -g, delta) + F.parker(b - np.pi + 2.0 * g, -g, delta)
+        assert np.max(np.abs(total_w - 1.0)) < 1e-12, (total, sign)
+
+
+def test_short_scan_reconstructs_the_disc_in_both_directions():
+    n_ch, n, fov = 400, 96, 30.0
+    dg = FAN / n_ch
+    gamma0 = -0.5 * (n_ch - 1) * dg
+    for total, sign, beta0 in ((np.pi + FAN + 0.05, 1, 0.3), (4.4, -1, -1.1), (5.6, 1, 2.0)):
+        n_views = 300
+        db = sign * total / n_views
+        beta = beta0 + np.arange(n_views) * db
+        sino = F.disc_sinogram(beta, gamma0 + np.arange(n_ch) * dg, SID, (3.0, -2.0), 8.0, 0.2)
+        img = F.fbp_fan(sino, beta, gamma0, dg, db, SID, n, fov, 1.0, short_scan=True)
+        c = (np.arange(n) - 0.5 * (n - 1)) * (fov / n)
+        X, Y = np.meshgrid(c, c)
+        r = np.hypot(X - 3.0, Y + 2.0)
+        inside, outside = img[r < 6.5], img[(r > 9.5) & (r < 14.0)]
+        assert abs(inside.mean() - 0.2) < 0.003 and inside.std() < 0.006, (total, sign, inside.mean(), inside.std())
+        assert abs(outside.mean()) < 0.003
+    with np.testing.assert_raises(ValueError):
+        F.parker_weights(100, (np.pi + 0.5 * FAN) / 100, gamma0 + np.arange(n_ch) * dg)

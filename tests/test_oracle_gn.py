@@ -60,3 +60,25 @@ def test_table_assembly_matches_reference(have_reference, golden_dir):
                                           n_iters=int(d['n_iters']), mask_thresh=float(d['mask_thresh']))
     assert np.array_equal(m1, d['mat1']) and np.array_equal(m2, d['mat2'])
     assert (m1[0, :4] == 0).all() and (m2[0, :4] == 0).all()       # the air pixels planted by make_golden.py
+
+
+def test_restatement_matches_reference_function_in_its_general_form(have_reference, rng):
+    """matdecomp.py:87-127 as written takes a spectrum per detector bin and any number of measurements / basis materials
+    (:95,101-105,118,125); the restatement must follow it there too (the general CUDA kernel is checked against it)."""
+    if not have_reference:
+        pytest.skip('reference tree not mounted on this machine')
+    ref = gn_oracle.load_reference_matdecomp()
+    nV, nB, nE = 2, 17, 41
+    E = 30.0 + 2.0 * np.arange(nE)
+    base = np.stack([0.2 + 5.0 / E, 0.15 + 60.0 / E ** 1.5, 0.1 + 900.0 / E ** 2.5])
+    for n_meas, n_mats in ((2, 2), (3, 3), (3, 2), (4, 3), (1, 1)):
+        mus = base[:n_mats]
+        shape = np.exp(-0.5 * ((E[None, :] - np.linspace(50, 95, n_meas)[:, None]) / 18.0) ** 2) + 0.02
+        i0 = shape[:, None, :] * rng.uniform(0.5, 1.5, (n_meas, nB, 1)) * rng.uniform(0.9, 1.1, (n_meas, nB, nE)) * 1e4
+        a = np.stack([rng.uniform(0, [12, 2.5, 0.3][q], (nV, nB)) for q in range(n_mats)], axis=-1)
+        att = np.exp(-(a[..., None, :] * mus.T[None, None]).sum(-1))               # [nV, nB, nE]
+        g = np.stack([(att * i0[m][None]).sum(-1) for m in range(n_meas)])
+        for n_iters in (1, 6):
+            want = ref.optimize_sino_cpu(g, E, i0, mus, n_iters, verbose=False)
+            got = gn_oracle.optimize_sino_cpu(g, E, i0, mus, n_iters)
+            assert np.array_equal(got, want), (n_meas, n_mats, n_iters)
