@@ -454,11 +454,13 @@ __global__ void __launch_bounds__(256, (PX == 4 && CTAB) ? 3 : 1) gn_kernel(cons
 // bin).  Here they leave the FP32 pipe: a CTA owns a tile of 128 pixels (thread t <-> pixel t <-> lane t of tensor memory);
 // per chunk of bins each thread evaluates its exponentials, splits every value into a TF32 head and a tail
 // (att = hi + lo exactly: hi = att with the low 13 mantissa bits cleared) and stores both into tensor memory as the A operand
-// (tcgen05.st); one thread of a fifth warp then issues, per eight bins, three M128 x N16 x K8 TF32 MMAs
-//     D += hi x Bhi,  D += lo x Bhi,  D += hi x Blo            (Bhi + Blo = the moment rows, split once per call)
+// (tcgen05.st); one thread of a fifth warp then issues, per eight bins, two M128 x K8 TF32 MMAs
+//     D[0..31] += hi x [Bhi | Blo]  (N = 32),     D[0..15] += lo x Bhi  (N = 16)      (Bhi + Blo = the moment rows, split once)
 // -- the "3xTF32" scheme: products of 11-bit significands are exact in the FP32 accumulator, and the one missing term
-// lo x Blo is below 2^-22 of the sum -- with B read from shared memory through a K-major no-swizzle matrix descriptor and D
-// (128 lanes x 16 columns of FP32) accumulating in tensor memory over all bins of a Newton iteration.  The threads read their
+// lo x Blo is below 2^-22 of the sum.  An MMA costs ~45 cycles whatever its N up to 64 (tools/microbench/tc_rate.cu,
+// profiles/r02c_tc_rate.txt), so the two products with hi share one instruction; the thread adds the two halves of its
+// accumulator row when it reads it back.  B is read from shared memory through a K-major no-swizzle matrix descriptor, D
+// (128 lanes x 32 columns of FP32) accumulates in tensor memory over all bins of a Newton iteration.  The threads read their
 // row of D back (tcgen05.ld), do the 2x2 Newton step in registers as before, and go round again.  A-operand chunks are double
 // buffered (mbarriers: full[b] by the compute warps, free[b] and done by tcgen05.commit), four CTAs share an SM (4 x 128
 // columns of tensor memory), so exponentials, MMAs and Newton updates of different tiles overlap.
@@ -468,16 +470,19 @@ constexpr int GT_KS = 8;                    // bins per MMA: 32 bytes of TF32 al
 constexpr int GT_CHUNK_KS = 3;              // k-steps per A-operand chunk
 constexpr int GT_CH = GT_KS * GT_CHUNK_KS;  // bins per chunk
 constexpr int GT_NBUF = 2;
-constexpr int GT_COLS = 128;                // tensor-memory columns per CTA: 2 x (24 hi + 24 lo) + 16 accumulator + 16 spare
+constexpr int GT_COLS = 128;                // tensor-memory columns per CTA: 2 x (24 hi + 24 lo) + 32 accumulator
 constexpr int GT_DCOL = GT_NBUF * 2 * GT_CH;
 constexpr int GT_THREADS = 160;             // four compute warps (one per 32 lanes of tensor memory) + the MMA warp
 constexpr int GT_MAX_KS = 56;               // 56 KiB of B operand + 3.5 KiB of exponent pairs fit the 64 KiB staging slot
-constexpr uint32_t GT_IDESC = (1u << 4) | (2u << 7) | (2u << 10) | ((16u >> 3) << 17) | ((128u >> 4) << 24);   // F32 += TF32 x TF32, K-major A and B, N = 16, M = 128
+// instruction descriptors: F32 += TF32 x TF32, K-major A and B, M = 128, N = 32 (hi x [Bhi | Blo]) and N = 16 (lo x Bhi)
+constexpr uint32_t GT_IDESC32 = (1u << 4) | (2u << 7) | (2u << 10) | ((32u >> 3) << 17) | ((128u >> 4) << 24);
+constexpr uint32_t GT_IDESC16 = (1u << 4) | (2u << 7) | (2u << 10) | ((16u >> 3) << 17) | ((128u >> 4) << 24);
 __constant__ ulonglong2 gn_tcx[GT_MAX_KS * 4];      // per k-step: -mu1 s of its 8 bins, then -mu2 s of its 8 bins (zero past nE)
 
-// B operand image: per k-step 512 B of TF32 heads then 512 B of tails, each the canonical K-major no-swizzle layout
-// [K half (4 bins)][moment group of 8][moment][4 bins]  -- core matrices of 8 rows x 16 bytes; LBO (next K half) = 256 B,
-// SBO (next moment group) = 128 B.  Followed by the exponent table [nks][16].
+// B operand image: per k-step one 32-row matrix [Bhi (16 moment rows) ; Blo (16 rows)] x 8 bins in the canonical K-major
+// no-swizzle layout [K half (4 bins)][row group of 8][row][4 bins] -- core matrices of 8 rows x 16 bytes; LBO (next K half)
+// = 512 B, SBO (next row group) = 128 B.  An N = 32 MMA reads all of it, an N = 16 MMA on the same descriptor the Bhi rows.
+// Followed by the exponent table [nks][16].
 __global__ void gn_tc_table_kernel(const float *__restrict__ i0, const float *__restrict__ mus, int nE, int nks, float *__restrict__ tab)
 {
     const int e = blockIdx.x * blockDim.x + threadIdx.x;
@@ -498,9 +503,8 @@ __global__ void gn_tc_table_kernel(const float *__restrict__ i0, const float *__
 #pragma unroll
     for (int n = 0; n < 16; ++n) {
         const float hi = __uint_as_float((__float_as_uint(row[n]) + 0x1000u) & 0xffffe000u);      // nearest TF32 (11-bit significand)
-        const int at = ((kc * 2 + n / 8) * 8 + n % 8) * 4 + kk;
-        b[at] = hi;
-        b[128 + at] = row[n] - hi;                                                                  // exact
+        b[((kc * 4 + n / 8) * 8 + n % 8) * 4 + kk] = hi;
+        b[((kc * 4 + 2 + n / 8) * 8 + n % 8) * 4 + kk] = row[n] - hi;                               // exact
     }
     float *x = tab + (size_t)nks * 256 + ks * 16;
     x[e % GT_KS] = t0;
@@ -548,11 +552,26 @@ __device__ __forceinline__ void tmem_ld16(uint32_t taddr, float (&v)[16])
 #pragma unroll
     for (int q = 0; q < 16; ++q) v[q] = __uint_as_float(r[q]);
 }
-// D[tmem] (+)= A[tmem] x B[smem descriptor], M128 N16 K8, TF32 in, FP32 accumulate
-__device__ __forceinline__ void tc_mma_tf32(uint32_t d_tmem, uint32_t a_tmem, uint64_t b_desc, uint32_t accumulate)
+__device__ __forceinline__ void tmem_ld32(uint32_t taddr, float (&v)[32])
+{
+    uint32_t r[32];
+#pragma unroll
+    for (int h = 0; h < 2; ++h)
+        asm volatile("tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15}, [%16];"
+                     : "=r"(r[16 * h + 0]), "=r"(r[16 * h + 1]), "=r"(r[16 * h + 2]), "=r"(r[16 * h + 3]), "=r"(r[16 * h + 4]),
+                       "=r"(r[16 * h + 5]), "=r"(r[16 * h + 6]), "=r"(r[16 * h + 7]), "=r"(r[16 * h + 8]), "=r"(r[16 * h + 9]),
+                       "=r"(r[16 * h + 10]), "=r"(r[16 * h + 11]), "=r"(r[16 * h + 12]), "=r"(r[16 * h + 13]), "=r"(r[16 * h + 14]),
+                       "=r"(r[16 * h + 15])
+                     : "r"(taddr + 16 * h) : "memory");
+    asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+#pragma unroll
+    for (int q = 0; q < 32; ++q) v[q] = __uint_as_float(r[q]);
+}
+// D[tmem] (+)= A[tmem] x B[smem descriptor], M128 K8, TF32 in, FP32 accumulate
+__device__ __forceinline__ void tc_mma_tf32(uint32_t d_tmem, uint32_t a_tmem, uint64_t b_desc, uint32_t idesc, uint32_t accumulate)
 {
     asm volatile("{ .reg .pred p; setp.ne.b32 p, %4, 0; tcgen05.mma.cta_group::1.kind::tf32 [%0], [%1], %2, %3, p; }" ::"r"(d_tmem),
-                 "r"(a_tmem), "l"(b_desc), "r"(GT_IDESC), "r"(accumulate) : "memory");
+                 "r"(a_tmem), "l"(b_desc), "r"(idesc), "r"(accumulate) : "memory");
 }
 __device__ __forceinline__ void tc_commit(uint32_t bar)
 {
@@ -589,7 +608,7 @@ __global__ void __launch_bounds__(GT_THREADS) gn_tc_kernel(const float *__restri
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     if (warp == 4) {
-        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&tmem_base_sm)), "r"(GT_COLS) : "memory");
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&tmem_base_sm)), "n"(GT_COLS) : "memory");
         asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
     }
     asm volatile("fence.proxy.async.shared::cta;" ::: "memory");     // the B operand written above is read by the tensor core (async proxy)
@@ -604,7 +623,7 @@ __global__ void __launch_bounds__(GT_THREADS) gn_tc_kernel(const float *__restri
     if (warp == 4) {
         // ---- MMA issuer: one thread mirrors the loop structure of the compute warps
         if (lane == 0) {
-            const uint64_t lbo = lbo_sbo_swapped ? 128 : 256, sbo = lbo_sbo_swapped ? 256 : 128;
+            const uint64_t lbo = lbo_sbo_swapped ? 128 : 512, sbo = lbo_sbo_swapped ? 512 : 128;
             const uint64_t desc0 = ((lbo >> 4) << 16) | ((sbo >> 4) << 32) | (1ull << 46);
             const uint32_t bsm_addr = smem_u32(bsm);
             uint32_t cnt = 0;
@@ -619,11 +638,10 @@ __global__ void __launch_bounds__(GT_THREADS) gn_tc_kernel(const float *__restri
                         for (int s = 0; s < GT_CHUNK_KS; ++s) {
                             const int ks = c * GT_CHUNK_KS + s;
                             if (ks < nks) {
-                                const uint64_t d_hi = desc0 | (uint64_t)(((bsm_addr + ks * 1024) & 0x3ffff) >> 4);
-                                const uint64_t d_lo = desc0 | (uint64_t)(((bsm_addr + ks * 1024 + 512) & 0x3ffff) >> 4);
-                                tc_mma_tf32(tmem + GT_DCOL, a_hi + s * GT_KS, d_hi, ks > 0);
-                                tc_mma_tf32(tmem + GT_DCOL, a_lo + s * GT_KS, d_hi, 1);
-                                tc_mma_tf32(tmem + GT_DCOL, a_hi + s * GT_KS, d_lo, 1);
+                                const uint64_t db = desc0 | (uint64_t)(((bsm_addr + ks * 1024) & 0x3ffff) >> 4);
+                                // columns 0..15 += hi x Bhi + lo x Bhi, columns 16..31 += hi x Blo
+                                tc_mma_tf32(tmem + GT_DCOL, a_hi + s * GT_KS, db, GT_IDESC32, ks > 0);
+                                tc_mma_tf32(tmem + GT_DCOL, a_lo + s * GT_KS, db, GT_IDESC16, 1);
                             }
                         }
                         tc_commit(bar_free + 8 * b);                  // the chunk's A operand may be overwritten once these MMAs are done
@@ -694,9 +712,11 @@ __global__ void __launch_bounds__(GT_THREADS) gn_tc_kernel(const float *__restri
                 }
                 mbar_wait(bar_done, done_cnt++ & 1);
                 tc_fence_after();
-                float A[16];
-                tmem_ld16(lane_base + GT_DCOL, A);
+                float D[32], A[12];
+                tmem_ld32(lane_base + GT_DCOL, D);
                 tc_fence_before();
+#pragma unroll
+                for (int q = 0; q < 12; ++q) A[q] = D[q] + D[16 + q];
                 newton_update<float>(A, g1, g2, a1, a2, sane);
             }
             if (p < P) {
@@ -716,7 +736,7 @@ __global__ void __launch_bounds__(GT_THREADS) gn_tc_kernel(const float *__restri
     }
     tc_fence_before();
     __syncthreads();
-    if (warp == 4) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "r"(GT_COLS) : "memory");
+    if (warp == 4) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "n"(GT_COLS) : "memory");
 }
 
 // ---------------------------------------------------------------------------------------------------------------------
@@ -955,10 +975,12 @@ static int launch_gn_tc(const void *g, const void *i0, const void *mus, int nE, 
     const int nks = (nE + GT_KS - 1) / GT_KS;
     const size_t smem = (size_t)nks * 1024;
     DEXCT_CUDA_OK(cudaFuncSetAttribute(gn_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    int per_sm = 0;
-    DEXCT_CUDA_OK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, gn_tc_kernel, GT_THREADS, smem));
-    if (per_sm < 1) per_sm = 1;
-    if (per_sm > 512 / GT_COLS) per_sm = 512 / GT_COLS;         // tensor memory: 512 columns per SM
+    // CTAs per SM: 512 columns of tensor memory / GT_COLS, and what fits the shared memory.  (The occupancy calculator
+    // answers 1 for a kernel that allocates tensor memory -- profiles/r02c: a grid of 148 CTAs ran at 3x the time.)
+    int per_sm = 512 / GT_COLS;
+    while (per_sm > 1 && (size_t)per_sm * (smem + 2048) > 220 * 1024) --per_sm;
+    const char *ps = getenv("DEXCT_GN_TC_CTAS");             // tuning knob
+    if (ps && atoi(ps) >= 1 && atoi(ps) <= 512 / GT_COLS) per_sm = atoi(ps);
     const long long n_tiles = (P + 127) / 128;
     long long grid = (long long)sm_count() * per_sm;           // one resident wave; the tile-stride loop does the rest
     if (grid > n_tiles) grid = n_tiles;

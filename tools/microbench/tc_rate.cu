@@ -9,14 +9,14 @@
 __device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
 
 template <bool TF32, bool A_TMEM>
-__global__ void k(long long *cyc, int N, int rep)
+__global__ void k(long long *cyc, int N, int rep, int nacc, int nissue)
 {
     extern __shared__ __align__(128) unsigned char smem[];     // zeros: A [128 x 32 B] then B [256 x 32 B], core-matrix layout
     __shared__ __align__(8) unsigned long long bar;
     __shared__ uint32_t tmem_sm;
     for (int i = threadIdx.x; i < (128 * 32 + 256 * 32) / 4; i += blockDim.x) ((uint32_t *)smem)[i] = 0;
     if (threadIdx.x == 0) {
-        asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;" ::"r"(smem_u32(&bar)) : "memory");
+        asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(&bar)), "r"(nissue) : "memory");
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     if (threadIdx.x < 32) {
@@ -42,14 +42,15 @@ __global__ void k(long long *cyc, int N, int rep)
     const uint64_t dA = ((uint64_t)((smem_u32(smem) & 0x3ffff) >> 4)) | ((uint64_t)(128 * 16 >> 4) << 16) | ((uint64_t)(128 >> 4) << 32) | (1ull << 46);
     const uint64_t dB = ((uint64_t)((smem_u32(smem + 128 * 32) & 0x3ffff) >> 4)) | ((uint64_t)(256 * 16 >> 4) << 16) | ((uint64_t)(128 >> 4) << 32) | (1ull << 46);
     long long t0 = clock64();
-    if (threadIdx.x == 0) {
+    if ((threadIdx.x & 31) == 0 && (threadIdx.x >> 5) < nissue) {       // nissue warps issue at the same time, each into its own accumulators
         for (int r = 0; r < rep; ++r) {
+            const uint32_t dcol = tmem + (uint32_t)((r + (threadIdx.x >> 5)) % nacc) * 64;      // nacc > 1: successive MMAs feed different accumulators
             if (A_TMEM) {
-                if (TF32) asm volatile("{ .reg .pred p; setp.ne.b32 p, %4, 0; tcgen05.mma.cta_group::1.kind::tf32 [%0], [%1], %2, %3, p; }" ::"r"(tmem), "r"(tmem + 256), "l"(dB), "r"(idesc), "r"(1u) : "memory");
-                else asm volatile("{ .reg .pred p; setp.ne.b32 p, %4, 0; tcgen05.mma.cta_group::1.kind::f16 [%0], [%1], %2, %3, p; }" ::"r"(tmem), "r"(tmem + 256), "l"(dB), "r"(idesc), "r"(1u) : "memory");
+                if (TF32) asm volatile("{ .reg .pred p; setp.ne.b32 p, %4, 0; tcgen05.mma.cta_group::1.kind::tf32 [%0], [%1], %2, %3, p; }" ::"r"(dcol), "r"(tmem + 256), "l"(dB), "r"(idesc), "r"(1u) : "memory");
+                else asm volatile("{ .reg .pred p; setp.ne.b32 p, %4, 0; tcgen05.mma.cta_group::1.kind::f16 [%0], [%1], %2, %3, p; }" ::"r"(dcol), "r"(tmem + 256), "l"(dB), "r"(idesc), "r"(1u) : "memory");
             } else {
-                if (TF32) asm volatile("{ .reg .pred p; setp.ne.b32 p, %4, 0; tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p; }" ::"r"(tmem), "l"(dA), "l"(dB), "r"(idesc), "r"(1u) : "memory");
-                else asm volatile("{ .reg .pred p; setp.ne.b32 p, %4, 0; tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p; }" ::"r"(tmem), "l"(dA), "l"(dB), "r"(idesc), "r"(1u) : "memory");
+                if (TF32) asm volatile("{ .reg .pred p; setp.ne.b32 p, %4, 0; tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p; }" ::"r"(dcol), "l"(dA), "l"(dB), "r"(idesc), "r"(1u) : "memory");
+                else asm volatile("{ .reg .pred p; setp.ne.b32 p, %4, 0; tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p; }" ::"r"(dcol), "l"(dA), "l"(dB), "r"(idesc), "r"(1u) : "memory");
             }
         }
         asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(&bar)) : "memory");
@@ -66,23 +67,24 @@ __global__ void k(long long *cyc, int N, int rep)
 }
 
 template <bool TF32, bool A_TMEM>
-static void run(const char *name)
+static void run(const char *name, int nacc, int nissue = 1)
 {
     long long *d, h[2];
     cudaMalloc(&d, 16);
     const int smem = 128 * 32 + 256 * 32;
     for (int N : {16, 32, 64, 128, 256}) {
+        if (nacc > 1 && N > 64) continue;
         long long c[2][2];
         int reps[2] = {64, 576};
         for (int q = 0; q < 2; ++q) {
-            k<TF32, A_TMEM><<<1, 128, smem>>>(d, N, reps[q]);
-            k<TF32, A_TMEM><<<1, 128, smem>>>(d, N, reps[q]);
+            k<TF32, A_TMEM><<<1, 128, smem>>>(d, N, reps[q], nacc, nissue);
+            k<TF32, A_TMEM><<<1, 128, smem>>>(d, N, reps[q], nacc, nissue);
             cudaError_t e = cudaDeviceSynchronize();
             if (e != cudaSuccess) { printf("%s N=%d: %s\n", name, N, cudaGetErrorString(e)); return; }
             cudaMemcpy(h, d, 16, cudaMemcpyDeviceToHost);
             c[q][0] = h[0]; c[q][1] = h[1];
         }
-        printf("%-22s N=%3d: %7.1f cycles per MMA (total), %6.1f per issue; %lld cycles for 64\n", name, N,
+        printf("%-22s %d accumulator(s) %d issuer(s) N=%3d: %7.1f cycles per MMA (total), %6.1f per issue; %lld cycles for 64\n", name, nacc, nissue, N,
                (double)(c[1][0] - c[0][0]) / 512.0, (double)(c[1][1] - c[0][1]) / 512.0, c[0][0]);
     }
     cudaFree(d);
@@ -90,9 +92,12 @@ static void run(const char *name)
 
 int main()
 {
-    run<true, true>("tf32 K=8  A in TMEM");
-    run<true, false>("tf32 K=8  A in smem");
-    run<false, true>("bf16 K=16 A in TMEM");
-    run<false, false>("bf16 K=16 A in smem");
+    for (int nacc : {1, 2, 4}) {
+        run<true, true>("tf32 K=8  A in TMEM", nacc);
+        run<false, true>("bf16 K=16 A in TMEM", nacc);
+    }
+    for (int ni : {2, 4}) run<true, true>("tf32 K=8  A in TMEM", 4, ni);
+    run<true, false>("tf32 K=8  A in smem", 1);
+    run<false, false>("bf16 K=16 A in smem", 1);
     return 0;
 }
