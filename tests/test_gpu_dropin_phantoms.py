@@ -43,10 +43,10 @@ def test_in_place_edit_of_a_large_phantom_invalidates_the_workspace(on_device):
     raw0b, _ = FP.get_sino(ct, big, lo)
     # the second call is served from the stored lengths (poly_detect): same values, another summation order in float32
     assert np.allclose(raw0, raw0b, rtol=1e-5)
-    big.M[nz // 2 - 3:nz // 2 + 3, 250:262, 251:263] = 5                   # a small dense insert near the centre, in place
+    big.M[nz // 2 - 3:nz // 2 + 3, 250:262, 251:263] = 7                   # a small dense insert near the centre, in place
     raw1, _ = FP.get_sino(ct, big, lo)
     assert not np.allclose(raw0, raw1, rtol=1e-3)
-    assert (raw1 <= raw0 * (1 + 1e-6)).all() and raw1.min() < raw0.min()
+    assert (raw1 <= raw0 * (1 + 1e-5)).all() and raw1.min() < raw0.min()
     FP.clear_cache()
     raw2, _ = FP.get_sino(ct, big, lo)                                     # a fresh workspace gives the same as the invalidated one
     assert np.array_equal(raw1, raw2)
