@@ -44,7 +44,7 @@ __global__ void k(long long *cyc, int N, int rep, int nacc, int nissue)
     long long t0 = clock64();
     if ((threadIdx.x & 31) == 0 && (threadIdx.x >> 5) < nissue) {       // nissue warps issue at the same time, each into its own accumulators
         for (int r = 0; r < rep; ++r) {
-            const uint32_t dcol = tmem + (uint32_t)((r + (threadIdx.x >> 5)) % nacc) * 64;      // nacc > 1: successive MMAs feed different accumulators
+            const uint32_t dcol = tmem + (uint32_t)((r + (threadIdx.x >> 5)) & (nacc - 1)) * 64;    // nacc (a power of two) > 1: successive MMAs feed different accumulators; no integer division in the issue loop (r02d measured the division, not the MMA)
             if (A_TMEM) {
                 if (TF32) asm volatile("{ .reg .pred p; setp.ne.b32 p, %4, 0; tcgen05.mma.cta_group::1.kind::tf32 [%0], [%1], %2, %3, p; }" ::"r"(dcol), "r"(tmem + 256), "l"(dB), "r"(idesc), "r"(1u) : "memory");
                 else asm volatile("{ .reg .pred p; setp.ne.b32 p, %4, 0; tcgen05.mma.cta_group::1.kind::f16 [%0], [%1], %2, %3, p; }" ::"r"(dcol), "r"(tmem + 256), "l"(dB), "r"(idesc), "r"(1u) : "memory");
@@ -84,8 +84,8 @@ static void run(const char *name, int nacc, int nissue = 1)
             cudaMemcpy(h, d, 16, cudaMemcpyDeviceToHost);
             c[q][0] = h[0]; c[q][1] = h[1];
         }
-        printf("%-22s %d accumulator(s) %d issuer(s) N=%3d: %7.1f cycles per MMA (total), %6.1f per issue; %lld cycles for 64\n", name, nacc, nissue, N,
-               (double)(c[1][0] - c[0][0]) / 512.0, (double)(c[1][1] - c[0][1]) / 512.0, c[0][0]);
+        printf("%-22s %d accumulator(s) %d issuer(s) N=%3d: %7.1f cycles per MMA (SM aggregate), %6.1f per issue of one thread; %lld cycles for 64\n", name, nacc, nissue, N,
+               (double)(c[1][0] - c[0][0]) / (512.0 * nissue), (double)(c[1][1] - c[0][1]) / 512.0, c[0][0]);
     }
     cudaFree(d);
 }
@@ -96,7 +96,7 @@ int main()
         run<true, true>("tf32 K=8  A in TMEM", nacc);
         run<false, true>("bf16 K=16 A in TMEM", nacc);
     }
-    for (int ni : {2, 4}) run<true, true>("tf32 K=8  A in TMEM", 4, ni);
+    for (int ni : {2, 4}) { run<true, true>("tf32 K=8  A in TMEM", 4, ni); run<true, true>("tf32 K=8  A in TMEM", 1, ni); }
     run<true, false>("tf32 K=8  A in smem", 1);
     run<false, false>("bf16 K=16 A in smem", 1);
     return 0;
