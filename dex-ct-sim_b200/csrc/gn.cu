@@ -468,21 +468,21 @@ __global__ void __launch_bounds__(256, (PX == 4 && CTAB) ? 3 : 1) gn_kernel(cons
 // FADD2 -- the kernel is bound by the MUFU unit (16 ex2 per clock and SM) instead of the FMA pipe.
 constexpr int GT_KS = 8;                    // bins per MMA: 32 bytes of TF32 along K
 constexpr int GT_CHUNK_KS = 3;              // k-steps per A-operand chunk
-constexpr int GT_CH = GT_KS * GT_CHUNK_KS;  // bins per chunk
+constexpr int GT_KCOLS = 2 * GT_KS;         // tensor-memory columns of one k-step of A: 8 heads, then 8 tails
+constexpr int GT_CH = GT_KCOLS * GT_CHUNK_KS;   // columns per chunk
 constexpr int GT_NBUF = 2;
-constexpr int GT_COLS = 128;                // tensor-memory columns per CTA: 2 x (24 hi + 24 lo) + 32 accumulator
-constexpr int GT_DCOL = GT_NBUF * 2 * GT_CH;
+constexpr int GT_COLS = 128;                // tensor-memory columns per CTA: 2 x 48 (A operand chunks) + 32 (accumulator)
+constexpr int GT_DCOL = GT_NBUF * GT_CH;
 constexpr int GT_THREADS = 160;             // four compute warps (one per 32 lanes of tensor memory) + the MMA warp
 constexpr int GT_MAX_KS = 56;               // 56 KiB of B operand + 3.5 KiB of exponent pairs fit the 64 KiB staging slot
 // instruction descriptors: F32 += TF32 x TF32, K-major A and B, M = 128, N = 32 (hi x [Bhi | Blo]) and N = 16 (lo x Bhi)
 constexpr uint32_t GT_IDESC32 = (1u << 4) | (2u << 7) | (2u << 10) | ((32u >> 3) << 17) | ((128u >> 4) << 24);
 constexpr uint32_t GT_IDESC16 = (1u << 4) | (2u << 7) | (2u << 10) | ((16u >> 3) << 17) | ((128u >> 4) << 24);
-__constant__ ulonglong2 gn_tcx[GT_MAX_KS * 4];      // per k-step: -mu1 s of its 8 bins, then -mu2 s of its 8 bins (zero past nE)
 
 // B operand image: per k-step one 32-row matrix [Bhi (16 moment rows) ; Blo (16 rows)] x 8 bins in the canonical K-major
 // no-swizzle layout [K half (4 bins)][row group of 8][row][4 bins] -- core matrices of 8 rows x 16 bytes; LBO (next K half)
 // = 512 B, SBO (next row group) = 128 B.  An N = 32 MMA reads all of it, an N = 16 MMA on the same descriptor the Bhi rows.
-// Followed by the exponent table [nks][16].
+// Followed by the exponent table [nks][4 bin pairs]{-mu1 s (2 bins), -mu2 s (2 bins)}: one LDS.128 feeds an FMUL2 and an FFMA2.
 __global__ void gn_tc_table_kernel(const float *__restrict__ i0, const float *__restrict__ mus, int nE, int nks, float *__restrict__ tab)
 {
     const int e = blockIdx.x * blockDim.x + threadIdx.x;
@@ -506,9 +506,9 @@ __global__ void gn_tc_table_kernel(const float *__restrict__ i0, const float *__
         b[((kc * 4 + n / 8) * 8 + n % 8) * 4 + kk] = hi;
         b[((kc * 4 + 2 + n / 8) * 8 + n % 8) * 4 + kk] = row[n] - hi;                               // exact
     }
-    float *x = tab + (size_t)nks * 256 + ks * 16;
-    x[e % GT_KS] = t0;
-    x[8 + e % GT_KS] = t1;
+    float *x = tab + (size_t)nks * 256 + ks * 16 + ((e % GT_KS) / 2) * 4 + (e & 1);
+    x[0] = t0;
+    x[2] = t1;
 }
 
 __device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
@@ -524,14 +524,13 @@ __device__ __forceinline__ void mbar_arrive(uint32_t bar)
 // instead of hanging the device.
 __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity)
 {
-    uint32_t ok = 0;
-    long long t0 = 0;
+    uint32_t ok = 0, spins = 0;
     for (;;) {
+        // try_wait suspends the warp until the phase completes or a hardware time limit passes: no issue slots burnt
         asm volatile("{ .reg .pred p; mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2; selp.u32 %0, 1, 0, p; }"
                      : "=r"(ok) : "r"(bar), "r"(parity) : "memory");
         if (ok) return;
-        if (t0 == 0) t0 = clock64();
-        else if (clock64() - t0 > 8000000000ll) __trap();
+        if (++spins > (1u << 26)) __trap();
     }
 }
 __device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
@@ -540,6 +539,12 @@ __device__ __forceinline__ void tmem_st8(uint32_t taddr, const uint32_t (&v)[8])
 {
     asm volatile("tcgen05.st.sync.aligned.32x32b.x8.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8};" ::"r"(taddr), "r"(v[0]), "r"(v[1]),
                  "r"(v[2]), "r"(v[3]), "r"(v[4]), "r"(v[5]), "r"(v[6]), "r"(v[7]) : "memory");
+}
+__device__ __forceinline__ void tmem_st16(uint32_t taddr, const uint32_t (&v)[16])
+{
+    asm volatile("tcgen05.st.sync.aligned.32x32b.x16.b32 [%0], {%1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, %16};" ::"r"(taddr),
+                 "r"(v[0]), "r"(v[1]), "r"(v[2]), "r"(v[3]), "r"(v[4]), "r"(v[5]), "r"(v[6]), "r"(v[7]), "r"(v[8]), "r"(v[9]), "r"(v[10]),
+                 "r"(v[11]), "r"(v[12]), "r"(v[13]), "r"(v[14]), "r"(v[15]) : "memory");
 }
 __device__ __forceinline__ void tmem_ld16(uint32_t taddr, float (&v)[16])
 {
@@ -590,18 +595,21 @@ __device__ __forceinline__ f32x2 fsub2(f32x2 a, f32x2 b)
     return r;
 }
 
-__global__ void __launch_bounds__(GT_THREADS) gn_tc_kernel(const float *__restrict__ g, const float *__restrict__ btab, int nks, long long P,
+__global__ void __launch_bounds__(GT_THREADS, 4) gn_tc_kernel(const float *__restrict__ g, const float *__restrict__ btab, int nks, long long P,
                                                            int n_iters, float mask_thresh, void *scratch, float *__restrict__ a_out,
                                                            const GnMirrors mir, const GnRider rider, int lbo_sbo_swapped)
 {
     extern __shared__ __align__(128) unsigned char smem_raw[];
-    float *bsm = (float *)smem_raw;                           // [nks][hi 128 floats, lo 128 floats]
+    float *bsm = (float *)smem_raw;                           // [nks][hi 128 floats, lo 128 floats], then [nks][4] exponent float4s
     __shared__ __align__(8) unsigned long long bars[2 * GT_NBUF + 1];
     __shared__ uint32_t tmem_base_sm;
-    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    const int tid = threadIdx.x, lane = tid & 31;
+    // the warp index as a value the compiler knows to be the same in all lanes: the role branches below are then uniform
+    // branches and the code inside them may use the uniform datapath
+    const int warp = __shfl_sync(0xffffffffu, tid >> 5, 0);
     const uint32_t bar_full = smem_u32(&bars[0]), bar_free = smem_u32(&bars[GT_NBUF]), bar_done = smem_u32(&bars[2 * GT_NBUF]);
 
-    for (int i = tid; i < nks * 64; i += GT_THREADS) ((float4 *)bsm)[i] = ((const float4 *)btab)[i];
+    for (int i = tid; i < nks * 68; i += GT_THREADS) ((float4 *)bsm)[i] = ((const float4 *)btab)[i];
     if (tid == 0) {
         for (int b = 0; b < GT_NBUF; ++b) { mbar_init(bar_full + 8 * b, 4); mbar_init(bar_free + 8 * b, 1); }
         mbar_init(bar_done, 1);
@@ -633,15 +641,15 @@ __global__ void __launch_bounds__(GT_THREADS) gn_tc_kernel(const float *__restri
                         const uint32_t b = cnt % GT_NBUF;
                         mbar_wait(bar_full + 8 * b, (cnt / GT_NBUF) & 1);
                         tc_fence_after();
-                        const uint32_t a_hi = tmem + b * 2 * GT_CH, a_lo = a_hi + GT_CH;
+                        const uint32_t a_buf = tmem + b * GT_CH;
 #pragma unroll
                         for (int s = 0; s < GT_CHUNK_KS; ++s) {
                             const int ks = c * GT_CHUNK_KS + s;
                             if (ks < nks) {
                                 const uint64_t db = desc0 | (uint64_t)(((bsm_addr + ks * 1024) & 0x3ffff) >> 4);
                                 // columns 0..15 += hi x Bhi + lo x Bhi, columns 16..31 += hi x Blo
-                                tc_mma_tf32(tmem + GT_DCOL, a_hi + s * GT_KS, db, GT_IDESC32, ks > 0);
-                                tc_mma_tf32(tmem + GT_DCOL, a_lo + s * GT_KS, db, GT_IDESC16, 1);
+                                tc_mma_tf32(tmem + GT_DCOL, a_buf + s * GT_KCOLS, db, GT_IDESC32, ks > 0);
+                                tc_mma_tf32(tmem + GT_DCOL, a_buf + s * GT_KCOLS + GT_KS, db, GT_IDESC16, 1);
                             }
                         }
                         tc_commit(bar_free + 8 * b);                  // the chunk's A operand may be overwritten once these MMAs are done
@@ -653,6 +661,7 @@ __global__ void __launch_bounds__(GT_THREADS) gn_tc_kernel(const float *__restri
         // ---- compute warps: thread t owns pixel tile * 128 + t and lane t of tensor memory
         const float thr = mask_thresh > 0.f ? mask_thresh * decode_max<float>(scratch) : INFINITY;
         const uint32_t lane_base = tmem + ((uint32_t)(warp * 32) << 16);
+        const uint32_t xsm_addr = smem_u32(bsm + (size_t)nks * 256);         // exponent pairs, four float4 (64 B) per k-step
         const int rider_per_tile = n_iters > 0 ? n_iters : 1;
         const int rider_nk = rider_per_tile * (int)((n_tiles + gridDim.x - 1) / gridDim.x);
         int rider_k = 0;
@@ -678,32 +687,37 @@ __global__ void __launch_bounds__(GT_THREADS) gn_tc_kernel(const float *__restri
                     const uint32_t b = cnt % GT_NBUF;
                     mbar_wait(bar_free + 8 * b, ((cnt / GT_NBUF) & 1) ^ 1);
                     tc_fence_after();
-                    const uint32_t col = lane_base + b * 2 * GT_CH;
+                    const uint32_t col = lane_base + b * GT_CH;
+                    // A k-step: eight exponentials, split into TF32 head and tail, one 16-column store.  A full chunk is
+                    // straight-line code (no branch between its k-steps), so that the table loads and exponent FMAs of the
+                    // next k-step are scheduled under the MUFU latency of the current one; only the last, partly filled
+                    // chunk of an energy grid takes the branchy path.
+                    auto kstep = [&](uint32_t xaddr, uint32_t tcol) {
+                        uint32_t v[16];                                        // heads of the 8 bins, then their tails
 #pragma unroll
-                    for (int s = 0; s < GT_CHUNK_KS; ++s) {
-                        const int ks = c * GT_CHUNK_KS + s;
-                        if (ks < nks) {
-                            const ulonglong2 *x = gn_tcx + ks * 4;
-                            const ulonglong2 t0a = x[0], t0b = x[1], t1a = x[2], t1b = x[3];
-                            const f32x2 t0[4] = {t0a.x, t0a.y, t0b.x, t0b.y}, t1[4] = {t1a.x, t1a.y, t1b.x, t1b.y};
-                            uint32_t hi[8], lo[8];
-#pragma unroll
-                            for (int j = 0; j < 4; ++j) {
-                                const f32x2 xx = ffma2(a2p, t1[j], fmul2(a1p, t0[j]));
-                                float x0, x1;
-                                unpack2(xx, x0, x1);
-                                const float e0 = GnMath<float>::att(x0), e1 = GnMath<float>::att(x1);
-                                hi[2 * j] = __float_as_uint(e0) & 0xffffe000u;
-                                hi[2 * j + 1] = __float_as_uint(e1) & 0xffffe000u;
-                                const f32x2 l2 = fsub2(pack2(e0, e1), pack2(__uint_as_float(hi[2 * j]), __uint_as_float(hi[2 * j + 1])));
-                                float l0, l1;
-                                unpack2(l2, l0, l1);
-                                lo[2 * j] = __float_as_uint(l0);
-                                lo[2 * j + 1] = __float_as_uint(l1);
-                            }
-                            tmem_st8(col + s * GT_KS, hi);
-                            tmem_st8(col + GT_CH + s * GT_KS, lo);
+                        for (int j = 0; j < 4; ++j) {
+                            float4 t;                                          // {-mu1 s (bins 2j, 2j+1), -mu2 s (bins 2j, 2j+1)}
+                            asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(t.x), "=f"(t.y), "=f"(t.z), "=f"(t.w) : "r"(xaddr + 16 * j));
+                            const f32x2 xx = ffma2(a2p, pack2(t.z, t.w), fmul2(a1p, pack2(t.x, t.y)));
+                            float x0, x1;
+                            unpack2(xx, x0, x1);
+                            const float e0 = GnMath<float>::att(x0), e1 = GnMath<float>::att(x1);
+                            v[2 * j] = __float_as_uint(e0) & 0xffffe000u;
+                            v[2 * j + 1] = __float_as_uint(e1) & 0xffffe000u;
+                            const f32x2 l2 = fsub2(pack2(e0, e1), pack2(__uint_as_float(v[2 * j]), __uint_as_float(v[2 * j + 1])));
+                            float l0, l1;
+                            unpack2(l2, l0, l1);
+                            v[8 + 2 * j] = __float_as_uint(l0);
+                            v[8 + 2 * j + 1] = __float_as_uint(l1);
                         }
+                        tmem_st16(tcol, v);
+                    };
+                    const uint32_t xa = xsm_addr + (uint32_t)c * (GT_CHUNK_KS * 64);
+                    if ((c + 1) * GT_CHUNK_KS <= nks) {
+#pragma unroll
+                        for (int s = 0; s < GT_CHUNK_KS; ++s) kstep(xa + 64 * s, col + s * GT_KCOLS);
+                    } else {
+                        for (int s = 0; c * GT_CHUNK_KS + s < nks; ++s) kstep(xa + 64 * s, col + s * GT_KCOLS);
                     }
                     asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
                     tc_fence_before();
@@ -973,7 +987,7 @@ static int launch_gn_tc(const void *g, const void *i0, const void *mus, int nE, 
                         void *a_out, void *scratch, bool have_max, cudaStream_t st, const GnMirrors &mir, const GnRider &rider)
 {
     const int nks = (nE + GT_KS - 1) / GT_KS;
-    const size_t smem = (size_t)nks * 1024;
+    const size_t smem = (size_t)nks * (1024 + 64);          // B operand + exponent pairs
     DEXCT_CUDA_OK(cudaFuncSetAttribute(gn_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     // CTAs per SM: 512 columns of tensor memory / GT_COLS, and what fits the shared memory.  (The occupancy calculator
     // answers 1 for a kernel that allocates tensor memory -- profiles/r02c: a grid of 148 CTAs ran at 3x the time.)
@@ -990,12 +1004,10 @@ static int launch_gn_tc(const void *g, const void *i0, const void *mus, int nE, 
     DEXCT_CUDA_OK(cudaMemsetAsync((char *)scratch + 8, 0, 8, st));                              // count of flagged pixels
     const char *sw = getenv("DEXCT_GN_TC_SWAP");                // debugging knob: LBO/SBO of the B descriptor exchanged
     {
-        ConstSlot slot(SLOT_GN, st);                          // exclusive use of gn_tcx and the staging image until the kernel has run
+        ConstSlot slot(SLOT_GN, st);                          // exclusive use of the staging image until the kernel has run
         if (!slot.ok()) return DEXCT_ECUDA;
         gn_tc_table_kernel<<<(nks * GT_KS + 127) / 128, 128, 0, st>>>((const float *)i0, (const float *)mus, nE, nks, (float *)slot.staging());
         DEXCT_CUDA_OK(cudaGetLastError());
-        DEXCT_CUDA_OK(cudaMemcpyToSymbolAsync(gn_tcx, (const float *)slot.staging() + (size_t)nks * 256, sizeof(float) * 16 * (size_t)nks, 0,
-                                              cudaMemcpyDeviceToDevice, st));
         gn_tc_kernel<<<(unsigned)grid, GT_THREADS, smem, st>>>((const float *)g, (const float *)slot.staging(), nks, P, n_iters,
                                                               (float)mask_thresh, scratch, (float *)a_out, mir, rider, sw && atoi(sw));
         DEXCT_CUDA_OK(cudaGetLastError());
