@@ -573,14 +573,19 @@ __device__ __forceinline__ void tmem_ld32(uint32_t taddr, float (&v)[32])
     for (int q = 0; q < 32; ++q) v[q] = __uint_as_float(r[q]);
 }
 // D[tmem] (+)= A[tmem] x B[smem descriptor], M128 K8, TF32 in, FP32 accumulate
+// Called by ALL lanes of a converged warp with warp-uniform arguments; one elected lane issues.  (Issued from inside an
+// `if (lane == 0)` region the operands reach the uniform registers the instruction needs through a per-lane waterfall --
+// ELECT / R2UR / BRA.U.ANY around every MMA -- and the issuing warp, not the tensor pipe, bounds the kernel: profiles/r02j.)
 __device__ __forceinline__ void tc_mma_tf32(uint32_t d_tmem, uint32_t a_tmem, uint64_t b_desc, uint32_t idesc, uint32_t accumulate)
 {
-    asm volatile("{ .reg .pred p; setp.ne.b32 p, %4, 0; tcgen05.mma.cta_group::1.kind::tf32 [%0], [%1], %2, %3, p; }" ::"r"(d_tmem),
+    asm volatile("{ .reg .pred p, q; elect.sync _|q, 0xffffffff; setp.ne.b32 p, %4, 0;\n"
+                 "  @q tcgen05.mma.cta_group::1.kind::tf32 [%0], [%1], %2, %3, p; }" ::"r"(d_tmem),
                  "r"(a_tmem), "l"(b_desc), "r"(idesc), "r"(accumulate) : "memory");
 }
 __device__ __forceinline__ void tc_commit(uint32_t bar)
 {
-    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(bar) : "memory");
+    asm volatile("{ .reg .pred q; elect.sync _|q, 0xffffffff;\n"
+                 "  @q tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0]; }" ::"r"(bar) : "memory");
 }
 __device__ __forceinline__ f32x2 fmul2(f32x2 a, f32x2 b)
 {
@@ -629,33 +634,32 @@ __global__ void __launch_bounds__(GT_THREADS, 4) gn_tc_kernel(const float *__res
     const int n_chunks = (nks + GT_CHUNK_KS - 1) / GT_CHUNK_KS;
 
     if (warp == 4) {
-        // ---- MMA issuer: one thread mirrors the loop structure of the compute warps
-        if (lane == 0) {
-            const uint64_t lbo = lbo_sbo_swapped ? 128 : 512, sbo = lbo_sbo_swapped ? 512 : 128;
-            const uint64_t desc0 = ((lbo >> 4) << 16) | ((sbo >> 4) << 32) | (1ull << 46);
-            const uint32_t bsm_addr = smem_u32(bsm);
-            uint32_t cnt = 0;
-            for (long long tile = blockIdx.x; tile < n_tiles; tile += gridDim.x)
-                for (int it = 0; it < n_iters; ++it)
-                    for (int c = 0; c < n_chunks; ++c, ++cnt) {
-                        const uint32_t b = cnt % GT_NBUF;
-                        mbar_wait(bar_full + 8 * b, (cnt / GT_NBUF) & 1);
-                        tc_fence_after();
-                        const uint32_t a_buf = tmem + b * GT_CH;
+        // ---- MMA issuer warp: mirrors the loop structure of the compute warps, converged; one elected lane issues
+        const uint64_t lbo = lbo_sbo_swapped ? 128 : 512, sbo = lbo_sbo_swapped ? 512 : 128;
+        const uint64_t desc0 = ((lbo >> 4) << 16) | ((sbo >> 4) << 32) | (1ull << 46);
+        const uint32_t bsm_addr = smem_u32(bsm);
+        uint32_t cnt = 0;
+        for (long long tile = blockIdx.x; tile < n_tiles; tile += gridDim.x)
+            for (int it = 0; it < n_iters; ++it)
+#pragma unroll 1
+                for (int c = 0; c < n_chunks; ++c, ++cnt) {
+                    const uint32_t b = cnt % GT_NBUF;
+                    mbar_wait(bar_full + 8 * b, (cnt / GT_NBUF) & 1);
+                    tc_fence_after();
+                    const uint32_t a_buf = tmem + b * GT_CH;
 #pragma unroll
-                        for (int s = 0; s < GT_CHUNK_KS; ++s) {
-                            const int ks = c * GT_CHUNK_KS + s;
-                            if (ks < nks) {
-                                const uint64_t db = desc0 | (uint64_t)(((bsm_addr + ks * 1024) & 0x3ffff) >> 4);
-                                // columns 0..15 += hi x Bhi + lo x Bhi, columns 16..31 += hi x Blo
-                                tc_mma_tf32(tmem + GT_DCOL, a_buf + s * GT_KCOLS, db, GT_IDESC32, ks > 0);
-                                tc_mma_tf32(tmem + GT_DCOL, a_buf + s * GT_KCOLS + GT_KS, db, GT_IDESC16, 1);
-                            }
+                    for (int s = 0; s < GT_CHUNK_KS; ++s) {
+                        const int ks = c * GT_CHUNK_KS + s;
+                        if (ks < nks) {
+                            const uint64_t db = desc0 | (uint64_t)(((bsm_addr + ks * 1024) & 0x3ffff) >> 4);
+                            // columns 0..15 += hi x Bhi + lo x Bhi, columns 16..31 += hi x Blo
+                            tc_mma_tf32(tmem + GT_DCOL, a_buf + s * GT_KCOLS, db, GT_IDESC32, ks > 0);
+                            tc_mma_tf32(tmem + GT_DCOL, a_buf + s * GT_KCOLS + GT_KS, db, GT_IDESC16, 1);
                         }
-                        tc_commit(bar_free + 8 * b);                  // the chunk's A operand may be overwritten once these MMAs are done
-                        if (c == n_chunks - 1) tc_commit(bar_done);   // ... and the sums of this iteration are complete
                     }
-        }
+                    tc_commit(bar_free + 8 * b);                  // the chunk's A operand may be overwritten once these MMAs are done
+                    if (c == n_chunks - 1) tc_commit(bar_done);   // ... and the sums of this iteration are complete
+                }
         __syncwarp();
     } else {
         // ---- compute warps: thread t owns pixel tile * 128 + t and lane t of tensor memory

@@ -9,7 +9,7 @@
 __device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
 
 template <bool TF32, bool A_TMEM>
-__global__ void k(long long *cyc, int N, int rep, int nacc, int nissue)
+__global__ void k(long long *cyc, int N, int rep, int nacc, int nissue, int wstride)
 {
     extern __shared__ __align__(128) unsigned char smem[];     // zeros: A [128 x 32 B] then B [256 x 32 B], core-matrix layout
     __shared__ __align__(8) unsigned long long bar;
@@ -30,7 +30,7 @@ __global__ void k(long long *cyc, int N, int rep, int nacc, int nissue)
     const uint32_t tmem = tmem_sm;
     // zero the A columns in tensor memory (columns 256..263)
     {
-        const uint32_t a = tmem + ((uint32_t)((threadIdx.x >> 5) * 32) << 16) + 256;
+        const uint32_t a = tmem + ((uint32_t)(((threadIdx.x >> 5) & 3) * 32) << 16) + 256;
         asm volatile("tcgen05.st.sync.aligned.32x32b.x8.b32 [%0], {%1, %1, %1, %1, %1, %1, %1, %1};" ::"r"(a), "r"(0u) : "memory");
         asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
     }
@@ -42,7 +42,7 @@ __global__ void k(long long *cyc, int N, int rep, int nacc, int nissue)
     const uint64_t dA = ((uint64_t)((smem_u32(smem) & 0x3ffff) >> 4)) | ((uint64_t)(128 * 16 >> 4) << 16) | ((uint64_t)(128 >> 4) << 32) | (1ull << 46);
     const uint64_t dB = ((uint64_t)((smem_u32(smem + 128 * 32) & 0x3ffff) >> 4)) | ((uint64_t)(256 * 16 >> 4) << 16) | ((uint64_t)(128 >> 4) << 32) | (1ull << 46);
     long long t0 = clock64();
-    if ((threadIdx.x & 31) == 0 && (threadIdx.x >> 5) < nissue) {       // nissue warps issue at the same time, each into its own accumulators
+    if ((threadIdx.x & 31) == 0 && (int)(threadIdx.x >> 5) % wstride == 0 && (int)(threadIdx.x >> 5) / wstride < nissue) {       // nissue warps issue at the same time (warps 0, wstride, 2 wstride, ...: wstride = 4 puts them on one scheduler)
         for (int r = 0; r < rep; ++r) {
             const uint32_t dcol = tmem + (uint32_t)((r + (threadIdx.x >> 5)) & (nacc - 1)) * 64;    // nacc (a power of two) > 1: successive MMAs feed different accumulators; no integer division in the issue loop (r02d measured the division, not the MMA)
             if (A_TMEM) {
@@ -67,7 +67,7 @@ __global__ void k(long long *cyc, int N, int rep, int nacc, int nissue)
 }
 
 template <bool TF32, bool A_TMEM>
-static void run(const char *name, int nacc, int nissue = 1)
+static void run(const char *name, int nacc, int nissue = 1, int wstride = 1)
 {
     long long *d, h[2];
     cudaMalloc(&d, 16);
@@ -77,14 +77,14 @@ static void run(const char *name, int nacc, int nissue = 1)
         long long c[2][2];
         int reps[2] = {64, 576};
         for (int q = 0; q < 2; ++q) {
-            k<TF32, A_TMEM><<<1, 128, smem>>>(d, N, reps[q], nacc, nissue);
-            k<TF32, A_TMEM><<<1, 128, smem>>>(d, N, reps[q], nacc, nissue);
+            k<TF32, A_TMEM><<<1, wstride == 1 ? 128 : 32 * wstride * nissue, smem>>>(d, N, reps[q], nacc, nissue, wstride);
+            k<TF32, A_TMEM><<<1, wstride == 1 ? 128 : 32 * wstride * nissue, smem>>>(d, N, reps[q], nacc, nissue, wstride);
             cudaError_t e = cudaDeviceSynchronize();
             if (e != cudaSuccess) { printf("%s N=%d: %s\n", name, N, cudaGetErrorString(e)); return; }
             cudaMemcpy(h, d, 16, cudaMemcpyDeviceToHost);
             c[q][0] = h[0]; c[q][1] = h[1];
         }
-        printf("%-22s %d accumulator(s) %d issuer(s) N=%3d: %7.1f cycles per MMA (SM aggregate), %6.1f per issue of one thread; %lld cycles for 64\n", name, nacc, nissue, N,
+        printf("%-22s %d accumulator(s) %d issuer(s) warp stride %d N=%3d: %7.1f cycles per MMA (SM aggregate), %6.1f per issue of one thread; %lld cycles for 64\n", name, nacc, nissue, wstride, N,
                (double)(c[1][0] - c[0][0]) / (512.0 * nissue), (double)(c[1][1] - c[0][1]) / 512.0, c[0][0]);
     }
     cudaFree(d);
@@ -97,6 +97,7 @@ int main()
         run<false, true>("bf16 K=16 A in TMEM", nacc);
     }
     for (int ni : {2, 4}) { run<true, true>("tf32 K=8  A in TMEM", 4, ni); run<true, true>("tf32 K=8  A in TMEM", 1, ni); }
+    for (int ni : {2, 4}) run<true, true>("tf32 K=8  A in TMEM", 1, ni, 4);
     run<true, false>("tf32 K=8  A in smem", 1);
     run<false, false>("bf16 K=16 A in smem", 1);
     return 0;
