@@ -600,6 +600,18 @@ __device__ __forceinline__ f32x2 fsub2(f32x2 a, f32x2 b)
     return r;
 }
 
+#ifdef GT_PROF
+// Phase clocks of CTA 0 (debug build only): [0..7] compute warp 0: free-wait, k-steps, st-wait+arrive, done-wait, ld+newton,
+// chunks, iterations, -; [8..15] MMA warp: full-wait, issue, commit, chunks, latency commit(done)->seen, -
+__device__ unsigned long long gt_prof[16];
+__device__ long long gt_prof_done_stamp;
+__device__ unsigned long long gt_cta[4096 * 3];               // per CTA: globaltimer at birth, at death, SM id
+#define GT_T(var) const long long var = clock64()
+#define GT_ADD(slot, a, b) (gt_loc[(slot) & 7] += (unsigned long long)((b) - (a)))       // registers; flushed once at the end
+#else
+#define GT_T(var)
+#define GT_ADD(slot, a, b)
+#endif
 __global__ void __launch_bounds__(GT_THREADS, 4) gn_tc_kernel(const float *__restrict__ g, const float *__restrict__ btab, int nks, long long P,
                                                            int n_iters, float mask_thresh, void *scratch, float *__restrict__ a_out,
                                                            const GnMirrors mir, const GnRider rider, int lbo_sbo_swapped)
@@ -608,11 +620,18 @@ __global__ void __launch_bounds__(GT_THREADS, 4) gn_tc_kernel(const float *__res
     float *bsm = (float *)smem_raw;                           // [nks][hi 128 floats, lo 128 floats], then [nks][4] exponent float4s
     __shared__ __align__(8) unsigned long long bars[2 * GT_NBUF + 1];
     __shared__ uint32_t tmem_base_sm;
+    __shared__ unsigned next_tile_sm[2];
     const int tid = threadIdx.x, lane = tid & 31;
     // the warp index as a value the compiler knows to be the same in all lanes: the role branches below are then uniform
     // branches and the code inside them may use the uniform datapath
     const int warp = __shfl_sync(0xffffffffu, tid >> 5, 0);
     const uint32_t bar_full = smem_u32(&bars[0]), bar_free = smem_u32(&bars[GT_NBUF]), bar_done = smem_u32(&bars[2 * GT_NBUF]);
+#ifdef GT_PROF
+    unsigned long long gt_loc[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    const long long gt_birth = clock64();
+    unsigned long long gt_birth_ns;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(gt_birth_ns));
+#endif
 
     for (int i = tid; i < nks * 68; i += GT_THREADS) ((float4 *)bsm)[i] = ((const float4 *)btab)[i];
     if (tid == 0) {
@@ -621,8 +640,19 @@ __global__ void __launch_bounds__(GT_THREADS, 4) gn_tc_kernel(const float *__res
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
     }
     if (warp == 4) {
+#ifdef GT_PROF
+        const long long ta0 = clock64();
+#endif
         asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(&tmem_base_sm)), "n"(GT_COLS) : "memory");
         asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+#ifdef GT_PROF
+        if (lane == 0) {                                      // all CTAs: time spent waiting for tensor-memory columns
+            const unsigned long long dt = (unsigned long long)(clock64() - ta0);
+            atomicAdd(&gt_prof[13], dt);
+            atomicMax(&gt_prof[14], dt);
+            if (dt > 20000) atomicAdd(&gt_prof[15], 1ull);
+        }
+#endif
     }
     asm volatile("fence.proxy.async.shared::cta;" ::: "memory");     // the B operand written above is read by the tensor core (async proxy)
     tc_fence_before();
@@ -638,14 +668,16 @@ __global__ void __launch_bounds__(GT_THREADS, 4) gn_tc_kernel(const float *__res
         const uint64_t lbo = lbo_sbo_swapped ? 128 : 512, sbo = lbo_sbo_swapped ? 512 : 128;
         const uint64_t desc0 = ((lbo >> 4) << 16) | ((sbo >> 4) << 32) | (1ull << 46);
         const uint32_t bsm_addr = smem_u32(bsm);
-        uint32_t cnt = 0;
-        for (long long tile = blockIdx.x; tile < n_tiles; tile += gridDim.x)
+        uint32_t cnt = 0, tpar = 0;
+        for (long long tile = blockIdx.x; tile < n_tiles; tile = next_tile_sm[tpar], tpar ^= 1) {
             for (int it = 0; it < n_iters; ++it)
 #pragma unroll 1
                 for (int c = 0; c < n_chunks; ++c, ++cnt) {
                     const uint32_t b = cnt % GT_NBUF;
+                    GT_T(m0);
                     mbar_wait(bar_full + 8 * b, (cnt / GT_NBUF) & 1);
                     tc_fence_after();
+                    GT_T(m1);
                     const uint32_t a_buf = tmem + b * GT_CH;
 #pragma unroll
                     for (int s = 0; s < GT_CHUNK_KS; ++s) {
@@ -657,9 +689,17 @@ __global__ void __launch_bounds__(GT_THREADS, 4) gn_tc_kernel(const float *__res
                             tc_mma_tf32(tmem + GT_DCOL, a_buf + s * GT_KCOLS + GT_KS, db, GT_IDESC16, 1);
                         }
                     }
+                    GT_T(m2);
                     tc_commit(bar_free + 8 * b);                  // the chunk's A operand may be overwritten once these MMAs are done
                     if (c == n_chunks - 1) tc_commit(bar_done);   // ... and the sums of this iteration are complete
+                    GT_T(m3);
+                    GT_ADD(8, m0, m1); GT_ADD(9, m1, m2); GT_ADD(10, m2, m3); GT_ADD(11, 0, 1);
+#ifdef GT_PROF
+                    if (c == n_chunks - 1 && blockIdx.x == 0 && lane == 0) gt_prof_done_stamp = m3;
+#endif
                 }
+            asm volatile("bar.sync 1, %0;" ::"n"(GT_THREADS) : "memory");      // the next tile of this CTA is known (see below)
+        }
         __syncwarp();
     } else {
         // ---- compute warps: thread t owns pixel tile * 128 + t and lane t of tensor memory
@@ -677,20 +717,27 @@ __global__ void __launch_bounds__(GT_THREADS, 4) gn_tc_kernel(const float *__res
                 for (int d = 0; d < rider.n; ++d) ((uint4 *)rider.dst[d])[i] = v;
             }
         };
-        uint32_t cnt = 0, done_cnt = 0;
-        for (long long tile = blockIdx.x; tile < n_tiles; tile += gridDim.x) {
+        // Tiles are handed out dynamically (a counter in the scratch block): the CTAs of an SM progress at different rates,
+        // and with a fixed share each the last of them ran alone for a quarter of the kernel (profiles/r02k: CTA deaths
+        // 335 .. 466 us).  Thread 0 draws the CTA's next tile while the current one is being worked on.
+        unsigned *tile_counter = (unsigned *)scratch + 3;
+        uint32_t cnt = 0, done_cnt = 0, tpar = 0;
+        for (long long tile = blockIdx.x; tile < n_tiles; tile = next_tile_sm[tpar], tpar ^= 1) {
+            if (tid == 0) next_tile_sm[tpar] = gridDim.x + atomicAdd(tile_counter, 1u);
             const long long p = tile * 128 + tid;
             const float g1 = p < P ? g[p] : 1.f, g2 = p < P ? g[P + p] : 1.f;
             float a1 = 1e-6f, a2 = 1e-6f;                                     // matdecomp.py:98
             bool sane = true;
             for (int it = 0; it < n_iters; ++it) {
-                if (ride) rider_slice(rider_k++);
+                if (ride && rider_k < rider_nk) rider_slice(rider_k++);       // (a CTA may draw more tiles than its even share)
                 const f32x2 a1p = pack2(a1, a1), a2p = pack2(a2, a2);
 #pragma unroll 1
                 for (int c = 0; c < n_chunks; ++c, ++cnt) {
                     const uint32_t b = cnt % GT_NBUF;
+                    GT_T(c0);
                     mbar_wait(bar_free + 8 * b, ((cnt / GT_NBUF) & 1) ^ 1);
                     tc_fence_after();
+                    GT_T(c1);
                     const uint32_t col = lane_base + b * GT_CH;
                     // A k-step: eight exponentials, split into TF32 head and tail, one 16-column store.  A full chunk is
                     // straight-line code (no branch between its k-steps), so that the table loads and exponent FMAs of the
@@ -723,19 +770,28 @@ __global__ void __launch_bounds__(GT_THREADS, 4) gn_tc_kernel(const float *__res
                     } else {
                         for (int s = 0; c * GT_CHUNK_KS + s < nks; ++s) kstep(xa + 64 * s, col + s * GT_KCOLS);
                     }
+                    GT_T(c2);
                     asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
                     tc_fence_before();
                     __syncwarp();
                     if (lane == 0) mbar_arrive(bar_full + 8 * b);
+                    GT_T(c3);
+                    GT_ADD(0, c0, c1); GT_ADD(1, c1, c2); GT_ADD(2, c2, c3); GT_ADD(5, 0, 1);
                 }
+                GT_T(d0);
                 mbar_wait(bar_done, done_cnt++ & 1);
                 tc_fence_after();
+                GT_T(d1);
                 float D[32], A[12];
                 tmem_ld32(lane_base + GT_DCOL, D);
                 tc_fence_before();
 #pragma unroll
                 for (int q = 0; q < 12; ++q) A[q] = D[q] + D[16 + q];
                 newton_update<float>(A, g1, g2, a1, a2, sane);
+#ifdef GT_PROF
+                const long long d2 = clock64() + (long long)(__float_as_int(a1) & 0);      // after the update
+                GT_ADD(3, d0, d1); GT_ADD(4, d1, d2); GT_ADD(6, 0, 1); GT_ADD(7, gt_prof_done_stamp, d1);
+#endif
             }
             if (p < P) {
                 const bool masked = g1 >= thr;                                    // matdecomp.py:196,204-205
@@ -748,10 +804,22 @@ __global__ void __launch_bounds__(GT_THREADS, 4) gn_tc_kernel(const float *__res
                     fl[4 + atomicAdd(fl + 2, 1u)] = (unsigned)p;
                 }
             }
+            asm volatile("bar.sync 1, %0;" ::"n"(GT_THREADS) : "memory");
         }
         if (ride)
             for (; rider_k < rider_nk; ++rider_k) rider_slice(rider_k);
     }
+#ifdef GT_PROF
+    if (warp == 4) gt_loc[4] = (unsigned long long)(clock64() - gt_birth);          // life of the CTA
+    if (tid == 0 && blockIdx.x < 4096) {
+        unsigned long long t, sm;
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+        asm volatile("{ .reg .u32 r; mov.u32 r, %%smid; cvt.u64.u32 %0, r; }" : "=l"(sm));
+        gt_cta[3 * blockIdx.x] = gt_birth_ns; gt_cta[3 * blockIdx.x + 1] = t; gt_cta[3 * blockIdx.x + 2] = sm;
+    }
+    if (blockIdx.x == 0 && lane == 0 && (warp == 0 || warp == 4))
+        for (int q = 0; q < (warp == 4 ? 5 : 8); ++q) gt_prof[(warp == 4 ? 8 : 0) + q] += gt_loc[q];
+#endif
     tc_fence_before();
     __syncthreads();
     if (warp == 4) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(tmem), "n"(GT_COLS) : "memory");
@@ -1005,7 +1073,7 @@ static int launch_gn_tc(const void *g, const void *i0, const void *mus, int nE, 
     if (mask_thresh > 0 && !have_max) {
         if (int e = launch_max<float>(g, P, scratch, st)) return e;
     }
-    DEXCT_CUDA_OK(cudaMemsetAsync((char *)scratch + 8, 0, 8, st));                              // count of flagged pixels
+    DEXCT_CUDA_OK(cudaMemsetAsync((char *)scratch + 8, 0, 8, st));                              // count of flagged pixels, tile counter
     const char *sw = getenv("DEXCT_GN_TC_SWAP");                // debugging knob: LBO/SBO of the B descriptor exchanged
     {
         ConstSlot slot(SLOT_GN, st);                          // exclusive use of the staging image until the kernel has run
@@ -1027,6 +1095,20 @@ static int launch_gn_tc(const void *g, const void *i0, const void *mus, int nE, 
 }  // namespace dexct
 
 using namespace dexct;
+
+#ifdef GT_PROF
+extern "C" int dexct_debug_gn_tc_ctas(unsigned long long *out, int n)
+{
+    return cudaMemcpyFromSymbol(out, gt_cta, sizeof(unsigned long long) * 3 * (size_t)n) == cudaSuccess ? DEXCT_OK : DEXCT_ECUDA;
+}
+extern "C" int dexct_debug_gn_tc_prof(unsigned long long *out16, int reset)
+{
+    unsigned long long z[16] = {0};
+    if (cudaMemcpyFromSymbol(out16, gt_prof, sizeof(z)) != cudaSuccess) return DEXCT_ECUDA;
+    if (reset && cudaMemcpyToSymbol(gt_prof, z, sizeof(z)) != cudaSuccess) return DEXCT_ECUDA;
+    return DEXCT_OK;
+}
+#endif
 
 extern "C" size_t dexct_gn_scratch_bytes(int64_t P, int32_t dtype)
 {
