@@ -734,21 +734,21 @@ __global__ void __launch_bounds__(GT_THREADS, 4) gn_tc_kernel(const float *__res
 #pragma unroll 1
                 for (int c = 0; c < n_chunks; ++c, ++cnt) {
                     const uint32_t b = cnt % GT_NBUF;
-                    GT_T(c0);
-                    mbar_wait(bar_free + 8 * b, ((cnt / GT_NBUF) & 1) ^ 1);
-                    tc_fence_after();
-                    GT_T(c1);
-                    const uint32_t col = lane_base + b * GT_CH;
+                    GT_T(cb);
                     // A k-step: eight exponentials, split into TF32 head and tail, one 16-column store.  A full chunk is
                     // straight-line code (no branch between its k-steps), so that the table loads and exponent FMAs of the
                     // next k-step are scheduled under the MUFU latency of the current one; only the last, partly filled
                     // chunk of an energy grid takes the branchy path.
-                    auto kstep = [&](uint32_t xaddr, uint32_t tcol) {
-                        uint32_t v[16];                                        // heads of the 8 bins, then their tails
+                    // A k-step: eight exponentials, each split into its TF32 head and tail -- 16 words for one 16-column store.
+                    // A full chunk is straight-line code, so that the table loads and exponent FMAs of the next k-step are
+                    // scheduled under the MUFU latency of the current one; only the last, partly filled chunk of an energy grid
+                    // takes the branchy path.  The values are computed BEFORE waiting for the buffer: the wait (a ~100-cycle
+                    // round trip to the barrier even when the buffer is free) then runs under the exponentials in flight.
+                    auto kvals = [&](uint32_t xaddr, uint32_t (&v)[16]) {
 #pragma unroll
                         for (int j = 0; j < 4; ++j) {
                             float4 t;                                          // {-mu1 s (bins 2j, 2j+1), -mu2 s (bins 2j, 2j+1)}
-                            asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(t.x), "=f"(t.y), "=f"(t.z), "=f"(t.w) : "r"(xaddr + 16 * j));
+                            asm("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(t.x), "=f"(t.y), "=f"(t.z), "=f"(t.w) : "r"(xaddr + 16 * j));
                             const f32x2 xx = ffma2(a2p, pack2(t.z, t.w), fmul2(a1p, pack2(t.x, t.y)));
                             float x0, x1;
                             unpack2(xx, x0, x1);
@@ -761,14 +761,28 @@ __global__ void __launch_bounds__(GT_THREADS, 4) gn_tc_kernel(const float *__res
                             v[8 + 2 * j] = __float_as_uint(l0);
                             v[8 + 2 * j + 1] = __float_as_uint(l1);
                         }
-                        tmem_st16(tcol, v);
                     };
                     const uint32_t xa = xsm_addr + (uint32_t)c * (GT_CHUNK_KS * 64);
+                    const uint32_t col = lane_base + b * GT_CH;
                     if ((c + 1) * GT_CHUNK_KS <= nks) {
+                        uint32_t v[GT_CHUNK_KS][16];
 #pragma unroll
-                        for (int s = 0; s < GT_CHUNK_KS; ++s) kstep(xa + 64 * s, col + s * GT_KCOLS);
+                        for (int s = 0; s < GT_CHUNK_KS; ++s) kvals(xa + 64 * s, v[s]);
+                        GT_T(c0);
+                        mbar_wait(bar_free + 8 * b, ((cnt / GT_NBUF) & 1) ^ 1);
+                        tc_fence_after();
+                        GT_T(c1);
+                        GT_ADD(0, c0, c1);
+#pragma unroll
+                        for (int s = 0; s < GT_CHUNK_KS; ++s) tmem_st16(col + s * GT_KCOLS, v[s]);
                     } else {
-                        for (int s = 0; c * GT_CHUNK_KS + s < nks; ++s) kstep(xa + 64 * s, col + s * GT_KCOLS);
+                        mbar_wait(bar_free + 8 * b, ((cnt / GT_NBUF) & 1) ^ 1);
+                        tc_fence_after();
+                        for (int s = 0; c * GT_CHUNK_KS + s < nks; ++s) {
+                            uint32_t v[16];
+                            kvals(xa + 64 * s, v);
+                            tmem_st16(col + s * GT_KCOLS, v);
+                        }
                     }
                     GT_T(c2);
                     asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
@@ -776,7 +790,7 @@ __global__ void __launch_bounds__(GT_THREADS, 4) gn_tc_kernel(const float *__res
                     __syncwarp();
                     if (lane == 0) mbar_arrive(bar_full + 8 * b);
                     GT_T(c3);
-                    GT_ADD(0, c0, c1); GT_ADD(1, c1, c2); GT_ADD(2, c2, c3); GT_ADD(5, 0, 1);
+                    GT_ADD(1, cb, c2); GT_ADD(2, c2, c3); GT_ADD(5, 0, 1);
                 }
                 GT_T(d0);
                 mbar_wait(bar_done, done_cnt++ & 1);
