@@ -205,6 +205,39 @@ __device__ __forceinline__ void newton_update(const R *A, R g1, R g2, R &a1, R &
     if (sizeof(R) == 4) sane = sane && det > (R)0 && h11 > (R)0 && fmin(a1, a2) > (R)GN_A_FLOOR;
 }
 
+// The same step for the tensor-core kernel, where the instructions of the update are no longer hidden behind an FMA-bound
+// loop (they were 14 % of the kernel: profiles/r02n): three approximate reciprocals (MUFU.RCP, 1 ulp) instead of five IEEE
+// divisions.  g/nu - 1 is formed with one FMA, so the rounding of the quotient does not enter the residual twice.
+__device__ __forceinline__ float rcp_fast(float x)
+{
+    float y;
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
+    return y;
+}
+__device__ __forceinline__ void newton_update_fast(const float *A, float g1, float g2, float &a1, float &a2, bool &sane)
+{
+    const float nu1 = A[0], nu2 = A[6];
+    float big = fmaxf(fabsf(A[3]), fabsf(A[9]));
+    big = fmaxf(big, fmaxf(fmaxf(fabsf(A[4]), fabsf(A[10])), fmaxf(fabsf(A[5]), fabsf(A[11]))));
+    sane = sane && (nu1 < 1e18f) && (nu2 < 1e18f) && (big < 1e30f) && (nu1 > 0.f) && (nu2 > 0.f);
+    const float i1 = rcp_fast(nu1), i2 = rcp_fast(nu2);
+    const float q1 = g1 * i1, q2 = g2 * i2;
+    const float r1 = fmaf(g1, i1, -1.f), r2 = fmaf(g2, i2, -1.f);   // g/nu - 1
+    const float s1 = q1 * i1, s2 = q2 * i2;                        // g/nu^2
+    const float d1 = r1 * A[1] + r2 * A[7];
+    const float d2 = r1 * A[2] + r2 * A[8];
+    const float h11 = -(r1 * A[3] + r2 * A[9]) + (s1 * A[1] * A[1] + s2 * A[7] * A[7]);
+    const float h12 = -(r1 * A[4] + r2 * A[10]) + (s1 * A[1] * A[2] + s2 * A[7] * A[8]);
+    const float h22 = -(r1 * A[5] + r2 * A[11]) + (s1 * A[2] * A[2] + s2 * A[8] * A[8]);
+    const float w = h12 * h12;
+    const float err = fmaf(-h12, h12, w);
+    const float det = fmaf(h11, h22, -w) + err;
+    const float inv = rcp_fast(det);
+    a1 -= (h22 * d1 - h12 * d2) * inv;
+    a2 -= (h11 * d2 - h12 * d1) * inv;
+    sane = sane && det > 0.f && h11 > 0.f && fminf(a1, a2) > GN_A_FLOOR;
+}
+
 template <typename R, int PX, bool CTAB, int VAR>
 __global__ void __launch_bounds__(256, (PX == 4 && CTAB) ? 3 : 1) gn_kernel(const R *__restrict__ g, const R *__restrict__ i0, const R *__restrict__ mus,
                                                  int nE, long long P, int n_iters, R mask_thresh, void *scratch,
@@ -801,7 +834,7 @@ __global__ void __launch_bounds__(GT_THREADS, 4) gn_tc_kernel(const float *__res
                 tc_fence_before();
 #pragma unroll
                 for (int q = 0; q < 12; ++q) A[q] = D[q] + D[16 + q];
-                newton_update<float>(A, g1, g2, a1, a2, sane);
+                newton_update_fast(A, g1, g2, a1, a2, sane);
 #ifdef GT_PROF
                 const long long d2 = clock64() + (long long)(__float_as_int(a1) & 0);      // after the update
                 GT_ADD(3, d0, d1); GT_ADD(4, d1, d2); GT_ADD(6, 0, 1); GT_ADD(7, gt_prof_done_stamp, d1);
