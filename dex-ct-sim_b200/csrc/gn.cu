@@ -1187,8 +1187,10 @@ static int gn_decompose_impl(const void *g, const void *i0, const void *mus, int
     cudaStream_t st = (cudaStream_t)stream;
     const bool have = scratch_has_max != 0;
     if (dtype == DEXCT_F32) {
-        const char *tc = getenv("DEXCT_GN_TC");          // 1: tensor-core kernel (tcgen05), 0: FP32-pipe kernel
-        if (tc && atoi(tc) && (nE + GT_KS - 1) / GT_KS <= GT_MAX_KS)
+        // Default: the tensor-core kernel (tcgen05 + tensor memory), 1.44x the FP32-pipe kernel at C2 size; energy grids
+        // beyond 448 bins (the B operand would not fit its staging slot) and DEXCT_GN_TC=0 take the FP32-pipe kernel.
+        const char *tc = getenv("DEXCT_GN_TC");
+        if ((!tc || atoi(tc)) && (nE + GT_KS - 1) / GT_KS <= GT_MAX_KS)
             return launch_gn_tc(g, i0, mus, nE, P, n_iters, mask_thresh, a_out, scratch, have, st, mir, rider);
         const char *px = getenv("DEXCT_GN_PX");          // tuning knob (pixels per thread)
         const int npx = px ? atoi(px) : 4;            // 4: the table row of a bin is fetched once for four pixels

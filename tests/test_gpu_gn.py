@@ -23,6 +23,19 @@ from oracle import gn_oracle
 pytestmark = pytest.mark.gpu
 
 
+@pytest.fixture(autouse=True, params=['tensor-core', 'fp32-pipe'])
+def f32_kernel(request):
+    """Every test of this module runs twice: single precision through the tensor-core kernel (gn_tc_kernel, the default up
+    to 448 energy bins) and through the FP32-pipe kernel (gn_kernel: DEXCT_GN_TC=0, and the fallback beyond 448 bins)."""
+    old = os.environ.get('DEXCT_GN_TC')
+    os.environ['DEXCT_GN_TC'] = '1' if request.param == 'tensor-core' else '0'
+    yield request.param
+    if old is None:
+        os.environ.pop('DEXCT_GN_TC', None)
+    else:
+        os.environ['DEXCT_GN_TC'] = old
+
+
 def _load(golden_dir, name):
     return np.load(os.path.join(golden_dir, name + '.npz'))
 
