@@ -20,7 +20,8 @@ the decomposition kernel (`fused`), large ones go out on the copy engines beside
 `e2e`     : the same work through the reference-facing Python entry points (get_sinos / get_basismat_sinos) with host
             numpy arrays in and out; every step uploads the phantom again and reads the results back.
 `roofline`: the 3-D Siddon kernel against the bytes-per-ray HBM roofline of SURVEY.md section 8(d); `roofline_gn`: the GN
-            kernel against the FP32 FMA pipe.
+            kernel against the MUFU unit (tensor-core kernel: one ex2 per pixel, bin and iteration is what stays on the SM)
+            or, with DEXCT_GN_TC=0, against the FP32 FMA pipe.
 `cpu_baseline` / `--impl reference`: the CPU oracle (oracle/: C restatement of Siddon 1985 with OpenMP + the numpy
             restatement of the reference's optimize_sino_cpu, one process per core) on a bounded view sample of the SAME scan.
 """
@@ -611,8 +612,22 @@ class ScanBench:
                 'traffic_source': traffic_src, 'algorithmic_bytes_per_launch': self.rays_local * bytes_per_ray,
                 'kernel': kern, 'bytes_per_ray': bytes_per_ray, 'segments_per_ray': seg, 'launch_ms': t['siddon'],
                 'peak_source': ('MEASURED_PEAKS.json hbm_gbs' if peaks else 'fallback') + (f' x {ws} GPUs' if ws > 1 else '')}
-        roof_gn = {'bound': 'fp32_fma', 'achieved': gn_ach, 'peak': fma_peak, 'unit': 'TFLOP/s', 'frac': gn_ach / fma_peak,
-                   'kernel': 'gn_kernel', 'flop_per_pixel': 28.0 * self.nE * GN_ITERS, 'launch_ms': t['gn'], 'sm_mhz': sm_mhz}
+        if os.environ.get('DEXCT_GN_TC', '1') != '0' and self.nE <= 448:
+            # tensor-core kernel: the twelve moment sums run on tcgen05 (3xTF32), what is left on the SM is one MUFU.EX2 per
+            # (pixel, bin, iteration) -- the unit that bounds it: 15.9 ex2 per clock and SM measured (tools/microbench/xu_rate.cu,
+            # profiles/r02m_xu_rate.txt).  The FP32-FMA figure of the earlier rounds is kept beside it for continuity: it can
+            # exceed 1 now, the FMAs are no longer on that pipe.
+            ex2 = float(self.nE) * GN_ITERS * self.rays_total
+            xu_peak = 15.9 * 148 * sm_mhz * 1e6 / 1e9 * ws                # Gex2/s
+            xu_ach = ex2 / (t['gn'] * 1e-3) / 1e9
+            roof_gn = {'bound': 'mufu', 'achieved': xu_ach, 'peak': xu_peak, 'unit': 'Gex2/s', 'frac': xu_ach / xu_peak,
+                       'kernel': 'gn_tc_kernel', 'ex2_per_pixel': float(self.nE) * GN_ITERS, 'launch_ms': t['gn'], 'sm_mhz': sm_mhz,
+                       'peak_source': '15.9 MUFU.EX2 per clock and SM (measured, profiles/r02m_xu_rate.txt) x 148 SMs x sm_mhz',
+                       'fp32_fma_equivalent': {'achieved': gn_ach, 'peak': fma_peak, 'unit': 'TFLOP/s', 'frac': gn_ach / fma_peak,
+                                               'flop_per_pixel': 28.0 * self.nE * GN_ITERS}}
+        else:
+            roof_gn = {'bound': 'fp32_fma', 'achieved': gn_ach, 'peak': fma_peak, 'unit': 'TFLOP/s', 'frac': gn_ach / fma_peak,
+                       'kernel': 'gn_kernel', 'flop_per_pixel': 28.0 * self.nE * GN_ITERS, 'launch_ms': t['gn'], 'sm_mhz': sm_mhz}
         return roof, roof_gn
 
     def collective_text(self):
