@@ -721,15 +721,43 @@ def e2e_leg(name, dev, rank, ws, dtype, steps):
     if ws > 1:
         dist.all_reduce(dt, op=dist.ReduceOp.MAX)
     FP.clear_cache()
+
+    # the call sequence of /root/reference/main.py:109-120,153: one get_sino per spectrum (the second is served from the path
+    # lengths the first one stored), then get_basismat_sinos
+    def step_main_py():
+        FP.clear_cache()
+        raw_lo, log_lo = FP.get_sino(ct, ph, lo)
+        raw_hi, log_hi = FP.get_sino(ct, ph, hi)
+        m1, m2 = matdecomp.get_basismat_sinos(ct, raw_lo, raw_hi, lo, hi, n_iters=GN_ITERS, mask_thresh=MASK_THRESH)
+        return raw_lo, m1
+
+    two = None
+    try:
+        step_main_py()
+        barrier()
+        t0 = time.perf_counter()
+        for _ in range(max(1, steps - 1)):
+            step_main_py()
+        barrier()
+        dt2 = torch.tensor([(time.perf_counter() - t0) / max(1, steps - 1)], dtype=torch.float64, device=dev)
+        if ws > 1:
+            dist.all_reduce(dt2, op=dist.ReduceOp.MAX)
+        two = {'value': rays / float(dt2[0]), 'unit': UNIT, 'ms_per_step': 1e3 * float(dt2[0]), 'steps': max(1, steps - 1),
+               'api': 'get_sino(spec1), get_sino(spec2) [second call from the stored path lengths], get_basismat_sinos -- the '
+                      'call sequence of the reference main.py:109-120,153'}
+    except Exception as ex:                                               # noqa: BLE001
+        two = {'unavailable': f'{type(ex).__name__}: {ex}'[:200]}
+    FP.clear_cache()
     # up: labels + the two float64 count sinograms handed to get_basismat_sinos (they sit in page-locked memory: get_sinos
     # returned them); down: 2 x (raw, log) + 2 basis sinograms, float64 like the reference's arrays; summed over ranks; the
     # KB-sized tables are uploaded once per content
     h2d = ws * label_bytes + 2 * rays * 8
     d2h = 6 * rays * 8
     return {'value': rays / float(dt[0]), 'unit': UNIT, 'h2d_bytes_per_step': int(h2d), 'd2h_bytes_per_step': int(d2h),
-            'ms_per_step': 1e3 * float(dt[0]), 'steps': steps, 'config': name,
+            'ms_per_step': 1e3 * float(dt[0]), 'steps': steps, 'config': name, 'main_py_call_sequence': two,
             'api': 'xtomosim.forward_project.get_sinos + matdecomp.get_basismat_sinos (float64 numpy in/out through page-locked '
-                   'buffers, phantom re-uploaded and re-laid-out every step'
+                   'buffers, in view chunks whose host copies overlap the kernels of the next ones; phantom re-uploaded and '
+                   're-laid-out every step'
                    + (')' if ws == 1 else '; every rank keeps the host arrays of its own view range, bytes summed over ranks)')}, None
 
 

@@ -86,6 +86,72 @@ def _host_f64(t):
     return h.numpy()
 
 
+PIPELINE_MIN_BYTES = 512 << 20       # host sinograms at least this large are decomposed in chunks (see below)
+
+
+def _decompose_host_pipelined(sinos, i0, mus, n_iters, mask_thresh, code, reduce_max_over_ranks=False):
+    """Two LARGE host count sinograms -> float64 host result, in chunks of the leading axis: the upload of the next chunks
+    (stream `up`), the Newton iterations of the current one and the float64 download of the finished ones (stream `down`)
+    run side by side -- the reference-shaped API moves 8 bytes per pixel and sinogram in and out (17.7 GB for configuration
+    C5), which costs more time on the PCIe link than the kernel takes.  The air threshold needs the maximum of the WHOLE
+    first measurement (matdecomp.py:196), so the first measurement goes up first and its chunk maxima are combined
+    (gn_air_key) before the first chunk is decomposed.  Pixels are independent: same results as the one-shot path."""
+    from dexct.ops import gn_air_key
+    td = torch.float32 if code == 0 else torch.float64
+    dev = torch.device('cuda', torch.cuda.current_device())
+    host = []
+    for sg in sinos:
+        a = np.asarray(sg)
+        if a.dtype not in (np.float32, np.float64) or not a.flags.c_contiguous:
+            a = np.ascontiguousarray(a, dtype=np.float64)
+        host.append(torch.from_numpy(a))
+    if tuple(host[0].shape) != tuple(host[1].shape):
+        raise ValueError('the two sinograms must have the same shape')
+    shape = tuple(host[0].shape)
+    n0 = shape[0]
+    n_chunks = int(min(16, max(2, -(-host[0].numel() * 8 // (1 << 30)))))
+    step = -(-n0 // n_chunks)
+    spans = [(a, min(step, n0 - a)) for a in range(0, n0, step)]
+    out_h = torch.empty(shape + (2,), dtype=torch.float64, pin_memory=True)
+    up, down = torch.cuda.Stream(device=dev), torch.cuda.Stream(device=dev)
+    main = torch.cuda.current_stream(dev)
+    bufs = [torch.empty((2, n) + shape[1:], dtype=td, device=dev) for _, n in spans]
+    ev = [[torch.cuda.Event(), torch.cuda.Event()] for _ in spans]
+    with torch.cuda.stream(up):
+        up.wait_stream(main)
+        for m in range(2):                                # all of measurement 1 first: its maximum sets the air threshold
+            for k, (a, n) in enumerate(spans):
+                bufs[k][m].copy_(host[m][a:a + n], non_blocking=True)
+                ev[k][m].record()
+    for b in bufs:
+        b.record_stream(up)
+    key = None
+    if mask_thresh > 0:
+        for k in range(len(spans)):
+            main.wait_event(ev[k][0])
+            kk = gn_air_key(bufs[k][0], dtype=code)
+            kv = kk.view(torch.int64) if code == 1 else kk[:4].view(torch.int32)
+            if key is None:
+                key, key_v = kk, kv
+            else:
+                torch.maximum(key_v, kv, out=key_v)
+        if reduce_max_over_ranks:                         # view shards: the threshold of the unsharded sinogram
+            import torch.distributed as tdist
+            tdist.all_reduce(key_v, op=tdist.ReduceOp.MAX)
+    for k, (a, n) in enumerate(spans):
+        main.wait_event(ev[k][0])
+        main.wait_event(ev[k][1])
+        o = gn_decompose(bufs[k], i0, mus, n_iters, mask_thresh=mask_thresh, dtype=code, air_key=key)
+        done = torch.cuda.Event()
+        done.record()
+        with torch.cuda.stream(down):
+            down.wait_event(done)
+            out_h[a:a + n].copy_(o, non_blocking=True)
+        o.record_stream(down)
+    down.synchronize()
+    return out_h.numpy()
+
+
 def optimize_sino(Sino_gg, ee, i0, mus, n_iters, verbose=True, dtype=None, mask_thresh=0.0, to_host=True,
                   reduce_max_over_ranks=False):
     """GPU Newton iterations; signature of matdecomp.py:20 (``ee`` is unused there too).
@@ -125,6 +191,10 @@ def optimize_sino(Sino_gg, ee, i0, mus, n_iters, verbose=True, dtype=None, mask_
     else:
         if len(Sino_gg) != 2:
             raise ValueError('Sino_gg must hold two measurements')
+        first = Sino_gg[0]
+        if (to_host and not isinstance(first, torch.Tensor) and not isinstance(Sino_gg[1], torch.Tensor)
+                and np.ndim(first) >= 2 and np.shape(first)[0] >= 2 and np.size(first) * 8 >= PIPELINE_MIN_BYTES):
+            return _decompose_host_pipelined([Sino_gg[0], Sino_gg[1]], i0, mus, n_iters, mask_thresh, code, reduce_max_over_ranks)
         g = _counts_to_device([Sino_gg[0], Sino_gg[1]], td)
     out = gn_decompose(g, i0, mus, n_iters, mask_thresh=mask_thresh, dtype=code,
                        reduce_max_over_ranks=reduce_max_over_ranks)
@@ -152,6 +222,8 @@ def do_matdecomp_gn(ct, sino1, sino2, spec1, spec2, n_iters, mask_thresh=0.0, to
             raise ValueError(f'sinograms have {sino1.shape[0]} views: expected the whole scan ({n_views})'
                              + ('' if config.gather_views else f' or this rank\'s range ({nv})'))
         # the air threshold needs the maximum over the whole sinogram: one integer MAX all-reduce between the shards
+        if to_host and not config.gather_views:          # the rank's own range, host to host (chunked when large)
+            return optimize_sino(part, ee, i0, mus, n_iters, mask_thresh=mask_thresh, to_host=True, reduce_max_over_ranks=True)
         local = optimize_sino(part, ee, i0, mus, n_iters, mask_thresh=mask_thresh, to_host=False, reduce_max_over_ranks=True)
         full = dist.all_gather_views(local, n_views, dim=0) if config.gather_views else local
         return _host_f64(full) if to_host else full

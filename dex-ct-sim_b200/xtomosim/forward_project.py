@@ -194,12 +194,78 @@ def _to_host(tensors, ct):
     return out
 
 
+PIPELINE_MIN_BYTES = 512 << 20       # host results at least this large are produced in view chunks (see _project_to_host)
+
+
+def _project_to_host(ct, phantom, specs):
+    """get_sino / get_sinos for LARGE scans: the projection runs in chunks of views and the float64 copy of every finished
+    chunk travels to page-locked host memory on a side stream while the next chunk is being traced -- the reference-shaped
+    API hands back 8 bytes per ray, sinogram and spectrum (17.7 GB for configuration C5), which costs more time on the PCIe
+    link than the kernels take.  Same arithmetic, same results as the one-shot path (a view range on its own equals the same
+    views inside the whole scan, tests/test_gpu_siddon.py).  Returns None when the call should take the one-shot path:
+    small results, view shards that are gathered, counting noise, several energy grids."""
+    code = dtype_code(config.dtype)
+    rank, ws = dist.world() if config.shard_views else (0, 1)
+    if ws > 1 and config.gather_views:
+        return None
+    if noise_enabled(ct):
+        return None
+    if not all(len(s.E) == len(specs[0].E) and np.array_equal(s.E, specs[0].E) for s in specs) or len(specs) > 4:
+        return None
+    v0, nv = dist.shard_range(ct.N_proj, rank, ws)
+    per_view = ct.N_rows * ct.N_channels
+    total = 2 * len(specs) * nv * per_view * 8
+    if total < PIPELINE_MIN_BYTES or nv < 2:
+        return None
+    st = _get_state(ct, phantom)
+    keep_L = config.cache_lengths and len(specs) == 1
+    if keep_L and st.L is not None and st.L_dtype == code and st.L.shape[0] == nv:
+        return None                                      # a second get_sino call: served from the stored lengths
+    E = specs[0].E
+    mu = phantom.mu_table(E)
+    W = np.stack([spectral_weights(ct, sp) for sp in specs])
+    nS = len(specs)
+    n_chunks = int(min(16, max(2, -(-total // (2 << 30)))))
+    step = -(-nv // n_chunks)
+    shape = (nS, nv, ct.N_rows, ct.N_channels)
+    h_c = torch.empty(shape, dtype=torch.float64, pin_memory=True)
+    h_l = torch.empty(shape, dtype=torch.float64, pin_memory=True)
+    dev = st.projector.device
+    td = torch.float32 if code == 0 else torch.float64
+    L_full = torch.empty((nv, ct.N_rows, ct.N_channels, mu.shape[0]), dtype=td, device=dev) if keep_L else None
+    side = torch.cuda.Stream(device=dev)
+    with torch.cuda.device(dev):
+        for a in range(0, nv, step):
+            n = min(step, nv - a)
+            c, lg, _ = st.projector.project(mu, W, view_begin=v0 + a, view_count=n, dtype=code, want_log=True,
+                                            want_L=keep_L, L=None if L_full is None else L_full[a:a + n])
+            done = torch.cuda.Event()
+            done.record()
+            with torch.cuda.stream(side):
+                side.wait_event(done)
+                for sp in range(nS):                     # conversion to float64 on the device, then one DMA per block
+                    h_c[sp, a:a + n].copy_(c[sp], non_blocking=True)
+                    h_l[sp, a:a + n].copy_(lg[sp], non_blocking=True)
+            c.record_stream(side)
+            lg.record_stream(side)
+        side.synchronize()
+    if keep_L:
+        st.L, st.L_dtype = L_full, code
+    raw, log = h_c.numpy(), h_l.numpy()
+    if ct.N_rows == 1:
+        raw, log = raw[..., 0, :], log[..., 0, :]
+    return [(raw[sp], log[sp]) for sp in range(nS)]
+
+
 def get_sino(ct, phantom, spec):
     """Forward-project ``phantom`` with scanner ``ct`` and spectrum ``spec``.
 
     Returns ``(sino_raw, sino_log)``: detected counts and ``-ln(counts / unattenuated counts)``, each a float64 numpy
     array ``[N_proj, N_channels]`` (``[N_proj, N_rows, N_channels]`` for multi-row scanners).
     """
+    piped = _project_to_host(ct, phantom, [spec])
+    if piped is not None:
+        return piped[0]
     (c, lg), = _project_groups(ct, phantom, [spec])[0]
     raw, log = _to_host([c[0], lg[0]], ct)
     return raw, log
@@ -208,6 +274,9 @@ def get_sino(ct, phantom, spec):
 def get_sinos(ct, phantom, specs):
     """Extension: all spectra of a multi-energy acquisition in one traversal (one fused kernel when they share an
     energy grid).  Returns a list of ``(sino_raw, sino_log)``."""
+    piped = _project_to_host(ct, phantom, list(specs))
+    if piped is not None:
+        return piped
     groups = _project_groups(ct, phantom, list(specs))[0]
     flat = _to_host([t for c, lg in groups for t in (c, lg)], ct)      # [n_in_group, views, (rows,) ch] each
     out = []

@@ -80,3 +80,38 @@ def test_main_py_call_sequence(tmp_path, golden_dir):
                 assert recon_raw.shape == (N_matrix, N_matrix) and np.isfinite(recon_raw).all()
             # (no level check on the basis images: the rays through the steel and titanium inserts are photon-starved at
             # 80 kV and decompose to huge values of either sign -- in the reference as well -- which streak the image)
+
+
+@pytest.mark.parametrize('cfg,n_spec', [('C2', 2), ('C4', 2), ('C4', 1)])
+def test_chunked_host_paths_equal_the_one_shot_paths(cfg, n_spec, monkeypatch):
+    """Large scans take get_sino(s) / get_basismat_sinos in view chunks, with the host copies of finished chunks overlapping the
+    kernels of the next ones (forward_project._project_to_host, matdecomp._decompose_host_pipelined).  Forced here on a small
+    scan: bit-identical arrays, including a second get_sino call served from the stored lengths and the air mask, whose
+    threshold comes from the maximum over ALL chunks."""
+    import matdecomp
+    from dexct import synthetic as S
+    from xtomosim import forward_project as FP
+    ct, ph, lo, hi = S.make_config(cfg, n=64, nz=48 if cfg == 'C4' else None, n_views=37)
+    specs = [lo, hi][:n_spec]
+
+    def run():
+        FP.clear_cache()
+        if n_spec == 1:
+            first = FP.get_sino(ct, ph, lo)
+            second = FP.get_sino(ct, ph, hi)                       # same energy grid: served from the stored lengths
+            return [first, second]
+        return FP.get_sinos(ct, ph, specs)
+    want = run()
+    monkeypatch.setattr(FP, 'PIPELINE_MIN_BYTES', 0)
+    got = run()
+    for (r0, l0), (r1, l1) in zip(want, got):
+        assert r1.dtype == np.float64 and r1.shape == r0.shape
+        assert np.array_equal(r0, r1) and np.array_equal(l0, l1)
+    raw_lo, raw_hi = want[0][0], want[1][0]
+    m_want = matdecomp.get_basismat_sinos(ct, raw_lo, raw_hi, lo, hi, n_iters=8)
+    monkeypatch.setattr(matdecomp, 'PIPELINE_MIN_BYTES', 0)
+    m_got = matdecomp.get_basismat_sinos(ct, raw_lo, raw_hi, lo, hi, n_iters=8)
+    for a, b in zip(m_want, m_got):
+        assert b.dtype == np.float64 and np.array_equal(a, b)
+    assert (m_got[0] == 0).any() and (m_got[0] != 0).any()         # the air mask acted, and not everywhere
+    FP.clear_cache()
