@@ -23,11 +23,11 @@ _state = {}      # (id(ct), id(phantom)) -> _ScanState
 class _ScanState:
     """Prepared device workspace of one (ct, phantom) pair and, optionally, its traced path lengths."""
 
-    def __init__(self, ct, phantom, signature):
+    def __init__(self, ct, phantom, signature, staged=None):
         self.signature = signature
         self.ct_ref = weakref.ref(ct)
         self.ph_ref = weakref.ref(phantom)
-        labels, voxel = _labels_for(ct, phantom)
+        labels, voxel = _labels_for(ct, phantom, staged)
         scan = make_scan(ct.N_proj, ct.N_channels, ct.gamma_fan, ct.SID, ct.SDD, n_rows=ct.N_rows, h_iso=ct.h_iso,
                          rotation=ct.rotation, beta0=ct.beta0)
         # host label arrays of moderate size: their maximum costs microseconds here and saves the projector a device
@@ -38,11 +38,13 @@ class _ScanState:
         self.L_dtype = None
 
 
-def _labels_for(ct, phantom):
-    """Single-row scans image slice ``z_index`` of the phantom (params.txt:12,16: Nz = 1, z_index = 0)."""
+def _labels_for(ct, phantom, staged=None):
+    """Single-row scans image slice ``z_index`` of the phantom (params.txt:12,16: Nz = 1, z_index = 0).  ``staged``: the
+    device copy of ``phantom.M`` that _signature already made (large host volumes)."""
+    M = phantom.M if staged is None else staged
     if ct.N_rows == 1:
-        return phantom.M[phantom.z_index:phantom.z_index + 1], (phantom.dx, phantom.dy, phantom.dz)
-    return phantom.M, (phantom.dx, phantom.dy, phantom.dz)
+        return M[phantom.z_index:phantom.z_index + 1], (phantom.dx, phantom.dy, phantom.dz)
+    return M, (phantom.dx, phantom.dy, phantom.dz)
 
 
 def _content_digest(lab):
@@ -80,20 +82,33 @@ def _content_digest(lab):
     return zlib.crc32(np.asarray(crcs, dtype=np.uint32).tobytes())
 
 
+STAGE_MIN_BYTES = 64 << 20
+
+
 def _signature(ct, phantom):
+    """(signature, staged): large HOST volumes are digested on the device -- the upload (20 ms for the 1 GiB labels of
+    configuration C5, from page-locked memory) is needed anyway whenever the workspace has to be rebuilt, and the device
+    digest of the copy costs a millisecond where the threaded CRC of the host array cost 100 ms per get_sino call.  The copy
+    is handed on to the projector when the signature turns out to be new, dropped otherwise."""
     lab = phantom.M
+    staged = None
+    if isinstance(lab, np.ndarray) and lab.nbytes >= STAGE_MIN_BYTES and lab.dtype == np.uint8 and torch.cuda.is_available():
+        staged = torch.from_numpy(np.ascontiguousarray(lab)).to(torch.device('cuda', torch.cuda.current_device()), non_blocking=True)
+        digest = _content_digest(staged)
+    else:
+        digest = _content_digest(lab)
     return (ct.N_proj, ct.N_channels, ct.N_rows, ct.gamma_fan, ct.SID, ct.SDD, ct.h_iso, ct.rotation, ct.beta0,
-            tuple(lab.shape), phantom.dx, phantom.dy, phantom.dz, phantom.z_index, _content_digest(lab))
+            tuple(lab.shape), phantom.dx, phantom.dy, phantom.dz, phantom.z_index, digest), staged
 
 
 def _get_state(ct, phantom):
     key = (id(ct), id(phantom))
-    sig = _signature(ct, phantom)
+    sig, staged = _signature(ct, phantom)
     st = _state.get(key)
     if st is None or st.signature != sig or st.ct_ref() is not ct or st.ph_ref() is not phantom:
         for k in [k for k, v in _state.items() if v.ct_ref() is None or v.ph_ref() is None]:
             del _state[k]
-        st = _ScanState(ct, phantom, sig)
+        st = _ScanState(ct, phantom, sig, staged)
         _state[key] = st
     return st
 
@@ -219,8 +234,7 @@ def _project_to_host(ct, phantom, specs):
         return None
     st = _get_state(ct, phantom)
     keep_L = config.cache_lengths and len(specs) == 1
-    if keep_L and st.L is not None and st.L_dtype == code and st.L.shape[0] == nv:
-        return None                                      # a second get_sino call: served from the stored lengths
+    have_L = config.cache_lengths and st.L is not None and st.L_dtype == code and st.L.shape[0] == nv   # a second get_sino call
     E = specs[0].E
     mu = phantom.mu_table(E)
     W = np.stack([spectral_weights(ct, sp) for sp in specs])
@@ -232,13 +246,16 @@ def _project_to_host(ct, phantom, specs):
     h_l = torch.empty(shape, dtype=torch.float64, pin_memory=True)
     dev = st.projector.device
     td = torch.float32 if code == 0 else torch.float64
-    L_full = torch.empty((nv, ct.N_rows, ct.N_channels, mu.shape[0]), dtype=td, device=dev) if keep_L else None
+    L_full = torch.empty((nv, ct.N_rows, ct.N_channels, mu.shape[0]), dtype=td, device=dev) if (keep_L and not have_L) else None
     side = torch.cuda.Stream(device=dev)
     with torch.cuda.device(dev):
         for a in range(0, nv, step):
             n = min(step, nv - a)
-            c, lg, _ = st.projector.project(mu, W, view_begin=v0 + a, view_count=n, dtype=code, want_log=True,
-                                            want_L=keep_L, L=None if L_full is None else L_full[a:a + n])
+            if have_L:                                   # detection alone, from the path lengths the first call stored
+                c, lg = poly_detect(st.L[a:a + n], mu, W, dtype=code, want_log=True)
+            else:
+                c, lg, _ = st.projector.project(mu, W, view_begin=v0 + a, view_count=n, dtype=code, want_log=True,
+                                                want_L=keep_L, L=None if L_full is None else L_full[a:a + n])
             done = torch.cuda.Event()
             done.record()
             with torch.cuda.stream(side):
@@ -249,7 +266,7 @@ def _project_to_host(ct, phantom, specs):
             c.record_stream(side)
             lg.record_stream(side)
         side.synchronize()
-    if keep_L:
+    if L_full is not None:
         st.L, st.L_dtype = L_full, code
     raw, log = h_c.numpy(), h_l.numpy()
     if ct.N_rows == 1:
