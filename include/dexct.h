@@ -75,12 +75,20 @@ int         dexct_device_count(void);
 
 /* ---- forward projection: replaces get_sino (main.py:120) ------------------------------------------------ */
 
-/* Bytes of device scratch needed by dexct_siddon_prepare for this scan + volume (angle tables and the two
- * minor-axis-contiguous "pair" layouts of the label volume).                        */
+/* Bytes of device scratch needed by dexct_siddon_prepare for this scan + volume:
+ *   - the angle tables (cos/sin of the view and channel angles, detector row heights; float64);
+ *   - two minor-axis-contiguous "pair" layouts of the label volume, one per possible major axis (2 B per voxel each,
+ *     one-voxel zero aprons): what the trace kernels and the K > 128 fallback walk;
+ *   - four "skip" layouts (major axis x sign of the minor slope, 2 B per voxel each): ordinary pairs or homogeneous
+ *     stretches of up to 127 columns -- what the production kernels walk;
+ *   - for volumes with more than one slice, two z-homogeneity radius volumes (1 B per voxel each) used to build them.
+ * About 14 B per voxel for a 3-D volume: 1 MiB for a 512 x 512 slice, 1.8 GiB for 512^3, 14 GiB for 1024^3.           */
 size_t dexct_siddon_workspace_bytes(const DexctScan *scan, const DexctVolume *vol);
 
-/* Fill the workspace: sin/cos tables (device double precision) and the re-laid-out label volume.  Must be
- * called again whenever labels, scan or vol change.  Cost: one pass over the volume.                        */
+/* Fill the workspace: angle tables (device double precision), pair layouts and skip layouts.  Must be called again
+ * whenever labels, scan or vol change.  Cost: a few passes over the volume (0.1 ms for a 512 x 512 slice, 10 ms for
+ * 512^3, 60 ms for 1024^3).  Refuses scans whose rays climb more than one slice per column (thin slices under a tall
+ * detector): the column routine assumes at most one z-plane crossing per column.                              */
 int dexct_siddon_prepare(const DexctScan *scan, const DexctVolume *vol, const uint8_t *labels,
                          void *workspace, void *stream);
 
