@@ -917,12 +917,21 @@ __global__ void __launch_bounds__(128) siddon_skip3_kernel(SiddonParams P, int v
 
     const long long n_blk = (n_rays + blockDim.x - 1) / blockDim.x;
     for (long long blk = blockIdx.x; blk < n_blk; blk += gridDim.x) {
-        const long long ray = blk * blockDim.x + tid;
-        if (ray >= n_rays) continue;
-        const int c = (int)(ray % P.scan.n_ch);
-        const long long line = ray / P.scan.n_ch;
-        const int r = (int)(line % P.scan.n_rows);
-        const int v = view_begin + (int)(line / P.scan.n_rows);
+        // Launch order: bands of `row_band` detector rows outermost, then views, then the rows of the band, then channels.
+        // The CTAs resident at any one time then work on a few rows of a dozen consecutive views -- a slab of a few dozen
+        // z planes of ONE layout, which stays in L2 from view to view -- instead of on all rows of one view, i.e. the whole
+        // volume (1024^3: 272 GB of DRAM reads per scan and an L2 hit rate of 39 % in view-major order, profiles/r02x).
+        const long long q_ray = blk * blockDim.x + tid;
+        if (q_ray >= n_rays) continue;
+        const int c = (int)(q_ray % P.scan.n_ch);
+        const long long q = q_ray / P.scan.n_ch;                           // position of the detector line in launch order
+        const long long per_band = (n_rays / P.scan.n_ch / P.scan.n_rows) * P.row_band;   // lines of a band: views x rows
+        const int band = (int)(q / per_band);
+        const long long rem = q - band * per_band;
+        const int v_rel = (int)(rem / P.row_band);
+        const int r = band * P.row_band + (int)(rem - (long long)v_rel * P.row_band);
+        const int v = view_begin + v_rel;
+        const long long ray = ((long long)v_rel * P.scan.n_rows + r) * P.scan.n_ch + c;     // where its results go
         for (int m = 0; m < KP; ++m) acc_s[m * blockDim.x + tid] = (R)0;
 
         RaySetup s;
@@ -1216,7 +1225,15 @@ static int launch_skip(const SiddonParams &P, int view_begin, long long n_rays, 
     if (per_sm < 1) per_sm = 1;
     const long long n_blk = (n_rays + block - 1) / block;
     const long long grid = std::min<long long>(n_blk, (long long)sm_count() * per_sm);     // resident CTAs stride over ray blocks
-    kern<<<(unsigned)grid, block, smem, st>>>(P, view_begin, n_rays, d);
+    SiddonParams Pl = P;
+    Pl.row_band = 1;
+    if (IS3D) {                                               // the largest divisor of the row count up to 8 (siddon_skip3_kernel)
+        const char *rb = getenv("DEXCT_ROW_BAND");            // tuning knob
+        const int want = rb && atoi(rb) >= 1 ? atoi(rb) : 8;
+        for (int b = 1; b <= want && b <= P.scan.n_rows; ++b)
+            if (P.scan.n_rows % b == 0) Pl.row_band = b;
+    }
+    kern<<<(unsigned)grid, block, smem, st>>>(Pl, view_begin, n_rays, d);
     DEXCT_CUDA_OK(cudaGetLastError());
     return DEXCT_OK;
 }

@@ -83,6 +83,7 @@ struct SiddonParams {
     int pitch_xm, pitch_ym;
     long long plane_xm, plane_ym;
     double inv_dx, inv_dy, inv_dz;    // 1/voxel size, rounded once on the host
+    int row_band;                     // 3-D production kernel: detector rows per band of its launch order (set per launch)
 };
 
 // Per-ray constants, computed in double with one rounding per operation (the CPU twin does the same).
