@@ -544,6 +544,35 @@ __global__ void gn_tc_table_kernel(const float *__restrict__ i0, const float *__
     x[2] = t1;
 }
 
+// Every pixel starts from a = (1e-6, 1e-6) (matdecomp.py:98), so the twelve energy sums of the FIRST Newton iteration are
+// the same for all pixels: they are computed once here (float64, one CTA) and the kernels take their first step from them
+// without evaluating a single exponential -- one iteration in n_iters of the work gone, same arithmetic otherwise.
+// out[0..5] = measurement 1 {nu, sum i0 mu1 att, sum i0 mu2 att, sum i0 mu1^2 att, sum i0 mu1 mu2 att, sum i0 mu2^2 att},
+// out[6..11] = measurement 2.
+__global__ void __launch_bounds__(256) gn_first_sums_kernel(const float *__restrict__ i0, const float *__restrict__ mus, int nE,
+                                                             float *__restrict__ out)
+{
+    __shared__ double part[12][256];
+    double acc[12];
+#pragma unroll
+    for (int q = 0; q < 12; ++q) acc[q] = 0.0;
+    for (int e = threadIdx.x; e < nE; e += blockDim.x) {
+        const double m1 = mus[e], m2 = mus[nE + e], s1 = i0[e], s2 = i0[nE + e];
+        const double att = exp(-1e-6 * (m1 + m2));
+        const double f[6] = {1.0, m1, m2, m1 * m1, m1 * m2, m2 * m2};
+#pragma unroll
+        for (int q = 0; q < 6; ++q) { acc[q] += s1 * f[q] * att; acc[6 + q] += s2 * f[q] * att; }
+    }
+#pragma unroll
+    for (int q = 0; q < 12; ++q) part[q][threadIdx.x] = acc[q];
+    __syncthreads();
+    if (threadIdx.x < 12) {
+        double t = 0.0;
+        for (int k = 0; k < 256; ++k) t += part[threadIdx.x][k];
+        out[threadIdx.x] = (float)t;
+    }
+}
+
 __device__ __forceinline__ uint32_t smem_u32(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
 __device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count)
 {
@@ -666,7 +695,7 @@ __global__ void __launch_bounds__(GT_THREADS, 4) gn_tc_kernel(const float *__res
     asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(gt_birth_ns));
 #endif
 
-    for (int i = tid; i < nks * 68; i += GT_THREADS) ((float4 *)bsm)[i] = ((const float4 *)btab)[i];
+    for (int i = tid; i < nks * 68 + 3; i += GT_THREADS) ((float4 *)bsm)[i] = ((const float4 *)btab)[i];     // + the first-iteration sums
     if (tid == 0) {
         for (int b = 0; b < GT_NBUF; ++b) { mbar_init(bar_full + 8 * b, 4); mbar_init(bar_free + 8 * b, 1); }
         mbar_init(bar_done, 1);
@@ -703,7 +732,7 @@ __global__ void __launch_bounds__(GT_THREADS, 4) gn_tc_kernel(const float *__res
         const uint32_t bsm_addr = smem_u32(bsm);
         uint32_t cnt = 0, tpar = 0;
         for (long long tile = blockIdx.x; tile < n_tiles; tile = next_tile_sm[tpar], tpar ^= 1) {
-            for (int it = 0; it < n_iters; ++it)
+            for (int it = 1; it < n_iters; ++it)              // (the first iteration needs no sums of its own, see below)
 #pragma unroll 1
                 for (int c = 0; c < n_chunks; ++c, ++cnt) {
                     const uint32_t b = cnt % GT_NBUF;
@@ -739,7 +768,8 @@ __global__ void __launch_bounds__(GT_THREADS, 4) gn_tc_kernel(const float *__res
         const float thr = mask_thresh > 0.f ? mask_thresh * decode_max<float>(scratch) : INFINITY;
         const uint32_t lane_base = tmem + ((uint32_t)(warp * 32) << 16);
         const uint32_t xsm_addr = smem_u32(bsm + (size_t)nks * 256);         // exponent pairs, four float4 (64 B) per k-step
-        const int rider_per_tile = n_iters > 0 ? n_iters : 1;
+        const float *first_sums = bsm + (size_t)nks * 272;                   // twelve sums of the first iteration
+        const int rider_per_tile = n_iters > 1 ? n_iters - 1 : 1;
         const int rider_nk = rider_per_tile * (int)((n_tiles + gridDim.x - 1) / gridDim.x);
         int rider_k = 0;
         const bool ride = rider.n != 0;
@@ -761,7 +791,14 @@ __global__ void __launch_bounds__(GT_THREADS, 4) gn_tc_kernel(const float *__res
             const float g1 = p < P ? g[p] : 1.f, g2 = p < P ? g[P + p] : 1.f;
             float a1 = 1e-6f, a2 = 1e-6f;                                     // matdecomp.py:98
             bool sane = true;
-            for (int it = 0; it < n_iters; ++it) {
+            if (n_iters > 0) {
+                // first iteration: a is the same for every pixel, and so are its energy sums (gn_first_sums_kernel)
+                float A0[12];
+#pragma unroll
+                for (int q = 0; q < 12; ++q) A0[q] = first_sums[q];
+                newton_update_fast(A0, g1, g2, a1, a2, sane);
+            }
+            for (int it = 1; it < n_iters; ++it) {
                 if (ride && rider_k < rider_nk) rider_slice(rider_k++);       // (a CTA may draw more tiles than its even share)
                 const f32x2 a1p = pack2(a1, a1), a2p = pack2(a2, a2);
 #pragma unroll 1
@@ -1106,7 +1143,7 @@ static int launch_gn_tc(const void *g, const void *i0, const void *mus, int nE, 
                         void *a_out, void *scratch, bool have_max, cudaStream_t st, const GnMirrors &mir, const GnRider &rider)
 {
     const int nks = (nE + GT_KS - 1) / GT_KS;
-    const size_t smem = (size_t)nks * (1024 + 64);          // B operand + exponent pairs
+    const size_t smem = (size_t)nks * (1024 + 64) + 48;     // B operand + exponent pairs + first-iteration sums
     DEXCT_CUDA_OK(cudaFuncSetAttribute(gn_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     // CTAs per SM: 512 columns of tensor memory / GT_COLS, and what fits the shared memory.  (The occupancy calculator
     // answers 1 for a kernel that allocates tensor memory -- profiles/r02c: a grid of 148 CTAs ran at 3x the time.)
@@ -1126,6 +1163,8 @@ static int launch_gn_tc(const void *g, const void *i0, const void *mus, int nE, 
         ConstSlot slot(SLOT_GN, st);                          // exclusive use of the staging image until the kernel has run
         if (!slot.ok()) return DEXCT_ECUDA;
         gn_tc_table_kernel<<<(nks * GT_KS + 127) / 128, 128, 0, st>>>((const float *)i0, (const float *)mus, nE, nks, (float *)slot.staging());
+        DEXCT_CUDA_OK(cudaGetLastError());
+        gn_first_sums_kernel<<<1, 256, 0, st>>>((const float *)i0, (const float *)mus, nE, (float *)slot.staging() + (size_t)nks * 272);
         DEXCT_CUDA_OK(cudaGetLastError());
         gn_tc_kernel<<<(unsigned)grid, GT_THREADS, smem, st>>>((const float *)g, (const float *)slot.staging(), nks, P, n_iters,
                                                               (float)mask_thresh, scratch, (float *)a_out, mir, rider, sw && atoi(sw));
