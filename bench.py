@@ -618,15 +618,34 @@ class ScanBench:
             # profiles/r02m_xu_rate.txt).  The FP32-FMA figure of the earlier rounds is kept beside it for continuity: it can
             # exceed 1 now, the FMAs are no longer on that pipe.
             ex2 = float(self.nE) * GN_ITERS * self.rays_total
+            # share of the 128-pixel tiles of this rank's shard that the kernel does not decompose because all their pixels are
+            # air (first measurement >= MASK_THRESH x its maximum: get_basismat_sinos zeroes them, matdecomp.py:195-196,204-205)
+            air_tiles = None
+            try:
+                torch = self.torch
+                g1 = self.counts[0].reshape(-1)
+                mx = g1.max()
+                if ws > 1:
+                    self.dist.all_reduce(mx, op=self.dist.ReduceOp.MAX)
+                pad = (-g1.numel()) % 128
+                air = g1 >= MASK_THRESH * mx
+                if pad:
+                    air = torch.cat([air, torch.ones(pad, dtype=torch.bool, device=air.device)])
+                air_tiles = float(air.view(-1, 128).all(dim=1).float().mean()) if MASK_THRESH > 0 else 0.0
+            except Exception:                                             # noqa: BLE001
+                pass
+            evaluated = (max(GN_ITERS - 1, 0) / GN_ITERS) * (1.0 - (air_tiles or 0.0))
             xu_peak = 15.9 * 148 * sm_mhz * 1e6 / 1e9 * ws                # Gex2/s
             xu_ach = ex2 / (t['gn'] * 1e-3) / 1e9
             roof_gn = {'bound': 'mufu', 'achieved': xu_ach, 'peak': xu_peak, 'unit': 'Gex2/s', 'frac': xu_ach / xu_peak,
                        'kernel': 'gn_tc_kernel', 'ex2_per_pixel': float(self.nE) * GN_ITERS, 'launch_ms': t['gn'], 'sm_mhz': sm_mhz,
-                       'ex2_evaluated_per_pixel': float(self.nE) * max(GN_ITERS - 1, 0),
-                       'frac_of_evaluated': xu_ach / xu_peak * max(GN_ITERS - 1, 0) / GN_ITERS,
-                       'note': 'achieved counts the exponentials of the algorithm (nE x iterations, what the reference evaluates); the '
-                               'kernel evaluates one iteration fewer -- the sums of the first iteration are the same for every pixel '
-                               'and are computed once -- which frac_of_evaluated accounts for',
+                       'air_tile_fraction': air_tiles, 'evaluated_share_of_algorithmic': evaluated,
+                       'frac_of_evaluated': xu_ach / xu_peak * evaluated,
+                       'note': 'achieved counts the exponentials of the algorithm (nE x iterations for every pixel: what the reference '
+                               'evaluates).  The kernel evaluates fewer for the same output: the sums of the first iteration are the '
+                               'same for every pixel and are computed once, and tiles of 128 pixels that are all air -- zeroed by the '
+                               'air mask whatever the iterations give -- are not iterated.  frac_of_evaluated = the MUFU work actually '
+                               'done over the peak',
                        'peak_source': '15.9 MUFU.EX2 per clock and SM (measured, profiles/r02m_xu_rate.txt) x 148 SMs x sm_mhz',
                        'fp32_fma_equivalent': {'achieved': gn_ach, 'peak': fma_peak, 'unit': 'TFLOP/s', 'frac': gn_ach / fma_peak,
                                                'flop_per_pixel': 28.0 * self.nE * GN_ITERS}}

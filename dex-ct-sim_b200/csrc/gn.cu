@@ -683,6 +683,7 @@ __global__ void __launch_bounds__(GT_THREADS, 4) gn_tc_kernel(const float *__res
     __shared__ __align__(8) unsigned long long bars[2 * GT_NBUF + 1];
     __shared__ uint32_t tmem_base_sm;
     __shared__ unsigned next_tile_sm[2];
+    __shared__ int tile_air_sm[4];                            // per compute warp: all its pixels of the current tile are air
     const int tid = threadIdx.x, lane = tid & 31;
     // the warp index as a value the compiler knows to be the same in all lanes: the role branches below are then uniform
     // branches and the code inside them may use the uniform datapath
@@ -732,7 +733,9 @@ __global__ void __launch_bounds__(GT_THREADS, 4) gn_tc_kernel(const float *__res
         const uint32_t bsm_addr = smem_u32(bsm);
         uint32_t cnt = 0, tpar = 0;
         for (long long tile = blockIdx.x; tile < n_tiles; tile = next_tile_sm[tpar], tpar ^= 1) {
-            for (int it = 1; it < n_iters; ++it)              // (the first iteration needs no sums of its own, see below)
+            asm volatile("bar.sync 2, %0;" ::"n"(GT_THREADS) : "memory");      // the compute warps have voted on the tile
+            const bool air_tile = (tile_air_sm[0] & tile_air_sm[1] & tile_air_sm[2] & tile_air_sm[3]) != 0;
+            for (int it = 1; it < n_iters && !air_tile; ++it)  // (the first iteration needs no sums of its own, see below)
 #pragma unroll 1
                 for (int c = 0; c < n_chunks; ++c, ++cnt) {
                     const uint32_t b = cnt % GT_NBUF;
@@ -791,14 +794,22 @@ __global__ void __launch_bounds__(GT_THREADS, 4) gn_tc_kernel(const float *__res
             const float g1 = p < P ? g[p] : 1.f, g2 = p < P ? g[P + p] : 1.f;
             float a1 = 1e-6f, a2 = 1e-6f;                                     // matdecomp.py:98
             bool sane = true;
-            if (n_iters > 0) {
+            // A tile whose 128 pixels are all air is not decomposed at all: get_basismat_sinos zeroes those pixels whatever the
+            // iterations made of them (matdecomp.py:195-196,204-205), and in a CT sinogram they come in long runs at both ends
+            // of every detector line.  (Pixels past the end of the sinogram count as air.)
+            const bool air_px = p < P ? g1 >= thr : true;
+            const bool air_warp = __all_sync(0xffffffffu, air_px);
+            if (lane == 0) tile_air_sm[warp] = air_warp;
+            asm volatile("bar.sync 2, %0;" ::"n"(GT_THREADS) : "memory");
+            const bool air_tile = (tile_air_sm[0] & tile_air_sm[1] & tile_air_sm[2] & tile_air_sm[3]) != 0;
+            if (n_iters > 0 && !air_tile) {
                 // first iteration: a is the same for every pixel, and so are its energy sums (gn_first_sums_kernel)
                 float A0[12];
 #pragma unroll
                 for (int q = 0; q < 12; ++q) A0[q] = first_sums[q];
                 newton_update_fast(A0, g1, g2, a1, a2, sane);
             }
-            for (int it = 1; it < n_iters; ++it) {
+            for (int it = 1; it < n_iters && !air_tile; ++it) {
                 if (ride && rider_k < rider_nk) rider_slice(rider_k++);       // (a CTA may draw more tiles than its even share)
                 const f32x2 a1p = pack2(a1, a1), a2p = pack2(a2, a2);
 #pragma unroll 1
