@@ -64,6 +64,32 @@ def main():
                             if pos[q] < len(lanes[q]):
                                 pos[q] += 1
         print(f'    warp cost model: today {costA:.3e} instructions, two-phase rounds {costB:.3e} ({costA / costB:.2f}x)')
+        # (C) lockstep: all lanes of a warp always stand at the same column and advance by the SHORTEST run any of them has
+        # there (a stretch may be cut short; an ordinary column anywhere makes it a one-column step) -- loads coalesce, no
+        # lane idles, but a warp takes more steps
+        stepsA = stepsC = 0
+        for r in rows:
+            ids = (v * ct.N_rows + r) * ct.N_channels + np.arange(ct.N_channels, dtype=np.int64)
+            recs, _ = pj.walk_trace(ids, 8, max_steps=2048, dtype='f32')
+            for w in range(0, len(recs) - 31, 32):
+                group = [rec for rec in recs[w:w + 32] if rec['n_steps'] and rec['xmajor'] == recs[w]['xmajor']]
+                if not group:
+                    continue
+                stepsA += max(rec['n_steps'] for rec in group)
+                lo_c = min(int(rec['col'][0]) for rec in group)
+                hi_c = max(int(rec['col'][-1]) + max(int(rec['run'][-1]), 1) for rec in group)
+                # remaining run of every lane at every column (0 outside its range, 1 on ordinary columns)
+                rem = np.zeros((len(group), hi_c - lo_c), dtype=np.int32)
+                for q, rec in enumerate(group):
+                    for c0, rn in zip(rec['col'], rec['run']):
+                        n = max(int(rn), 1)
+                        rem[q, c0 - lo_c:c0 - lo_c + n] = np.arange(n, 0, -1) if rn > 0 else 1
+                c = 0
+                while c < hi_c - lo_c:
+                    live = rem[:, c][rem[:, c] > 0]
+                    c += int(live.min()) if live.size else 1
+                    stepsC += 1
+        print(f'    lockstep model: {stepsC} warp steps against {stepsA} today ({stepsC / max(stepsA, 1):.2f}x)')
         ns = np.concatenate(n_steps)
         runs = np.concatenate(runs) if runs else np.zeros(0)
         hit = ns > 0
