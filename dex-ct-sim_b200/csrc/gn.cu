@@ -12,6 +12,7 @@
 // Every thread of a warp reads the same row (broadcast LDS.128), so the kernel is bound by the FP32 FMA pipe:
 // 14 FMA + 1 MUFU.EX2 per pixel, energy and iteration.  PX pixels per thread share each row load.
 #include "common.cuh"
+#include <algorithm>
 #include <stdlib.h>
 
 namespace dexct {
@@ -544,6 +545,54 @@ __global__ void gn_tc_table_kernel(const float *__restrict__ i0, const float *__
     x[2] = t1;
 }
 
+// Air pixels (first measurement >= mask_thresh x its maximum) are zeroed by get_basismat_sinos whatever the iterations made of
+// them (matdecomp.py:195-196,204-205): they are zeroed HERE, and only the indices of the other pixels are handed to the
+// decomposition kernel (a quarter of a CT sinogram is air, in runs at both ends of every detector line).  The list keeps the
+// pixels of a CTA's 1024 in order (coalescing survives); the order of the CTAs' pieces is whatever the atomics make it.
+// scratch: [0] max key, [2] flagged count, [3] tile counter, [4 .. 4 + P) flagged list, [4 + P] number of listed pixels,
+// [8 + P .. 8 + 2 P) the list.
+__global__ void __launch_bounds__(256) gn_compact_kernel(const float *__restrict__ g1, long long P, float mask_thresh, void *scratch,
+                                                         float *__restrict__ a_out, const GnMirrors mir)
+{
+    __shared__ unsigned warp_tot[8], base_sm;
+    const float thr = mask_thresh * decode_max<float>(scratch);
+    unsigned *count = (unsigned *)scratch + 4 + P, *list = (unsigned *)scratch + 8 + P;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    for (long long blk0 = (long long)blockIdx.x * 1024; blk0 < P; blk0 += (long long)gridDim.x * 1024) {
+        unsigned keep_bits[4], n_mine = 0;
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+            const long long p = blk0 + u * 256 + threadIdx.x;
+            const bool keep = p < P && !(g1[p] >= thr);
+            if (p < P && !keep) {
+                const float2 z = make_float2(0.f, 0.f);
+                ((float2 *)a_out)[p] = z;
+                for (int d = 0; d < mir.n; ++d) ((float2 *)mir.p[d])[p] = z;
+            }
+            keep_bits[u] = __ballot_sync(0xffffffffu, keep);
+            n_mine += __popc(keep_bits[u]);                  // (same in all lanes: the warp's count for this quarter)
+        }
+        if (lane == 0) warp_tot[warp] = n_mine;
+        __syncthreads();
+        if (threadIdx.x == 0) {
+            unsigned t = 0;
+            for (int w = 0; w < 8; ++w) t += warp_tot[w];
+            base_sm = atomicAdd(count, t);
+        }
+        __syncthreads();
+        // the CTA's piece is laid out [warp][quarter][lane]: runs of up to 32 consecutive pixels
+        unsigned ofs = base_sm;
+        for (int w = 0; w < warp; ++w) ofs += warp_tot[w];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+            const long long p = blk0 + u * 256 + threadIdx.x;
+            if ((keep_bits[u] >> lane) & 1u) list[ofs + __popc(keep_bits[u] & ((1u << lane) - 1u))] = (unsigned)p;
+            ofs += __popc(keep_bits[u]);
+        }
+        __syncthreads();
+    }
+}
+
 // Every pixel starts from a = (1e-6, 1e-6) (matdecomp.py:98), so the twelve energy sums of the FIRST Newton iteration are
 // the same for all pixels: they are computed once here (float64, one CTA) and the kernels take their first step from them
 // without evaluating a single exponential -- one iteration in n_iters of the work gone, same arithmetic otherwise.
@@ -676,7 +725,7 @@ __device__ unsigned long long gt_cta[4096 * 3];               // per CTA: global
 #endif
 __global__ void __launch_bounds__(GT_THREADS, 4) gn_tc_kernel(const float *__restrict__ g, const float *__restrict__ btab, int nks, long long P,
                                                            int n_iters, float mask_thresh, void *scratch, float *__restrict__ a_out,
-                                                           const GnMirrors mir, const GnRider rider, int lbo_sbo_swapped)
+                                                           const GnMirrors mir, const GnRider rider, int lbo_sbo_swapped, int compacted)
 {
     extern __shared__ __align__(128) unsigned char smem_raw[];
     float *bsm = (float *)smem_raw;                           // [nks][hi 128 floats, lo 128 floats], then [nks][4] exponent float4s
@@ -723,7 +772,10 @@ __global__ void __launch_bounds__(GT_THREADS, 4) gn_tc_kernel(const float *__res
     tc_fence_after();
     const uint32_t tmem = tmem_base_sm;
 
-    const long long n_tiles = (P + 127) / 128;
+    // compacted: the pixels to decompose are listed in the scratch block (gn_compact_kernel); the others are zeroed already
+    const unsigned *px_list = (const unsigned *)scratch + 8 + P;
+    const long long n_px = compacted ? (long long)((const unsigned *)scratch)[4 + P] : P;
+    const long long n_tiles = (n_px + 127) / 128;
     const int n_chunks = (nks + GT_CHUNK_KS - 1) / GT_CHUNK_KS;
 
     if (warp == 4) {
@@ -790,7 +842,8 @@ __global__ void __launch_bounds__(GT_THREADS, 4) gn_tc_kernel(const float *__res
         uint32_t cnt = 0, done_cnt = 0, tpar = 0;
         for (long long tile = blockIdx.x; tile < n_tiles; tile = next_tile_sm[tpar], tpar ^= 1) {
             if (tid == 0) next_tile_sm[tpar] = gridDim.x + atomicAdd(tile_counter, 1u);
-            const long long p = tile * 128 + tid;
+            const long long q = tile * 128 + tid;
+            const long long p = q < n_px ? (compacted ? (long long)px_list[q] : q) : P;      // P: no pixel
             const float g1 = p < P ? g[p] : 1.f, g2 = p < P ? g[P + p] : 1.f;
             float a1 = 1e-6f, a2 = 1e-6f;                                     // matdecomp.py:98
             bool sane = true;
@@ -1177,8 +1230,18 @@ static int launch_gn_tc(const void *g, const void *i0, const void *mus, int nE, 
         DEXCT_CUDA_OK(cudaGetLastError());
         gn_first_sums_kernel<<<1, 256, 0, st>>>((const float *)i0, (const float *)mus, nE, (float *)slot.staging() + (size_t)nks * 272);
         DEXCT_CUDA_OK(cudaGetLastError());
+        // with an air mask: zero the air pixels now and decompose only the others (gn_compact_kernel)
+        const char *cp = getenv("DEXCT_GN_COMPACT");             // 0: decompose every tile that holds a non-air pixel, as before
+        const int compacted = mask_thresh > 0 && !(cp && atoi(cp) == 0);
+        if (compacted) {
+            DEXCT_CUDA_OK(cudaMemsetAsync((unsigned *)scratch + 4 + P, 0, sizeof(unsigned), st));
+            const long long nb = (P + 1023) / 1024;
+            gn_compact_kernel<<<(unsigned)std::min<long long>(nb, (long long)sm_count() * 8), 256, 0, st>>>((const float *)g, P, (float)mask_thresh,
+                                                                                                         scratch, (float *)a_out, mir);
+            DEXCT_CUDA_OK(cudaGetLastError());
+        }
         gn_tc_kernel<<<(unsigned)grid, GT_THREADS, smem, st>>>((const float *)g, (const float *)slot.staging(), nks, P, n_iters,
-                                                              (float)mask_thresh, scratch, (float *)a_out, mir, rider, sw && atoi(sw));
+                                                              (float)mask_thresh, scratch, (float *)a_out, mir, rider, sw && atoi(sw), compacted);
         DEXCT_CUDA_OK(cudaGetLastError());
     }
     const size_t fsm = sizeof(double) * 14 * (size_t)nE;
@@ -1210,7 +1273,7 @@ extern "C" int dexct_debug_gn_tc_prof(unsigned long long *out16, int reset)
 extern "C" size_t dexct_gn_scratch_bytes(int64_t P, int32_t dtype)
 {
     if (P < 0) return 0;
-    return dtype == DEXCT_F32 ? 16 + sizeof(unsigned) * (size_t)P : 16;
+    return dtype == DEXCT_F32 ? 32 + 2 * sizeof(unsigned) * (size_t)P : 16;    // keys + counters, flagged list, list of non-air pixels
 }
 
 extern "C" int dexct_gn_air_max(const void *g1, int64_t P, void *scratch, int32_t dtype, void *stream)

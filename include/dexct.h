@@ -155,7 +155,9 @@ int dexct_siddon_walk_trace(const DexctScan *scan, const DexctVolume *vol, const
  * scratch = dexct_gn_scratch_bytes(P, dtype) bytes of device memory: the air maximum and, in single precision, the list
  * of pixels whose iterates left the float range (photon-starved or metal-crossing rays: the reference's exponent clip,
  * matdecomp.py:116, is what keeps them finite in float64) -- those are redone in float64 inside the same call, so the
- * result is finite wherever the reference's is.  May be NULL only for DEXCT_F64 with mask_thresh <= 0.
+ * result is finite wherever the reference's is -- and the list of the pixels that are not air (with a mask the air pixels are
+ * zeroed up front and only the others are decomposed).  32 + 8 P bytes in single precision, 16 in double.  May be NULL only
+ * for DEXCT_F64 with mask_thresh <= 0.
  * scratch_has_max != 0: scratch already holds the maximum as written by dexct_gn_air_max (pixel-sharded runs reduce it
  * over ranks first); 0: it is computed here from g[0][0..P).                                                     */
 size_t dexct_gn_scratch_bytes(int64_t P, int32_t dtype);
