@@ -305,3 +305,37 @@ def test_general_form_per_bin_spectra_and_other_material_counts(n_meas, n_mats):
     with pytest.raises(N.DexctError, match='1 to 4'):
         from dexct.ops import gn_decompose_general
         gn_decompose_general(np.ones((5, 1, 4)), np.ones((5, 8)), np.ones((2, 8)), 1, dtype=F64)
+
+
+@pytest.mark.parametrize('P', [1, 127, 128, 129, 1000, 5000, 70001])
+def test_air_pixels_left_out_of_the_list_equals_the_full_decomposition(P, f32_kernel):
+    """With an air mask the tensor-core kernel iterates only a LIST of the non-air pixels (gn_compact_kernel zeroes the others
+    up front).  Same results, bit for bit, as decomposing every tile and zeroing afterwards (DEXCT_GN_COMPACT=0) -- including
+    sinograms that are all air, have no air, or end in the middle of a tile."""
+    g, i0, mus, _ = S.gn_problem(71, 1000)
+    gg = np.ascontiguousarray(g.reshape(2, -1)[:, :P]).copy()
+    r = np.random.default_rng(P)
+    air = r.random(P) < 0.3
+    air[: P // 7] = True                                      # a run of air at the start, like the end of a detector line
+    gg[0, air] = gg[0].max() * 1.2
+    gg[1, air] = gg[1].max()
+    for mask in (0.8, 0.0):
+        outs = {}
+        for flag in ('1', '0'):
+            os.environ['DEXCT_GN_COMPACT'] = flag
+            try:
+                outs[flag] = gn_decompose(gg, i0, mus, 7, mask_thresh=mask, dtype=F32).cpu().numpy()
+            finally:
+                os.environ.pop('DEXCT_GN_COMPACT', None)
+        assert np.array_equal(outs['1'], outs['0'])
+        if mask > 0:
+            masked = gg[0].astype(np.float32) >= np.float32(mask) * gg[0].astype(np.float32).max()     # matdecomp.py:196
+            assert (outs['1'][masked] == 0).all() and (outs['1'][~masked] != 0).all()
+            assert masked[air].all()
+    # all air
+    os.environ['DEXCT_GN_COMPACT'] = '1'
+    try:
+        z = gn_decompose(np.full((2, P), 5.0), i0, mus, 7, mask_thresh=0.5, dtype=F32).cpu().numpy()
+    finally:
+        os.environ.pop('DEXCT_GN_COMPACT', None)
+    assert (z == 0).all()
