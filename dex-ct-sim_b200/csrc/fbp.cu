@@ -10,7 +10,9 @@
 // fc = ramp * Nyquist ("ramp_filter_percent_Nyquist", input/params.txt:35), in closed form:
 //   h(t) = (2 fc^2 / pi) [ s(pi/4 + pi fc t) + s(pi/4 - pi fc t) ],   s(u) = sin^2(u) / u   (ramp = 1: Shepp-Logan)
 // Multi-row sinograms are reconstructed row by row (one fan-beam slice per detector row).
+#include <algorithm>
 #include "common.cuh"
+#include "tc05.cuh"
 
 namespace dexct {
 
@@ -519,6 +521,186 @@ __global__ void __launch_bounds__(256) fbp_backproject_warprows_kernel(const R *
     }
 }
 
+// ---------------------------------------------------------------------------------------------------------------------
+// Filter on the tensor cores (single precision, row-fastest output, full-turn scans).  The convolution of every detector
+// line with the 2 n_ch - 1 taps is a product with a Toeplitz matrix: Q[line][c] = dgamma sum_c' X'[line][c'] g[c - c'] --
+// the one genuine contraction of the reconstruction (n_ch^2 FMAs per line, 72 % of the FMA pipe in fbp_filter8_kernel).
+// Here it runs as tcgen05.mma kind::tf32 with the "3xTF32" split of gn_tc_kernel (gn.cu):
+//   * a CTA (one per SM, 512 columns of tensor memory) owns a slab of 256 output channels [n0, n0 + 256) and walks over
+//     tiles of 128 detector lines (thread t of the four compute warps <-> line t <-> lane t of tensor memory);
+//   * B needs no work per step: for input channels [k0, k0 + 8) it is the 256 x 8 window B[n][k] = g[n0 + n - k0 - k] of the
+//     taps, and the windows of successive k0 are the SAME strip of 8-column rows shifted by 8 rows.  The strip
+//     S[r][k] = g[n0 + r - (Kp - 8) - k], r = 0 .. 255 + Kp - 8, is built once per CTA in shared memory in the K-major
+//     no-swizzle core-matrix layout (8 rows x 16 bytes; split into TF32 heads and tails: 2 x 64 KiB for 1800 channels), and
+//     the matrix descriptor of a step simply starts (Kp - 8 - k0) / 8 row groups into it;
+//   * A: every compute warp stages 32 lines x 32 input channels through shared memory (coalesced loads, one line per thread
+//     out), applies the pre-weight SID cos(gamma), splits heads and tails and stores them into tensor memory
+//     (tcgen05.st.x16 per 8 channels), double buffered in chunks of four k-steps;
+//   * the MMA warp issues per k-step  D += hi x Bhi,  D += lo x Bhi,  D += hi x Blo  (M128 N256 K8, 128 cycles each: the
+//     tensor pipe is the bound here -- 3 x 128 cycles per 8 channels, 128 lines and 256 outputs);
+//   * after the last k-step the threads read their line of D (128 lanes x 256 columns) back and write it row-fastest.
+constexpr int FT_N = 256;                    // output channels per CTA slab = accumulator columns
+constexpr int FT_CKS = 4;                    // k-steps (of 8 input channels) per A chunk
+constexpr int FT_CH = FT_CKS * 8;            // input channels per chunk
+constexpr int FT_ACOL = FT_N;                // first A column in tensor memory
+constexpr int FT_THREADS = 160;
+constexpr int FT_LSTRIDE = 36;               // floats per staged line (32 + 4: conflict-free LDS.128 by line)
+constexpr uint32_t FT_IDESC = (1u << 4) | (2u << 7) | (2u << 10) | ((uint32_t)(FT_N >> 3) << 17) | ((128u >> 4) << 24);
+
+__global__ void __launch_bounds__(FT_THREADS, 1) fbp_filter_tc_kernel(const float *__restrict__ sino, long long n_lines, int n_ch,
+                                                                       double gamma0, double dgamma, double sid,
+                                                                       const float *__restrict__ taps, float *__restrict__ q,
+                                                                       int n_rows, int row_pitch, int n_slabs)
+{
+    extern __shared__ __align__(128) unsigned char smem_raw[];
+    const int Kp = (n_ch + 7) & ~7;
+    const int R = FT_N + Kp - 8;                              // rows of the tap strip
+    float *s_hi = (float *)smem_raw;                          // [R / 8][2 K halves][8 rows][4]
+    float *s_lo = s_hi + (size_t)R * 8;
+    float *wgt = s_lo + (size_t)R * 8;                        // [Kp] pre-weights SID cos(gamma), zero past n_ch
+    float *stage = wgt + Kp;                                  // [4 warps][32 lines][FT_LSTRIDE]
+    __shared__ __align__(8) unsigned long long bars[5];
+    __shared__ uint32_t tmem_base_sm;
+    const int tid = threadIdx.x, lane = tid & 31;
+    const int warp = __shfl_sync(0xffffffffu, tid >> 5, 0);
+    const uint32_t bar_full = smem_u32(&bars[0]), bar_free = smem_u32(&bars[2]), bar_done = smem_u32(&bars[4]);
+
+    const int slab = blockIdx.x % n_slabs, group = blockIdx.x / n_slabs, n_groups = gridDim.x / n_slabs;
+    const int n0 = slab * FT_N;
+    // the tap strip of this slab, heads and tails
+    for (int e = tid; e < R * 8; e += FT_THREADS) {
+        const int r = e >> 3, k = e & 7;
+        const int n = n0 + r - (Kp - 8) - k;                  // tap index c - c'
+        const float g = (n > -n_ch && n < n_ch) ? taps[n + (n_ch - 1)] : 0.f;
+        const float hi = __uint_as_float((__float_as_uint(g) + 0x1000u) & 0xffffe000u);
+        const int at = ((r >> 3) * 2 + (k >> 2)) * 32 + (r & 7) * 4 + (k & 3);
+        s_hi[at] = hi;
+        s_lo[at] = g - hi;
+    }
+    for (int c = tid; c < Kp; c += FT_THREADS) wgt[c] = c < n_ch ? (float)(sid * cos(gamma0 + (double)c * dgamma)) : 0.f;
+    if (tid == 0) {
+        for (int b = 0; b < 2; ++b) { mbar_init(bar_full + 8 * b, 4); mbar_init(bar_free + 8 * b, 1); }
+        mbar_init(bar_done, 1);
+        asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    }
+    if (warp == 4) {
+        asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], 512;" ::"r"(smem_u32(&tmem_base_sm)) : "memory");
+        asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+    }
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+    tc_fence_before();
+    __syncthreads();
+    tc_fence_after();
+    const uint32_t tmem = tmem_base_sm;
+    const long long n_tiles = (n_lines + 127) / 128;
+    const int n_ks = Kp / 8, n_chunks = (n_ks + FT_CKS - 1) / FT_CKS;
+
+    if (warp == 4) {
+        // descriptors: K-major, no swizzle, core matrices of 8 rows x 16 B; next K half 128 B on, next row group 256 B on
+        const uint64_t desc0 = ((uint64_t)(128 >> 4) << 16) | ((uint64_t)(256 >> 4) << 32) | (1ull << 46);
+        const uint32_t hi_addr = smem_u32(s_hi), lo_addr = smem_u32(s_lo);
+        uint32_t cnt = 0;
+        for (long long tile = group; tile < n_tiles; tile += n_groups)
+#pragma unroll 1
+            for (int c = 0; c < n_chunks; ++c, ++cnt) {
+                const uint32_t b = cnt & 1;
+                mbar_wait(bar_full + 8 * b, (cnt >> 1) & 1);
+                tc_fence_after();
+                const uint32_t a_buf = tmem + FT_ACOL + b * (FT_CKS * 16);
+#pragma unroll
+                for (int s = 0; s < FT_CKS; ++s) {
+                    const int ks = c * FT_CKS + s;
+                    if (ks < n_ks) {
+                        const uint32_t row_ofs = (uint32_t)((Kp - 8 - 8 * ks) >> 3) * 256;        // bytes into the strip
+                        const uint64_t dhi = desc0 | (uint64_t)(((hi_addr + row_ofs) & 0x3ffff) >> 4);
+                        const uint64_t dlo = desc0 | (uint64_t)(((lo_addr + row_ofs) & 0x3ffff) >> 4);
+                        tc_mma_tf32(tmem, a_buf + s * 16, dhi, FT_IDESC, ks > 0);
+                        tc_mma_tf32(tmem, a_buf + s * 16 + 8, dhi, FT_IDESC, 1);
+                        tc_mma_tf32(tmem, a_buf + s * 16, dlo, FT_IDESC, 1);
+                    }
+                }
+                tc_commit(bar_free + 8 * b);
+                if (c == n_chunks - 1) tc_commit(bar_done);
+            }
+        __syncwarp();
+    } else {
+        float *my_stage = stage + warp * 32 * FT_LSTRIDE;
+        const uint32_t lane_base = tmem + ((uint32_t)(warp * 32) << 16);
+        const long long plane = row_pitch;                   // elements between channel planes of the row-fastest layout
+        uint32_t cnt = 0, done_cnt = 0;
+        for (long long tile = group; tile < n_tiles; tile += n_groups) {
+            const long long line0 = tile * 128 + warp * 32;   // first line of this warp
+            const long long my_line = line0 + lane;
+            // 32 lines x 32 channels per chunk: lane = channel on the way in (coalesced), lane = line on the way out; the
+            // loads of the NEXT chunk are in flight while this one is split and stored
+            float in[32];
+            auto fetch = [&](int k0) {
+#pragma unroll
+                for (int l = 0; l < 32; ++l) {
+                    const long long ln = line0 + l;
+                    in[l] = (ln < n_lines && k0 + lane < n_ch) ? __ldg(sino + ln * n_ch + k0 + lane) : 0.f;
+                }
+            };
+            fetch(0);
+#pragma unroll 1
+            for (int c = 0; c < n_chunks; ++c, ++cnt) {
+                const uint32_t b = cnt & 1;
+                const int k0 = c * FT_CH;
+                __syncwarp();
+#pragma unroll
+                for (int l = 0; l < 32; ++l) my_stage[l * FT_LSTRIDE + lane] = in[l];
+                __syncwarp();
+                if (c + 1 < n_chunks) fetch(k0 + FT_CH);
+                mbar_wait(bar_free + 8 * b, ((cnt >> 1) & 1) ^ 1);
+                tc_fence_after();
+#pragma unroll
+                for (int s = 0; s < FT_CKS; ++s) {
+                    if (c * FT_CKS + s < n_ks) {
+                        const float4 x0 = *(const float4 *)(my_stage + lane * FT_LSTRIDE + 8 * s);
+                        const float4 x1 = *(const float4 *)(my_stage + lane * FT_LSTRIDE + 8 * s + 4);
+                        const float4 w0 = *(const float4 *)(wgt + k0 + 8 * s), w1 = *(const float4 *)(wgt + k0 + 8 * s + 4);
+                        const float v[8] = {x0.x * w0.x, x0.y * w0.y, x0.z * w0.z, x0.w * w0.w, x1.x * w1.x, x1.y * w1.y, x1.z * w1.z, x1.w * w1.w};
+                        uint32_t a[16];
+#pragma unroll
+                        for (int j = 0; j < 8; ++j) {
+                            a[j] = __float_as_uint(v[j]) & 0xffffe000u;
+                            a[8 + j] = __float_as_uint(v[j] - __uint_as_float(a[j]));
+                        }
+                        tmem_st16(lane_base + FT_ACOL + b * (FT_CKS * 16) + s * 16, a);
+                    }
+                }
+                asm volatile("tcgen05.wait::st.sync.aligned;" ::: "memory");
+                tc_fence_before();
+                __syncwarp();
+                if (lane == 0) mbar_arrive(bar_full + 8 * b);
+            }
+            // the filtered line of this thread: 256 columns of its lane, written row-fastest
+            mbar_wait(bar_done, done_cnt++ & 1);
+            tc_fence_after();
+            const bool live = my_line < n_lines;
+            const long long view = live ? my_line / n_rows : 0;
+            const int row = live ? (int)(my_line - view * n_rows) : 0;
+            float *dst = q + view * (long long)(n_ch + 2) * plane + row;
+#pragma unroll 1
+            for (int cb = 0; cb < FT_N; cb += 32) {
+                float d[32];
+                tmem_ld32(lane_base + cb, d);
+                if (live) {
+#pragma unroll
+                    for (int j = 0; j < 32; ++j) {
+                        const int ch = n0 + cb + j;
+                        if (ch < n_ch) dst[(long long)(1 + ch) * plane] = d[j] * (float)dgamma;
+                    }
+                }
+            }
+            tc_fence_before();
+        }
+    }
+    tc_fence_before();
+    __syncthreads();
+    if (warp == 4) asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, 512;" ::"r"(tmem) : "memory");
+}
+
 template <typename R>
 __global__ void fbp_hu_kernel(const R *__restrict__ image, long long n, R mu_water, R *__restrict__ hu)
 {
@@ -571,7 +753,21 @@ static int fbp_run(const DexctScan &s, const void *sino, int view_begin, int vie
         const size_t smem8 = sizeof(R) * ((size_t)FBP_FL * lstride + 2 * n_chp + 8);
         const char *f_env = getenv("DEXCT_FBP_FILTER");       // tuning knob: 1 forces the one-line kernel
         const long long n_lines = (long long)view_count * s.n_rows;
-        if (smem8 <= 200 * 1024 && !(f_env && atoi(f_env) == 1)) {
+        // single precision, row-fastest output, full turn, at least one slab of channels: the tensor-core filter
+        const char *tc_env = getenv("DEXCT_FBP_TC");          // 0: the FP32-pipe filter kernels
+        const int Kp = (s.n_ch + 7) & ~7;
+        const size_t smem_tc = sizeof(float) * ((size_t)(FT_N + Kp - 8) * 16 + Kp + 4 * 32 * FT_LSTRIDE);
+        if (sizeof(R) == 4 && row_pitch && pk.delta < 0 && s.n_ch >= 64 && smem_tc <= 220 * 1024 && !(tc_env && atoi(tc_env) == 0) &&
+            !(f_env && atoi(f_env) == 1)) {
+            const int n_slabs = (s.n_ch + FT_N - 1) / FT_N;
+            const long long n_tiles = (n_lines + 127) / 128;
+            int groups = (int)std::min<long long>(n_tiles, std::max(1, sm_count() / n_slabs));
+            // planes 0 and n_ch + 1 (the zero taper) and the rows no line fills
+            DEXCT_CUDA_OK(cudaMemsetAsync(q, 0, sizeof(R) * (size_t)view_count * (s.n_ch + 2) * L.row_pitch, st));
+            DEXCT_CUDA_OK(cudaFuncSetAttribute(fbp_filter_tc_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_tc));
+            fbp_filter_tc_kernel<<<(unsigned)(groups * n_slabs), FT_THREADS, smem_tc, st>>>(
+                (const float *)sino, n_lines, s.n_ch, s.gamma0, s.dgamma, s.sid, (const float *)taps, (float *)q, s.n_rows, row_pitch, n_slabs);
+        } else if (smem8 <= 200 * 1024 && !(f_env && atoi(f_env) == 1)) {
             if (smem8 > 48 * 1024)
                 DEXCT_CUDA_OK(cudaFuncSetAttribute(fbp_filter8_kernel<R>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem8));
             fbp_filter8_kernel<R><<<(unsigned)((n_lines + FBP_FL - 1) / FBP_FL), 256, smem8, st>>>(
