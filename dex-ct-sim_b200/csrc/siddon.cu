@@ -664,12 +664,22 @@ struct NoStepSink {
     __device__ __forceinline__ void operator()(int, int, int, const int *, const int *, const int *, const R *) const {}
 };
 
-template <typename R, typename SINK>
+// One 16-bit skip word, sign-extended, through the read-only path; the address is one IMAD.WIDE from a 32-bit index.
+__device__ __forceinline__ int skip_word(const uint16_t *__restrict__ W, int o)
+{
+    int w;
+    asm("{ .reg .u64 p; .reg .s16 h; mad.wide.s32 p, %2, 2, %1; ld.global.nc.s16 h, [p]; cvt.s32.s16 %0, h; }"
+        : "=r"(w) : "l"(W), "r"(o));
+    return w;
+}
+
+template <typename R, int STRIDE, typename SINK>
 __device__ __forceinline__ void walk_skip(const uint16_t *__restrict__ W, int pitch, int i0, int i1, int i_c, R am, R c0,
                                           R ua, R ub, R inv_am, R *acc, int stride, SINK &sink)
 {
     typedef Rn<R> A;
     typedef FastInt<R> F;
+    const int st = STRIDE > 0 ? STRIDE : stride;                          // compile-time accumulator stride when known
     const R c0m1 = A::sub(c0, (R)1);
     R fi = A::sub(F::real(i0 - i_c + (1 << 20)), (R)(1 << 20));          // column coordinate of column i, as a real
     const R fend = A::sub(F::real(i1 - i_c + (1 << 20)), (R)(1 << 20));
@@ -680,7 +690,7 @@ __device__ __forceinline__ void walk_skip(const uint16_t *__restrict__ W, int pi
         const R qa = A::fma(am, a, c0);
         const R qbm1 = A::fma(am, b1, c0m1);                              // q(b1) - 1
         const R t = F::bias(qa);
-        const int w = (int)(short)W[ofs + F::to_int(t)];
+        const int w = skip_word(W, ofs + F::to_int(t));
         const bool hom = w < 0;
         const int f0 = w & 0x7f, f1 = (w >> 8) & 0x7f;
         const int step = hom ? f1 : 1;
@@ -690,7 +700,7 @@ __device__ __forceinline__ void walk_skip(const uint16_t *__restrict__ W, int pi
         R whi = A::max(A::mul(A::sub(qbm1, F::unbias(t)), inv_am), (R)0);
         whi = hom ? (R)0 : whi;
         const R wlo = A::sub(wtot, whi);
-        R *p0 = acc + f0 * stride, *p1 = acc + (hom ? f0 : f1) * stride;
+        R *p0 = acc + f0 * st, *p1 = acc + (hom ? f0 : f1) * st;
         const R v0 = *p0, v1 = *p1;
         *p1 = A::add(v1, whi);                                            // p1 == p0 only when whi == 0: order matters
         *p0 = A::add(v0, wlo);
@@ -743,8 +753,11 @@ __global__ void __launch_bounds__(128) siddon_skip_kernel(SiddonParams P, int vi
             const uint16_t *W = P.skip[(s.xmajor ? 0 : 2) + (mpos ? 0 : 1)] + (mpos ? s.j_c : s.nq - 1 - s.j_c) + 1;
             const double c0 = mpos ? s.cq : 1.0 - s.cq;
             NoStepSink none;
-            walk_skip<R>(W, pitch, s.i0, s.i1, s.i_c, (R)fabs(s.m), (R)c0, (R)s.ua, (R)s.ub, (R)s.inv_am, acc_s + tid,
-                         (int)blockDim.x, none);
+            if (blockDim.x == 128)
+                walk_skip<R, 128>(W, pitch, s.i0, s.i1, s.i_c, (R)fabs(s.m), (R)c0, (R)s.ua, (R)s.ub, (R)s.inv_am, acc_s + tid, 128, none);
+            else
+                walk_skip<R, 0>(W, pitch, s.i0, s.i1, s.i_c, (R)fabs(s.m), (R)c0, (R)s.ua, (R)s.ub, (R)s.inv_am, acc_s + tid,
+                                (int)blockDim.x, none);
             seglen = (R)s.seglen;
         }
 
@@ -796,15 +809,6 @@ template <typename R> __device__ __forceinline__ void acc_add(R *acc, int stride
 {
     R *p = acc + label * stride;
     *p = Rn<R>::add(*p, w);
-}
-
-// One 16-bit skip word, sign-extended, through the read-only path; the address is one IMAD.WIDE from a 32-bit index.
-__device__ __forceinline__ int skip_word(const uint16_t *__restrict__ W, int o)
-{
-    int w;
-    asm("{ .reg .u64 p; .reg .s16 h; mad.wide.s32 p, %2, 2, %1; ld.global.nc.s16 h, [p]; cvt.s32.s16 %0, h; }"
-        : "=r"(w) : "l"(W), "r"(o));
-    return w;
 }
 
 // Every step serves all lanes of the warp branch-free, but how much of the general step is needed is decided per step by
@@ -1149,7 +1153,7 @@ __global__ void siddon_walk_trace_kernel(SiddonParams P, const int64_t *__restri
                           (R)s.inv_am, (R)s.inv_amz, acc, 1, sink);
         } else {
             const uint16_t *W = P.skip[(s.xmajor ? 0 : 2) + (mpos ? 0 : 1)] + (mpos ? s.j_c : s.nq - 1 - s.j_c) + 1;
-            walk_skip<R>(W, pitch, s.i0, s.i1, s.i_c, (R)fabs(s.m), (R)c0, (R)s.ua, (R)s.ub, (R)s.inv_am, acc, 1, sink);
+            walk_skip<R, 0>(W, pitch, s.i0, s.i1, s.i_c, (R)fabs(s.m), (R)c0, (R)s.ua, (R)s.ub, (R)s.inv_am, acc, 1, sink);
         }
         for (int m = 0; m < K; ++m) acc[m] = Rn<R>::mul(acc[m], (R)s.seglen);
     }
