@@ -900,8 +900,11 @@ __device__ __forceinline__ void walk_skip3(const uint16_t *__restrict__ W, int p
     }
 }
 
-template <typename R, int KT, int NSP>
-__global__ void __launch_bounds__(128) siddon_skip3_kernel(SiddonParams P, int view_begin, long long n_rays, DetectArgs d)
+// MINB: resident CTAs per SM the register allocation is held to (9: the 56 registers the kernel takes unconstrained).  Volumes whose
+// layouts are far larger than L2 walk on DRAM latency and gain from more warps (1024^3: 127.6 -> 121.7 ms at 10 CTAs);
+// L2-resident ones lose (512^3: 11.7 -> 12.4 ms) -- launch_skip chooses.
+template <typename R, int KT, int NSP, int MINB>
+__global__ void __launch_bounds__(128, MINB) siddon_skip3_kernel(SiddonParams P, int view_begin, long long n_rays, DetectArgs d)
 {
     constexpr bool PACKED = (sizeof(R) == 4) && KT > 0;
     extern __shared__ __align__(16) unsigned char smem_raw[];
@@ -1222,7 +1225,15 @@ static int launch_skip(const SiddonParams &P, int view_begin, long long n_rays, 
         return DEXCT_ECAPACITY;
     }
     void (*kern)(SiddonParams, int, long long, DetectArgs) = siddon_skip_kernel<R, KT, NSP>;
-    if (IS3D) kern = siddon_skip3_kernel<R, KT, NSP>;
+    if (IS3D) {
+        // skip layouts far beyond L2 (126 MB): the walk waits on DRAM, more resident warps help
+        const double layout_bytes = 4.0 * 2.0 * (double)P.vol.nx * P.vol.ny * P.vol.nz;
+        const char *mb = getenv("DEXCT_SID3_MINB");           // tuning knob: 9, 10 or 12
+        const int minb = mb ? atoi(mb) : (layout_bytes > 4.0e9 ? 10 : 9);
+        kern = siddon_skip3_kernel<R, KT, NSP, 9>;
+        if (sizeof(R) == 4 && minb == 10) kern = siddon_skip3_kernel<R, KT, NSP, 10>;
+        if (sizeof(R) == 4 && minb == 12) kern = siddon_skip3_kernel<R, KT, NSP, 12>;
+    }
     if (smem > 48 * 1024) DEXCT_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     int per_sm = 0;
     DEXCT_CUDA_OK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, block, smem));
