@@ -368,7 +368,11 @@ class ScanBench:
             self.push_table = self.sbuf.table(rank * slot_s, exclude_self=True)
             mode = PUSH_MODE
             if mode == 'auto':
-                mode = 'dma' if slot_s > DMA_THRESHOLD else 'fused'
+                # small shards: with the tensor-core decomposition kernel a store kernel on a side stream costs less than the
+                # copy riding inside the kernel (its compute warps have no slack to hide the peer stores in: C2 at N = 8
+                # 0.588 ms against 0.639, copy engines 1.09); the FP32-pipe kernel hid the rider better (round 1)
+                small = 'sm' if os.environ.get('DEXCT_GN_TC', '1') != '0' else 'fused'
+                mode = 'dma' if slot_s > DMA_THRESHOLD else small
             self.push_mode = mode
             self.side = [torch.cuda.Stream(device=dev) for _ in range(4)]
         else:
