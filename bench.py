@@ -61,7 +61,8 @@ SCALING = {'C5': 'strong', 'C4': 'strong', 'C2': 'weak'}
 # choice for steps of ~1 ms (C2: profiles/r01h_scaling.txt).  'dma': the copy engines carry the count/log shard beside the
 # decomposition, which runs in view chunks whose basis pixels follow on the copy engines as they finish -- no SM time, the
 # choice for GB-sized shards (C5 at N = 8: the rider stretched the GN kernel from 52 to 72 ms, profiles/r01k_configs_n8.jsonl).
-# 'auto' picks by shard size.  'sm': a separate store kernel on a side stream (kept for comparison).
+# 'auto' picks by shard size.  'sm': a separate store kernel on a side stream -- the choice for small shards since the
+# tensor-core decomposition kernel, whose compute warps have no slack for the rider (C2 at N = 8: 0.588 against 0.639 ms).
 PUSH_MODE = os.environ.get('DEXCT_PUSH', 'auto')
 PUSH_CTAS = int(os.environ.get('DEXCT_PUSH_CTAS', '16'))
 DMA_THRESHOLD = int(os.environ.get('DEXCT_DMA_THRESHOLD', str(64 << 20)))     # count/log shard bytes
