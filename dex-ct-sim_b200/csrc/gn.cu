@@ -502,10 +502,16 @@ __global__ void __launch_bounds__(256, (PX == 4 && CTAB) ? 3 : 1) gn_kernel(cons
 // What is left per (pixel, bin) on the ordinary pipes: FMUL2/FFMA2 halves for the exponent, one MUFU.EX2, one LOP3, half an
 // FADD2 -- the kernel is bound by the MUFU unit (16 ex2 per clock and SM) instead of the FMA pipe.
 constexpr int GT_KS = 8;                    // bins per MMA: 32 bytes of TF32 along K
-constexpr int GT_CHUNK_KS = 3;              // k-steps per A-operand chunk
+#ifndef GT_CHUNK_KS_VARIANT                 // (tuning builds: make variant VARFLAGS="-DGT_CHUNK_KS_VARIANT=2 -DGT_NBUF_VARIANT=3")
+#define GT_CHUNK_KS_VARIANT 3
+#endif
+#ifndef GT_NBUF_VARIANT
+#define GT_NBUF_VARIANT 2
+#endif
+constexpr int GT_CHUNK_KS = GT_CHUNK_KS_VARIANT;   // k-steps per A-operand chunk
 constexpr int GT_KCOLS = 2 * GT_KS;         // tensor-memory columns of one k-step of A: 8 heads, then 8 tails
 constexpr int GT_CH = GT_KCOLS * GT_CHUNK_KS;   // columns per chunk
-constexpr int GT_NBUF = 2;
+constexpr int GT_NBUF = GT_NBUF_VARIANT;
 constexpr int GT_COLS = 128;                // tensor-memory columns per CTA: 2 x 48 (A operand chunks) + 32 (accumulator)
 constexpr int GT_DCOL = GT_NBUF * GT_CH;
 constexpr int GT_THREADS = 160;             // four compute warps (one per 32 lanes of tensor memory) + the MMA warp

@@ -13,6 +13,9 @@ for p in (ROOT, os.path.join(ROOT, 'dex-ct-sim_b200')):
 import numpy as np  # noqa: E402
 import torch  # noqa: E402
 
+from dexct import _native  # noqa: E402
+if os.environ.get('DEXCT_LIB_VARIANT'):          # a tuning build (make -C dex-ct-sim_b200/csrc variant VARFLAGS=...)
+    _native.LIB_PATH = os.path.join(ROOT, 'dex-ct-sim_b200', 'csrc', '_build', os.environ['DEXCT_LIB_VARIANT'])
 from dexct import synthetic as S  # noqa: E402
 from dexct.ops import F32, F64, gn_decompose  # noqa: E402
 
