@@ -63,6 +63,10 @@ SCALING = {'C5': 'strong', 'C4': 'strong', 'C2': 'weak'}
 # choice for GB-sized shards (C5 at N = 8: the rider stretched the GN kernel from 52 to 72 ms, profiles/r01k_configs_n8.jsonl).
 # 'auto' picks by shard size.  'sm': a separate store kernel on a side stream -- the choice for small shards since the
 # tensor-core decomposition kernel, whose compute warps have no slack for the rider (C2 at N = 8: 0.588 against 0.639 ms).
+# kernels the tensor-core decomposition launches beyond table / kernel / fix-up: gn_first_sums_kernel, and gn_compact_kernel when
+# the air mask is on and the list of non-air pixels is not switched off
+GN_EXTRA = (0 if os.environ.get('DEXCT_GN_TC', '1') == '0' else
+            1 + (1 if os.environ.get('DEXCT_GN_COMPACT', '1') != '0' else 0))
 PUSH_MODE = os.environ.get('DEXCT_PUSH', 'auto')
 PUSH_CTAS = int(os.environ.get('DEXCT_PUSH_CTAS', '16'))
 DMA_THRESHOLD = int(os.environ.get('DEXCT_DMA_THRESHOLD', str(64 << 20)))     # count/log shard bytes
@@ -438,7 +442,7 @@ class ScanBench:
             for a, b in zip(bounds[:-1], bounds[1:]):
                 gn_decompose(counts[:, a:b].reshape(2, -1), self.i0, self.mus, GN_ITERS, mask_thresh=MASK_THRESH, dtype=code,
                              out=basis[a:b].view(-1, 2), air_key=key)
-                n += 4                                                    # strided gather copy, gn_table, gn_kernel, gn_fixup
+                n += 4 + GN_EXTRA                                         # strided gather copy, gn_table, gn_kernel, gn_fixup (+ GN_EXTRA)
                 self._dma_push(self.bbuf, rank * self.slot_b + a * per_view, basis[a:b])
             if t is not None:
                 t[2].record()
@@ -452,7 +456,7 @@ class ScanBench:
             if t is not None:
                 t[2].record()
             pg.barrier()
-            n += 6                                                        # gn_max, peer_max, gn_table, gn_kernel, gn_fixup, barrier
+            n += 6 + GN_EXTRA                                             # gn_max, peer_max, gn_table, gn_kernel, gn_fixup, barrier
         elif pg is not None:                                              # 'sm': store kernel on a side stream
             main = torch.cuda.current_stream()
             self.side[0].wait_stream(main)
@@ -464,7 +468,7 @@ class ScanBench:
                 t[2].record()
             main.wait_stream(self.side[0])
             pg.barrier()
-            n += 7
+            n += 7 + GN_EXTRA
         else:
             pending = []
             if ws > 1 and self.even:
@@ -474,7 +478,7 @@ class ScanBench:
                 pending.append(dist.all_gather_into_tensor(self.g_logs, logs, async_op=True))
             gn_decompose(counts.view(2, -1), self.i0, self.mus, GN_ITERS, mask_thresh=MASK_THRESH, dtype=code, out=basis.view(-1, 2),
                          reduce_max_over_ranks=ws > 1)
-            n += 4                                                        # gn_max, gn_table, gn_kernel, gn_fixup
+            n += 4 + GN_EXTRA                                             # gn_max, gn_table, gn_kernel, gn_fixup
             if t is not None:
                 t[2].record()
             if ws > 1 and self.even:
