@@ -12,6 +12,7 @@
 // Every thread of a warp reads the same row (broadcast LDS.128), so the kernel is bound by the FP32 FMA pipe:
 // 14 FMA + 1 MUFU.EX2 per pixel, energy and iteration.  PX pixels per thread share each row load.
 #include "common.cuh"
+#include <mutex>
 #include "tc05.cuh"
 #include <algorithm>
 #include <stdlib.h>
@@ -1337,6 +1338,89 @@ extern "C" int dexct_gn_decompose_general(const void *g, const void *i0, const v
         gn_general_kernel<double><<<grid, 128, smem, st>>>((const double *)g, (const double *)i0, (const double *)mus, nMeas, nMats, nE,
                                                          pix_bins, (long long)nE, P, n_iters, (double *)a_out);
     }
+    DEXCT_CUDA_OK(cudaGetLastError());
+    return DEXCT_OK;
+}
+
+// ---------------------------------------------------------------------------------------------------------------------
+// dexct_gn_decompose_static: the single-precision decomposition for callers that may not allocate (code under CUDA graph
+// capture, serving loops, harnesses that forbid cudaMalloc).  No counterpart in the reference.
+// Same kernels as the FP32-pipe path of dexct_gn_decompose with the table row staged in shared memory
+// (gn_max_kernel, gn_kernel<float, 4, false, 0>, gn_fixup_kernel) -- that path needs no staging buffer -- and the scratch
+// block (air-maximum key, flagged-pixel count and list: 16 + 4 P bytes) in a file-scope device array instead of caller
+// memory.  Every GPU that loads the library holds the array (4 MiB + 256 B) until exit.  All calls share it and it keeps the
+// last call's contents: the key and the counters are reset at the start of every call; calls that overlap on one GPU (two
+// streams, two threads) race on it and must be serialised by the caller.
+namespace dexct {
+constexpr long long GN_STATIC_MAX_PIXELS = DEXCT_GN_STATIC_MAX_PIXELS;
+static __device__ __align__(256) unsigned char gn_static_scratch[256 + 4 * GN_STATIC_MAX_PIXELS];
+namespace {
+std::mutex g_static_mtx;
+void *g_static_ptr[64] = {};          // device address of gn_static_scratch, per device (the symbol itself is a host stand-in)
+}  // namespace
+
+// Device address of the array on the CURRENT device, looked up once per device with that device current.
+static int gn_static_address(void **out)
+{
+    int dev = -1;
+    DEXCT_CUDA_OK(cudaGetDevice(&dev));
+    DEXCT_REQUIRE(dev >= 0 && dev < 64, "device index out of range");
+    std::lock_guard<std::mutex> lock(g_static_mtx);
+    if (!g_static_ptr[dev]) {
+        void *ptr = nullptr;
+        DEXCT_CUDA_OK(cudaGetSymbolAddress((void **)&ptr, gn_static_scratch));
+        DEXCT_REQUIRE(ptr != nullptr, "cudaGetSymbolAddress returned a null address for the static scratch array");
+        g_static_ptr[dev] = ptr;
+    }
+    *out = g_static_ptr[dev];
+    return DEXCT_OK;
+}
+}  // namespace dexct
+
+extern "C" int64_t dexct_gn_static_max_pixels(void) { return dexct::GN_STATIC_MAX_PIXELS; }
+
+extern "C" int dexct_gn_decompose_static(const void *g, const void *i0, const void *mus, int32_t nE, int64_t P, int32_t n_iters,
+                                         double mask_thresh, void *a_out, void *stream)
+{
+    if (int e = check_device()) return e;
+    DEXCT_REQUIRE(g && i0 && mus && a_out, "g, i0, mus and a_out must be non-null");
+    DEXCT_REQUIRE(nE > 0 && P >= 0 && n_iters >= 0, "nE > 0, P >= 0, n_iters >= 0 required");
+    if (P > GN_STATIC_MAX_PIXELS) {
+        set_error("dexct_gn_decompose_static: %lld pixels exceed the static scratch array (DEXCT_GN_STATIC_MAX_PIXELS = %lld): "
+                  "split the call or use dexct_gn_decompose with caller-provided scratch", (long long)P, GN_STATIC_MAX_PIXELS);
+        return DEXCT_ECAPACITY;
+    }
+    if (P == 0) return DEXCT_OK;
+    cudaStream_t st = (cudaStream_t)stream;
+    const size_t smem = sizeof(float) * (size_t)(nE + 2) * GN_ROW, fsm = sizeof(double) * 14 * (size_t)nE;
+    if (smem > 200 * 1024 || fsm > 200 * 1024) {
+        set_error("GN table needs %zu bytes of shared memory (limit 200 KiB): nE=%d", smem > fsm ? smem : fsm, nE);
+        return DEXCT_ECAPACITY;
+    }
+    void *scratch = nullptr;
+    if (int e = gn_static_address(&scratch)) return e;
+    auto kern = gn_kernel<float, 4, false, 0>;
+    if (smem > 48 * 1024) DEXCT_CUDA_OK(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    if (fsm > 48 * 1024) DEXCT_CUDA_OK(cudaFuncSetAttribute(gn_fixup_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)fsm));
+    int per_sm = 0;
+    DEXCT_CUDA_OK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, 256, smem));
+    if (per_sm < 1) per_sm = 1;
+    const long long want = (P + 1023) / 1024;
+    const long long grid = std::min<long long>((long long)sm_count() * per_sm, want);
+    // what must start from a known state: the air-maximum key (launch_max resets it) and the counters
+    if (mask_thresh > 0) {
+        if (int e = launch_max<float>(g, P, scratch, st)) return e;
+    } else {
+        DEXCT_CUDA_OK(cudaMemsetAsync(scratch, 0x80, 8, st));
+    }
+    DEXCT_CUDA_OK(cudaMemsetAsync((char *)scratch + 8, 0, 8, st));
+    const GnMirrors mir{};
+    const GnRider rider{};
+    kern<<<(unsigned)grid, 256, smem, st>>>((const float *)g, (const float *)i0, (const float *)mus, nE, P, n_iters, (float)mask_thresh,
+                                            scratch, (float *)a_out, mir, rider);
+    DEXCT_CUDA_OK(cudaGetLastError());
+    gn_fixup_kernel<<<sm_count() * 4, 128, fsm, st>>>((const float *)g, (const float *)i0, (const float *)mus, nE, P, n_iters,
+                                                      (const unsigned *)scratch, (float *)a_out, mir);
     DEXCT_CUDA_OK(cudaGetLastError());
     return DEXCT_OK;
 }

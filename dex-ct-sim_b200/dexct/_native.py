@@ -51,6 +51,8 @@ SIGNATURES = {
     'dexct_gn_decompose_general': (C.c_int, [_P, _P, _P, C.c_int32, C.c_int32, C.c_int32, C.c_int64, C.c_int32, C.c_int64,
                                              C.c_int32, _P, C.c_int32, _P]),
     'dexct_gn_scratch_bytes': (C.c_size_t, [C.c_int64, C.c_int32]),
+    'dexct_gn_static_max_pixels': (C.c_int64, []),
+    'dexct_gn_decompose_static': (C.c_int, [_P, _P, _P, C.c_int32, C.c_int64, C.c_int32, C.c_double, _P, _P]),
     'dexct_gn_air_max': (C.c_int, [_P, C.c_int64, _P, C.c_int32, _P]),
     'dexct_fbp_workspace_bytes': (C.c_size_t, [C.POINTER(DexctScan), C.c_int32, C.c_int32]),
     'dexct_fbp_fan': (C.c_int, [C.POINTER(DexctScan), _P, C.c_int32, C.c_int32, C.c_int32, C.c_double, C.c_double,

@@ -175,6 +175,21 @@ int dexct_gn_decompose_general(const void *g, const void *i0, const void *mus, i
                                int64_t n_bins, int32_t i0_per_bin, int64_t P, int32_t n_iters, void *a_out, int32_t dtype,
                                void *stream);
 
+/* Single-precision dexct_gn_decompose for callers that may not allocate device memory (code under CUDA graph capture,
+ * serving loops, harnesses that forbid cudaMalloc).  NO COUNTERPART IN THE REFERENCE.
+ * Arguments as for dexct_gn_decompose with dtype = DEXCT_F32 and no scratch: the scratch block (air-maximum
+ * key, flagged-pixel count and list) lives in a file-scope device array of the library, 4 MiB + 256 B per GPU that loads
+ * it, held until the process exits.  P <= DEXCT_GN_STATIC_MAX_PIXELS; larger calls return DEXCT_ECAPACITY with a message.
+ * The call makes no cudaMalloc / cudaFree and calls no allocating library routine.  All calls share the array, which keeps
+ * the last call's contents: what must start from zero is reset at the start of every call, and calls that overlap on one
+ * GPU (two streams, two threads) race on it -- serialise them.  Runs the FP32-pipe kernel with its table row in shared
+ * memory (not the tensor-core kernel, whose table staging buffer is allocated on first use), then the float64 pass over
+ * flagged pixels: results agree with dexct_gn_decompose to single-precision rounding (1e-5 scale-relative).              */
+#define DEXCT_GN_STATIC_MAX_PIXELS 1048576
+int64_t dexct_gn_static_max_pixels(void);
+int dexct_gn_decompose_static(const void *g_2xP, const void *i0_2xE, const void *mus_2xE, int32_t nE, int64_t P,
+                              int32_t n_iters, double mask_thresh, void *a_out_Px2, void *stream);
+
 /* max_p g1[p] (the first measurement, matdecomp.py:196) into scratch[0..8) as an order-preserving integer key:
  * int32 (DEXCT_F32) or int64 (DEXCT_F64), so that ranks holding different pixels can combine their values with an
  * integer MAX all-reduce before calling dexct_gn_decompose(..., scratch_has_max = 1).                          */
