@@ -168,7 +168,10 @@ __global__ void __launch_bounds__(128) skip_cone_kernel(SkipBuildArgs A)
 // planes k-l-1 .. k+l+1 carry the same label at both voxels of the pair, and runs of that level are capped at
 // cap_l = floor((l + 1) / mu_z) columns.  The word stores the longest run over the levels; its meaning for the walk is the
 // same as in 2-D (every voxel the ray can touch in the next S columns has label l), whatever its z slope.
-constexpr int SKIP_LEVELS = 4;       // z radii 1..4 planes
+#ifndef SKIP_LEVELS_N
+#define SKIP_LEVELS_N 4
+#endif
+constexpr int SKIP_LEVELS = SKIP_LEVELS_N;       // z radii 1..SKIP_LEVELS planes (at most 8: SiddonParams::skip_cap)
 
 // rz [k][i][j] = number of planes on BOTH sides of k (capped at SKIP_LEVELS) that carry the label of voxel (i, j, k);
 // outside the volume counts as label 0.  Reads the low bytes of a pair layout, so i is the layout's column (major) index.
@@ -1194,7 +1197,7 @@ static int make_params(const DexctScan *scan, const DexctVolume *vol, const void
                   "cone too steep for the slab traversal: a ray climbs up to %.3f slices per column (detector half-height %.4g cm "
                   "at SDD %.4g cm, dz %.4g cm, dx %.4g cm, dy %.4g cm); at most 1 is supported -- use thicker slices or fewer rows",
                   muz, zmax, scan->sdd, vol->dz, vol->dx, vol->dy);
-    for (int l = 0; l < 4; ++l) {
+    for (int l = 0; l < SKIP_LEVELS; ++l) {
         double cap = muz > 0 ? floor((l + 1) / muz) : 127.0;
         P.skip_cap[l] = (int)fmin(fmax(cap, 1.0), 127.0);
     }

@@ -79,7 +79,7 @@ struct SiddonParams {
     const uint16_t *xm, *ym;          // pair layouts; element (k, i, j) at ((k+1)*plane + i*pitch + (j+1))
     const uint16_t *skip[4];          // skip layouts (null when unavailable); element (k, i, j) at ((k+1)*plane + i*pitch + (j+1))
                                       // for 3-D scans, (i, j) at (i*pitch + (j+1)) for 2-D scans
-    int skip_cap[4];                  // 3-D: longest run allowed at z-homogeneity level l (radius l + 1 planes)
+    int skip_cap[8];                  // 3-D: longest run allowed at z-homogeneity level l (radius l + 1 planes); SKIP_LEVELS used
     int pitch_xm, pitch_ym;
     long long plane_xm, plane_ym;
     double inv_dx, inv_dy, inv_dz;    // 1/voxel size, rounded once on the host

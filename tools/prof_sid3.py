@@ -11,6 +11,9 @@ for p in (ROOT, os.path.join(ROOT, 'dex-ct-sim_b200')):
 import numpy as np  # noqa: E402
 import torch  # noqa: E402
 
+from dexct import _native  # noqa: E402
+if os.environ.get('DEXCT_LIB_VARIANT'):          # a tuning build (make -C dex-ct-sim_b200/csrc variant_sid VARFLAGS=...)
+    _native.LIB_PATH = os.path.join(ROOT, 'dex-ct-sim_b200', 'csrc', '_build', os.environ['DEXCT_LIB_VARIANT'])
 from dexct import synthetic as S  # noqa: E402
 from dexct.ops import Projector, count_segments, make_scan  # noqa: E402
 from xtomosim import forward_project as FP  # noqa: E402
